@@ -1,0 +1,505 @@
+// mlp_fwd.cu -- fused forward kernels of one MeshGraphNet message-passing step.
+//
+// Replaces, per GraphNetBlock.forward (graphphysics/models/layers.py:667-701):
+//   edge kernel: x[col]/x[row] gathers (689-690), cat (717), edge_block = 4 x Linear +
+//                ReLU + RMSNorm (718, build_mlp 101-113), scatter-sum at edge_index[1]
+//                (694-696) and the edge residual (698);
+//   node kernel: cat[x, aggr] (744), node_block (745) and the node residual (699).
+//
+// Edge layer 1 uses the split W1 = [W_e | W_i | W_j]: the per-node products
+// P = x W_i^T + b1 | x W_j^T are computed once per node (p kernel below) and gathered
+// as fp16 rows in the layer-1 epilogue, so the per-edge tensor work is e W_e^T only.
+// All products run on tcgen05 (fp16 operands, fp32 accumulation in TMEM); residual
+// streams, RMSNorm and the segmented sum are fp32.
+#include "mlp_common.cuh"
+
+using namespace mgn;
+
+struct FwdParams {
+  long long M;                // rows: E (edge) or N (node)
+  const float* in0;           // edge: e [E,128]; node: x [N,128]
+  const float* in1;           // node: aggr [N,128]
+  const int32_t* rowmap;      // edge: CSR position -> caller row of e (null = identity)
+  float* out;                 // e_out / x_out, same row convention as in0
+  const __half* P;            // edge: [N,256] fp16 (P_i + b1 | P_j)
+  const int32_t* senders;     // edge, CSR order
+  const int32_t* receivers;   // edge, CSR order
+  float* aggr;                // edge: [N,128] fp32, zero on entry, receives red.add
+  const __half* W;            // packed fp16 weight tiles
+  const float* b1;            // node only
+  const float* b2;
+  const float* b3;
+  const float* b4;
+  const float* scale;
+  __half* save_h1;            // node: optional fp16 saves of the hidden activations
+  __half* save_h2;
+  __half* save_h3;
+};
+
+__device__ __forceinline__ uint32_t stage_off_half(uint32_t row, uint32_t col) {  // 64 fp32 columns per row
+  uint32_t chunk = col >> 2;
+  return row * 256 + (((chunk & 8u) | ((chunk ^ row) & 7u)) << 4) + ((col & 3) << 2);
+}
+
+template <bool EDGE>
+__global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdParams p) {
+  constexpr int NWG = EDGE ? 2 : 1;
+  constexpr uint32_t W_BYTES = EDGE ? 4 * TILE_BYTES : 5 * TILE_BYTES;
+  constexpr uint32_t A_BYTES = EDGE ? TILE_BYTES : 2 * TILE_BYTES;
+  constexpr uint32_t K0_STEPS = EDGE ? 8 : 16;
+  constexpr uint32_t W1_BYTES = EDGE ? TILE_BYTES : 2 * TILE_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;
+  __shared__ uint64_t wbar;
+  __shared__ uint64_t mbar[NWG];
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x;
+  const int wg = tid >> 7;
+  const int t = tid & 127;          // row owned in the epilogues
+  const int w = t >> 5;             // warp within the workgroup
+  const int lane = tid & 31;
+  uint8_t* sA = smem + W_BYTES + wg * A_BYTES;
+
+  if (tid == 0) {
+    mbar_init(&wbar, 1);
+    for (int i = 0; i < NWG; ++i) mbar_init(&mbar[i], 1);
+    mbar_init_fence();
+  }
+  if ((tid >> 5) == 0) tmem_alloc<256>(&tmem_slot);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_acc = tmem_slot + wg * 128;
+  const uint32_t tmem_row = tmem_acc + ((uint32_t)(w * 32) << 16);
+
+  if (tid == 0) {
+    mbar_arrive_expect_tx(&wbar, W_BYTES);
+    for (uint32_t o = 0; o < W_BYTES; o += TILE_BYTES)
+      bulk_g2s(sW + o, reinterpret_cast<const uint8_t*>(p.W) + o, TILE_BYTES, &wbar);
+  }
+  mbar_wait(&wbar, 0);
+
+  const long long num_tiles = (p.M + TILE_ROWS - 1) / TILE_ROWS;
+  uint32_t phase = 0;
+  const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
+
+  for (long long tile = (long long)blockIdx.x * NWG + wg; tile < num_tiles; tile += (long long)gridDim.x * NWG) {
+    const long long row0 = tile * TILE_ROWS;
+    const long long grow = row0 + t;            // my row (epilogue mapping)
+    const bool rvalid = grow < p.M;
+
+    // ---- load phase: fp32 rows -> fp16 operand tile
+    if (EDGE) {
+      const int32_t* rm = p.rowmap;
+      load_rows_f32_to_tile(sA, 128, 0, p.in0, w * 32, lane, 1.0f, [&](int r) -> long long {
+        long long g = row0 + r;
+        return g < p.M ? (rm ? (long long)__ldg(rm + g) : g) : -1;
+      });
+    } else {
+      auto rf = [&](int r) -> long long { long long g = row0 + r; return g < p.M ? g : -1; };
+      load_rows_f32_to_tile(sA, 128, 0, p.in0, w * 32, lane, 1.0f, rf);
+      load_rows_f32_to_tile(sA, 128, 128, p.in1, w * 32, lane, 1.0f, rf);
+    }
+    int rcv = 0, snd = 0;
+    if (EDGE && rvalid) {
+      rcv = __ldg(p.receivers + grow);
+      snd = __ldg(p.senders + grow);
+    }
+    fence_async_smem();
+    fence_before_sync();
+    named_bar(1 + wg, 128);
+
+    // ---- layers 1..3: product, then bias/ReLU epilogue back into the operand tile
+#pragma unroll 1
+    for (int layer = 0; layer < 3; ++layer) {
+      if (t == 0) {
+        fence_after_sync();
+        if (layer == 0)
+          umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32, 128, 0, 0, 128, K0_STEPS, 0);
+        else
+          umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        mma_commit(&mbar[wg]);
+      }
+      const float* bias = layer == 0 ? p.b1 : (layer == 1 ? p.b2 : p.b3);
+      __half* save = layer == 0 ? p.save_h1 : (layer == 1 ? p.save_h2 : p.save_h3);
+      mbar_wait(&mbar[wg], phase);
+      phase ^= 1;
+      fence_after_sync();
+#pragma unroll 1
+      for (int c0 = 0; c0 < H; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_row + c0, v);
+        if (EDGE && layer == 0) {
+          uint4 pi[4], pj[4];
+          if (rvalid) {
+            const __half* Pi = p.P + (long long)rcv * 256 + c0;
+            const __half* Pj = p.P + (long long)snd * 256 + 128 + c0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { pi[j] = ldg_u4(Pi + 8 * j); pj[j] = ldg_u4(Pj + 8 * j); }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float a[8], b[8];
+            unpack8(pi[j], a);
+            unpack8(pj[j], b);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
+          }
+        } else {
+          float4 bb[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bb[j] = ldg_f4(bias + c0 + 4 * j);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
+          }
+        }
+        store_row_chunk_f16(sA, 128, t, c0, v);
+        if (!EDGE && save != nullptr && rvalid) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(save + grow * H + c0 + 8 * j) =
+                *reinterpret_cast<const uint4*>(sA + tile_off(128, t, c0 + 8 * j));
+        }
+      }
+      fence_async_smem();
+      fence_before_sync();
+      named_bar(1 + wg, 128);
+    }
+
+    // ---- layer 4 + RMSNorm + residual (+ segmented sum over receivers)
+    if (t == 0) {
+      fence_after_sync();
+      umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+      mma_commit(&mbar[wg]);
+    }
+    // coalesced-mapping bookkeeping while the product runs
+    const int hw = lane >> 4, q = lane & 15;
+    const int cbase = w * 32 + hw * 16;       // first row of my half-warp
+    const long long gq = row0 + cbase + q;
+    int my_dst = -1, my_rcv = -1;
+    if (gq < p.M) {
+      my_dst = (EDGE && p.rowmap) ? __ldg(p.rowmap + gq) : (int)gq;
+      if (EDGE) my_rcv = __ldg(p.receivers + gq);
+    }
+    mbar_wait(&mbar[wg], phase);
+    phase ^= 1;
+    fence_after_sync();
+    float ss = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < H; c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_row + c0, v);
+      float4 bb[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bb[j] = ldg_f4(p.b4 + c0 + 4 * j);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a0 = v[4 * j] + bb[j].x, a1 = v[4 * j + 1] + bb[j].y, a2 = v[4 * j + 2] + bb[j].z,
+              a3 = v[4 * j + 3] + bb[j].w;
+        ss += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+      }
+    }
+    const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+    float* stage = reinterpret_cast<float*>(sA);   // operand tile is free: reuse as fp32 staging (64 columns)
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+#pragma unroll 1
+      for (int cc = 0; cc < 64; cc += 32) {
+        const int c0 = half * 64 + cc;
+        float v[32];
+        tmem_ld32(tmem_row + c0, v);
+        float4 bb[8], sc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { bb[j] = ldg_f4(p.b4 + c0 + 4 * j); sc[j] = ldg_f4(p.scale + c0 + 4 * j); }
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 o;
+          o.x = sc[j].x * ((v[4 * j + 0] + bb[j].x) * inv);
+          o.y = sc[j].y * ((v[4 * j + 1] + bb[j].y) * inv);
+          o.z = sc[j].z * ((v[4 * j + 2] + bb[j].z) * inv);
+          o.w = sc[j].w * ((v[4 * j + 3] + bb[j].w) * inv);
+          *reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(stage) + stage_off_half(t, cc + 4 * j)) = o;
+        }
+      }
+      fence_before_sync();
+      named_bar(1 + wg, 128);
+      // coalesced phase: half-warp per row, 16 rows per half-warp, 64 columns
+      {
+        int cur = -1;
+        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+        for (int ib = 0; ib < 16; ib += 8) {
+          float4 old[8];
+          int dst[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            dst[i] = __shfl_sync(0xffffffffu, my_dst, (lane & 16) + ib + i);
+            old[i] = dst[i] >= 0 ? ld_stream_f4(p.in0 + (long long)dst[i] * H + half * 64 + 4 * q)
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = cbase + ib + i;
+            const float4 v = *reinterpret_cast<const float4*>(reinterpret_cast<const uint8_t*>(stage) +
+                                                              stage_off_half(r, 4 * q));
+            const int rc = EDGE ? __shfl_sync(0xffffffffu, my_rcv, (lane & 16) + ib + i) : -1;
+            if (dst[i] >= 0) {
+              float4 o = make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w);
+              st_stream_f4(p.out + (long long)dst[i] * H + half * 64 + 4 * q, o);
+            }
+            if (EDGE) {
+              if (rc != cur) {
+                if (cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
+                cur = rc;
+                sum = v;
+              } else {
+                sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+              }
+            }
+          }
+        }
+        if (EDGE && cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
+      }
+      named_bar(1 + wg, 128);
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  if ((tid >> 5) == 0) tmem_dealloc<256>(tmem_slot);
+}
+
+// ---------------------------------------------------------------------------------
+// p kernel: P[N,256] (fp16) = x16 * [W_i | W_j]^T + [b1 | 0]   (one N=256 product per tile)
+struct PFwdParams {
+  long long N;
+  const float* x;        // [N,128]
+  const __half* Wcat;    // panel tile, 256 rows (out) x 128 cols (in) = 64 KB
+  const float* b1;       // [128] edge-block layer-1 bias, folded into P_i
+  __half* P;             // [N,256]
+};
+
+__global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;                   // 64 KB
+  uint8_t* sA = smem + 2 * TILE_BYTES;  // 32 KB
+  __shared__ uint64_t wbar, mbar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    mbar_init(&wbar, 1);
+    mbar_init(&mbar, 1);
+    mbar_init_fence();
+  }
+  if (w == 0) tmem_alloc<256>(&tmem_slot);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_acc = tmem_slot;
+  const uint32_t tmem_row = tmem_acc + ((uint32_t)(w * 32) << 16);
+  if (tid == 0) {
+    mbar_arrive_expect_tx(&wbar, 2 * TILE_BYTES);
+    bulk_g2s(sW, p.Wcat, TILE_BYTES, &wbar);
+    bulk_g2s(sW + TILE_BYTES, reinterpret_cast<const uint8_t*>(p.Wcat) + TILE_BYTES, TILE_BYTES, &wbar);
+  }
+  mbar_wait(&wbar, 0);
+  uint32_t phase = 0;
+  const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
+  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const long long row0 = tile * TILE_ROWS;
+    load_rows_f32_to_tile(sA, 128, 0, p.x, w * 32, lane, 1.0f,
+                          [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; });
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      umma_tile(tmem_acc, smem_u32(sA), 128, 0, smem_u32(sW), 256, 0, 0, 256, 8, 0);
+      mma_commit(&mbar);
+    }
+    mbar_wait(&mbar, phase);
+    phase ^= 1;
+    fence_after_sync();
+    const long long grow = row0 + tid;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_row + c0, v);
+      tmem_ld_wait();
+      if (c0 < 128) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 bb = ldg_f4(p.b1 + c0 + 4 * j);
+          v[4 * j] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+        }
+      }
+      if (grow < p.N) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 pk;
+          pk.x = pack_h2(v[8 * j + 0], v[8 * j + 1]);
+          pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
+          pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]);
+          pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
+          *reinterpret_cast<uint4*>(p.P + grow * 256 + c0 + 8 * j) = pk;
+        }
+      }
+    }
+    fence_before_sync();
+    __syncthreads();
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (w == 0) tmem_dealloc<256>(tmem_slot);
+}
+
+// ---------------------------------------------------------------------------------
+// weight packing: fp32 nn.Linear weights [out,in] -> fp16 panel tiles (mlp_fwd_abi.cuh)
+#include "mlp_fwd_abi.cuh"
+
+struct PackParams {
+  const float* eW[4];   // edge_block.{0,2,4,6}.weight: [128,384], [128,128] x3
+  const float* nW[4];   // node_block.{0,2,4,6}.weight: [128,256], [128,128] x3
+  uint8_t* out;
+};
+
+__global__ void pack_block_kernel(const PackParams p) {
+  // one thread per 8 consecutive columns (one 16-byte chunk)
+  const int total_chunks = (int)(PK_BYTES / 16);
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < total_chunks; c += gridDim.x * blockDim.x) {
+    const int64_t byte = (int64_t)c * 16;
+    const float* src;
+    int ld, rows, cols, coff = 0, roff = 0;
+    int64_t base;
+    if (byte < PK_WCAT) {
+      int ti = (int)(byte / 32768);
+      base = (int64_t)ti * 32768; rows = 128; cols = 128;
+      src = p.eW[ti]; ld = ti == 0 ? 384 : 128;
+    } else if (byte < PK_NODE) {
+      base = PK_WCAT; rows = 256; cols = 128; src = p.eW[0]; ld = 384;
+    } else if (byte < PK_NODE + 65536) {
+      base = PK_NODE; rows = 128; cols = 256; src = p.nW[0]; ld = 256;
+    } else {
+      int ti = (int)((byte - PK_NODE - 65536) / 32768);
+      base = PK_NODE + 65536 + (int64_t)ti * 32768; rows = 128; cols = 128; src = p.nW[1 + ti]; ld = 128;
+    }
+    // invert tile_off: byte offset inside tile -> (row, col of first element of the chunk)
+    const uint32_t off = (uint32_t)(byte - base);
+    const uint32_t panel = off / (rows * 128), rem = off % (rows * 128);
+    const uint32_t row = rem / 128, pchunk = (rem % 128) / 16;
+    const uint32_t col = panel * 64 + ((pchunk ^ (row & 7)) << 3);
+    int srow = row, scol = col;
+    if (base == PK_WCAT) {            // rows 0..127: W1[:,128:256]; rows 128..255: W1[:,256:384]
+      srow = row & 127;
+      scol = col + (row < 128 ? 128 : 256);
+    }
+    (void)cols; (void)coff; (void)roff;
+    const float* s = src + (int64_t)srow * ld + scol;
+    float4 a = __ldg(reinterpret_cast<const float4*>(s)), b = __ldg(reinterpret_cast<const float4*>(s + 4));
+    uint4 pk;
+    pk.x = pack_h2(a.x, a.y); pk.y = pack_h2(a.z, a.w); pk.z = pack_h2(b.x, b.y); pk.w = pack_h2(b.z, b.w);
+    *reinterpret_cast<uint4*>(p.out + byte) = pk;
+  }
+}
+
+extern "C" int64_t mgn_packed_block_bytes(void) { return PK_BYTES; }
+
+extern "C" int mgn_pack_block(const float* eW1, const float* eW2, const float* eW3, const float* eW4,
+                              const float* nW1, const float* nW2, const float* nW3, const float* nW4,
+                              void* packed, void* stream) {
+  MGN_CHECK_ARG(eW1 && eW2 && eW3 && eW4 && nW1 && nW2 && nW3 && nW4 && packed, "pack_block: null pointer");
+  PackParams p{{eW1, eW2, eW3, eW4}, {nW1, nW2, nW3, nW4}, (uint8_t*)packed};
+  pack_block_kernel<<<88, 256, 0, (cudaStream_t)stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 2 * 32768 + 1024;
+static constexpr int NODE_FWD_SMEM = 5 * 32768 + 2 * 32768 + 1024;
+static constexpr int P_FWD_SMEM = 3 * 32768 + 1024;
+
+// GraphNetBlock edge update + aggregation (layers.py:687-698).  e_in/e_out [E,128] fp32 in
+// the caller's edge order when rowmap (= CSR perm) is given, else already in CSR order.
+extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
+                            const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                            const void* packed, const float* b2, const float* b3, const float* b4,
+                            const float* scale, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
+  MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
+  if (E == 0) return MGN_OK;
+  MGN_CHECK_ARG(e_in && e_out && P && senders && receivers && packed && b2 && b3 && b4 && scale,
+                "edge_fwd: null pointer");
+  MGN_CHECK_ARG(e_in != e_out, "edge_fwd: in-place not supported");
+  FwdParams p{};
+  p.M = E; p.in0 = e_in; p.rowmap = rowmap; p.out = e_out; p.P = (const __half*)P;
+  p.senders = senders; p.receivers = receivers; p.aggr = aggr;
+  p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
+  p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_FWD_SMEM));
+    attr = true;
+  }
+  const int64_t tiles = ceil_div64(E, TILE_ROWS);
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(tiles, 2));
+  mlp_fwd_kernel<true><<<grid, 256, EDGE_FWD_SMEM, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+// GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).
+extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                            const float* b1, const float* b2, const float* b3, const float* b4,
+                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(N > 0 && x && aggr && x_out && packed && b1 && b2 && b3 && b4 && scale, "node_fwd: bad args");
+  MGN_CHECK_ARG(x != x_out, "node_fwd: in-place not supported");
+  FwdParams p{};
+  p.M = N; p.in0 = x; p.in1 = aggr; p.out = x_out;
+  p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
+  p.b1 = b1; p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
+  p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_FWD_SMEM));
+    attr = true;
+  }
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
+  mlp_fwd_kernel<false><<<grid, 128, NODE_FWD_SMEM, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+// per-node layer-1 partial products of the edge block: P = [x W_i^T + b1 | x W_j^T] (fp16)
+extern "C" int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P,
+                         void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(N > 0 && x && packed && b1_edge && P, "p_fwd: bad args");
+  PFwdParams p{N, x, reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_WCAT),
+               b1_edge, (__half*)P};
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(p_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_FWD_SMEM));
+    attr = true;
+  }
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
+  p_fwd_kernel<<<grid, 128, P_FWD_SMEM, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}

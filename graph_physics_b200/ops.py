@@ -1,0 +1,76 @@
+"""Thin typed wrappers over the step kernels of libmgn_b200.so (no autograd here; the
+autograd glue lives in processor.py).  All tensors are CUDA, contiguous, fp32 unless
+stated; H = 128."""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib as L
+
+H = 128
+
+
+def packed_block_bytes() -> int:
+    lib = L.lib()
+    lib.mgn_packed_block_bytes.restype = L.ctypes.c_int64
+    return int(lib.mgn_packed_block_bytes())
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        raise ValueError("libmgn_b200 takes fp32 tensors, got " + str(t.dtype))
+    return t.contiguous()
+
+
+def pack_block(edge_w: Sequence[torch.Tensor], node_w: Sequence[torch.Tensor],
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """edge_w = edge_block.{0,2,4,6}.weight, node_w = node_block.{0,2,4,6}.weight ->
+    fp16 tile pack (uint8 [packed_block_bytes])."""
+    L.require_device(edge_w[0])
+    if tuple(edge_w[0].shape) != (H, 3 * H) or tuple(node_w[0].shape) != (H, 2 * H):
+        raise ValueError("libmgn_b200 supports hidden_size=128 with 3H/2H first layers only")
+    for wt in list(edge_w[1:]) + list(node_w[1:]):
+        if tuple(wt.shape) != (H, H):
+            raise ValueError("libmgn_b200 supports hidden_size=128 only")
+    if out is None:
+        out = torch.empty(packed_block_bytes(), dtype=torch.uint8, device=edge_w[0].device)
+    ew = [_f32c(w.detach()) for w in edge_w]
+    nw = [_f32c(w.detach()) for w in node_w]
+    L.check(L.lib().mgn_pack_block(*[L.p(w) for w in ew], *[L.p(w) for w in nw], L.p(out), L.stream()))
+    return out
+
+
+def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
+          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    N = x.shape[0]
+    if out is None:
+        out = torch.empty((N, 2 * H), dtype=torch.float16, device=x.device)
+    L.check(L.lib().mgn_p_fwd(L.i64(N), L.p(x), L.p(packed), L.p(b1_edge), L.p(out), L.stream()))
+    return out
+
+
+def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor, senders: torch.Tensor,
+             receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
+             e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None):
+    E = e_in.shape[0]
+    if e_out is None:
+        e_out = torch.empty_like(e_in)
+    if aggr is None:
+        aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
+    L.check(L.lib().mgn_edge_fwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
+                                 L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
+                                 L.p(scale), L.stream()))
+    return e_out, aggr
+
+
+def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
+             x_out: Optional[torch.Tensor] = None, saves=None) -> torch.Tensor:
+    N = x.shape[0]
+    if x_out is None:
+        x_out = torch.empty_like(x)
+    s1, s2, s3 = saves if saves is not None else (None, None, None)
+    L.check(L.lib().mgn_node_fwd(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
+                                 L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.stream()))
+    return x_out

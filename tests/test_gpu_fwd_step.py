@@ -1,0 +1,94 @@
+"""GPU: one message-passing step of the fused forward kernels vs the fp32/fp64 oracle.
+Tolerance (BASELINE.json north_star): relative L2 <= 1e-3 per processor step."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import graph_oracle as go
+from oracle import mgn_oracle as mo
+from oracle.synth import processor_inputs
+
+pytestmark = pytest.mark.gpu
+TOL_STEP = 1e-3
+
+
+def _block_params(seed, dtype=torch.float32):
+    return mo.init_params(1, hidden=128, seed=seed, dtype=dtype)
+
+
+def _run_step(ei_np, n, x0, e0, p, use_rowmap):
+    from graph_physics_b200 import graph as G, ops
+    dev = "cuda"
+    ei = torch.as_tensor(ei_np, dtype=torch.int64, device=dev)
+    csr = G.build_csr(ei, n)
+    pre = "processor_list.0."
+    g = {k: v.to(dev) for k, v in p.items()}
+    ew = [g[pre + f"edge_block.{i}.weight"] for i in (0, 2, 4, 6)]
+    nw = [g[pre + f"node_block.{i}.weight"] for i in (0, 2, 4, 6)]
+    packed = ops.pack_block(ew, nw)
+    xd, ed = x0.to(dev), e0.to(dev)
+    P = ops.p_fwd(xd, packed, g[pre + "edge_block.0.bias"])
+    if use_rowmap:
+        e_in, rowmap = ed, csr.perm
+    else:
+        e_in, rowmap = ed.index_select(0, csr.perm.long()).contiguous(), None
+    e_out, aggr = ops.edge_fwd(e_in, rowmap, P, csr.senders, csr.receivers, n, packed,
+                               g[pre + "edge_block.2.bias"], g[pre + "edge_block.4.bias"],
+                               g[pre + "edge_block.6.bias"], g[pre + "edge_block.7.scale"])
+    x_out = ops.node_fwd(xd, aggr, packed, g[pre + "node_block.0.bias"], g[pre + "node_block.2.bias"],
+                         g[pre + "node_block.4.bias"], g[pre + "node_block.6.bias"], g[pre + "node_block.7.scale"])
+    torch.cuda.synchronize()
+    if not use_rowmap:
+        back = torch.empty_like(e_out)
+        back[csr.perm.long()] = e_out
+        e_out = back
+    return x_out.cpu(), e_out.cpu(), aggr.cpu(), P.cpu(), csr
+
+
+@pytest.mark.parametrize("use_rowmap", [True, False])
+def test_cylinder_one_step(golden_dir, use_rowmap):
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    ei = z["edge_index"].astype(np.int64)
+    n, e = 1923, ei.shape[1]
+    p = _block_params(0)
+    x0, e0, _ = processor_inputs(n, e, 128, seed=0)
+    x1, e1, aggr, P, _ = _run_step(ei, n, x0, e0, p, use_rowmap)
+    p64 = {k: v.double() for k, v in p.items()}
+    xr, er = mo.graph_net_block(x0.double(), torch.tensor(ei), e0.double(), p64, "processor_list.0")
+    # intermediate checks make failures easy to localise
+    W1 = p64["processor_list.0.edge_block.0.weight"]
+    Pref = torch.cat([x0.double() @ W1[:, 128:256].t() + p64["processor_list.0.edge_block.0.bias"],
+                      x0.double() @ W1[:, 256:384].t()], dim=1)
+    assert mo.rel_l2(P.double(), Pref) < TOL_STEP
+    e_ = er - e0.double()
+    aggr_ref = torch.zeros(n, 128, dtype=torch.float64).index_add_(0, torch.tensor(ei[1]), e_)
+    assert mo.rel_l2(e1.double() - e0.double(), e_) < 2e-3      # the MLP output alone
+    assert mo.rel_l2(aggr.double(), aggr_ref) < 2e-3
+    assert mo.rel_l2(e1, er) < TOL_STEP
+    assert mo.rel_l2(x1, xr) < TOL_STEP
+
+
+@pytest.mark.parametrize("n,e", [(4, 8), (5, 1), (130, 129), (300, 1000), (1000, 257)])
+def test_ragged_random_graphs(n, e):
+    g = torch.Generator().manual_seed(n * 1000 + e)
+    ei = torch.randint(0, n, (2, e), generator=g).numpy()
+    p = _block_params(1)
+    x0, e0, _ = processor_inputs(n, e, 128, seed=2)
+    x1, e1, aggr, P, _ = _run_step(ei, n, x0, e0, p, True)
+    p64 = {k: v.double() for k, v in p.items()}
+    xr, er = mo.graph_net_block(x0.double(), torch.tensor(ei), e0.double(), p64, "processor_list.0")
+    assert mo.rel_l2(e1, er) < TOL_STEP
+    assert mo.rel_l2(x1, xr) < TOL_STEP
+
+
+def test_no_edges():
+    p = _block_params(1)
+    x0, e0, _ = processor_inputs(10, 0, 128, seed=2)
+    x1, e1, aggr, P, _ = _run_step(np.zeros((2, 0), np.int64), 10, x0, e0, p, True)
+    p64 = {k: v.double() for k, v in p.items()}
+    xr, er = mo.graph_net_block(x0.double(), torch.zeros((2, 0), dtype=torch.int64), e0.double(), p64,
+                                "processor_list.0")
+    assert e1.shape[0] == 0 and float(aggr.abs().max()) == 0.0
+    assert mo.rel_l2(x1, xr) < TOL_STEP
