@@ -125,4 +125,261 @@ __device__ __forceinline__ uint32_t stage_off(uint32_t row, uint32_t col) {
   return row * 512 + (((chunk & ~7u) | ((chunk ^ row) & 7u)) << 4) + ((col & 3) << 2);
 }
 
+
+// Tail of every kernel's dynamic shared memory (right after the 32 KB tile slots): the block's
+// bias / scale vectors (read by every epilogue; kept on chip because the tile slots leave no L1),
+// the mbarriers and the TMEM base slot.  Kernels use NO static shared memory so that the dynamic
+// window starts 1024-byte aligned (checked at run time).
+struct SmemTail {
+  float vec[5][128];      // b1..b4, scale (kernel-specific subset)
+  uint64_t bar[8];
+  uint32_t tmem_slot;
+  uint32_t pad[3];
+};
+static constexpr uint32_t TAIL_BYTES = 3072;
+static_assert(sizeof(SmemTail) <= TAIL_BYTES, "SmemTail too large");
+
+__device__ __forceinline__ void check_smem_alignment(const void* base) {
+  if (smem_u32(base) & 1023u) __trap();
+}
+__device__ __forceinline__ void copy_vec128(float* dst, const float* __restrict__ src, int tid, int nthreads) {
+  if (src != nullptr)
+    for (int i = tid; i < 128; i += nthreads) dst[i] = __ldg(src + i);
+}
+
+// ------------------------------------------------------------------ prefetch / misc
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// one 512-byte fp32 row = 4 lines
+__device__ __forceinline__ void prefetch_row_f32(const float* row) {
+  const char* c = reinterpret_cast<const char*>(row);
+  prefetch_l2(c); prefetch_l2(c + 128); prefetch_l2(c + 256); prefetch_l2(c + 384);
+}
+__device__ __forceinline__ void prefetch_row_f16(const __half* row) {   // 256 bytes
+  const char* c = reinterpret_cast<const char*>(row);
+  prefetch_l2(c); prefetch_l2(c + 128);
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+
+// Column sums over the 32 lanes of a warp: lane j returns sum over lanes of v[j].
+// Destroys v.  (butterfly transpose-reduce: 31 shuffles)
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = up ? v[i] : v[i + s];
+      const float keep = up ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
+}
+
+// Column sums of a 128 x 128 fp16 panel tile over all 128 rows: thread t (0..127) adds
+// rows [64*(t>>6), +64) of columns 2*(t&63), 2*(t&63)+1 into a0, a1.
+__device__ __forceinline__ void tile_colsum_pair(const uint8_t* tile, int t, float& a0, float& a1) {
+  const int cp = t & 63, rbase = (t >> 6) * 64;
+#pragma unroll 8
+  for (int r = 0; r < 64; ++r) {
+    const uint32_t u = *reinterpret_cast<const uint32_t*>(tile + tile_off(128, rbase + r, 2 * cp));
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u));
+    a0 += f.x;
+    a1 += f.y;
+  }
+}
+
+// Load NR rows (NR <= 32, multiple of BATCH) of fp32 [*,128] -> fp16 panel tile, BATCH rows in flight.
+template <int BATCH, class RowFn>
+__device__ __forceinline__ void load_rows_f32_to_tile_b(uint8_t* tile, uint32_t tile_rows, uint32_t col0,
+                                                        const float* __restrict__ src, int row0, int nrows,
+                                                        int lane, RowFn src_row) {
+#pragma unroll 1
+  for (int rb = 0; rb < nrows; rb += BATCH) {
+    float4 v[BATCH];
+#pragma unroll
+    for (int i = 0; i < BATCH; ++i) {
+      long long g = src_row(row0 + rb + i);
+      v[i] = (g >= 0) ? ld_stream_f4(src + g * H + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < BATCH; ++i) {
+      uint2 pk;
+      pk.x = pack_h2(v[i].x, v[i].y);
+      pk.y = pack_h2(v[i].z, v[i].w);
+      *reinterpret_cast<uint2*>(tile + tile_off(tile_rows, row0 + rb + i, col0 + 4 * lane)) = pk;
+    }
+  }
+}
+
+// tile row <- fp16(a[ra(r)] + b[rb(r)]) ; either source may be absent (row fn returns -1)
+template <int BATCH, class RowFnA, class RowFnB>
+__device__ __forceinline__ void load_rows_sum2_to_tile(uint8_t* tile, uint32_t col0, const float* __restrict__ a,
+                                                       const float* __restrict__ b, int row0, int nrows, int lane,
+                                                       RowFnA ra, RowFnB rb_) {
+#pragma unroll 1
+  for (int rb = 0; rb < nrows; rb += BATCH) {
+    float4 va[BATCH], vb[BATCH];
+#pragma unroll
+    for (int i = 0; i < BATCH; ++i) {
+      long long ga = ra(row0 + rb + i), gb = rb_(row0 + rb + i);
+      va[i] = (ga >= 0) ? ld_stream_f4(a + ga * H + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+      vb[i] = (gb >= 0) ? ld_stream_f4(b + gb * H + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < BATCH; ++i) {
+      uint2 pk;
+      pk.x = pack_h2(va[i].x + vb[i].x, va[i].y + vb[i].y);
+      pk.y = pack_h2(va[i].z + vb[i].z, va[i].w + vb[i].w);
+      *reinterpret_cast<uint2*>(tile + tile_off(128, row0 + rb + i, col0 + 4 * lane)) = pk;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ shared epilogues
+// hidden layer: tile row t <- fp16(relu(acc + bias))
+__device__ __forceinline__ void epi_bias_relu(uint32_t tmem_row, const float* __restrict__ bias, uint8_t* tile,
+                                              int t) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_row + c0, v);
+    float4 bb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bb[j] = ld_f4(bias + c0 + 4 * j);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
+      v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
+      v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
+      v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
+    }
+    store_row_chunk_f16(tile, 128, t, c0, v);
+  }
+}
+// ReLU backward: tile row t holds h = relu(z); overwrite with fp16(acc * [h > 0])
+__device__ __forceinline__ void epi_relu_mask_inplace(uint32_t tmem_row, uint8_t* tile, int t) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32], h[32];
+    tmem_ld32(tmem_row + c0, v);
+    load_row_chunk_f16(tile, 128, t, c0, h);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = h[j] > 0.f ? v[j] : 0.f;
+    store_row_chunk_f16(tile, 128, t, c0, v);
+  }
+}
+// epi_bias_relu + optional fp16 copy of the row chunk to save[grow, :]
+__device__ __forceinline__ void epi_bias_relu_save(uint32_t tmem_row, const float* __restrict__ bias, uint8_t* tile,
+                                                   int t, __half* save, long long grow) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_row + c0, v);
+    float4 bb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bb[j] = ld_f4(bias + c0 + 4 * j);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
+      v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
+      v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
+      v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
+    }
+    store_row_chunk_f16(tile, 128, t, c0, v);
+    if (save != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<uint4*>(save + grow * H + c0 + 8 * j) =
+            *reinterpret_cast<const uint4*>(tile + tile_off(128, t, c0 + 8 * j));
+    }
+  }
+}
+// RMSNorm backward (layers.py:49-74 differentiated): acc = z - bias, gtile row t = upstream
+// gradient g of y = scale * z * inv, inv = 1 / (||z|| d^-1/2 + eps).  Overwrites gtile row t with
+// fp16(dL/dz) and adds this warp's column sums of g * z * inv (= dL/dscale) to dsc[0..3]
+// (lane j of the warp holds column 32*k + j in dsc[k]).
+__device__ __forceinline__ void epi_rmsnorm_bwd(uint32_t tmem_row, const float* __restrict__ bias,
+                                                const float* __restrict__ scale, uint8_t* gtile, int t, int lane,
+                                                float (&dsc)[4]) {
+  float ss = 0.f, dot = 0.f;
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32], g[32];
+    tmem_ld32(tmem_row + c0, v);
+    load_row_chunk_f16(gtile, 128, t, c0, g);
+    float4 bb[8], sc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { bb[j] = ld_f4(bias + c0 + 4 * j); sc[j] = ld_f4(scale + c0 + 4 * j); }
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float z0 = v[4 * j] + bb[j].x, z1 = v[4 * j + 1] + bb[j].y, z2 = v[4 * j + 2] + bb[j].z,
+                  z3 = v[4 * j + 3] + bb[j].w;
+      ss += z0 * z0 + z1 * z1 + z2 * z2 + z3 * z3;
+      dot += sc[j].x * g[4 * j] * z0 + sc[j].y * g[4 * j + 1] * z1 + sc[j].z * g[4 * j + 2] * z2 +
+             sc[j].w * g[4 * j + 3] * z3;
+    }
+  }
+  const float r = sqrtf(ss) * INV_SQRT_H;
+  const float inv = 1.0f / (r + RMS_EPS);
+  const float k = r > 0.f ? dot * inv * inv / ((float)H * r) : 0.f;
+#pragma unroll
+  for (int cq = 0; cq < 4; ++cq) {
+    const int c0 = cq * 32;
+    float v[32], g[32], q[32];
+    tmem_ld32(tmem_row + c0, v);
+    load_row_chunk_f16(gtile, 128, t, c0, g);
+    float4 bb[8], sc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { bb[j] = ld_f4(bias + c0 + 4 * j); sc[j] = ld_f4(scale + c0 + 4 * j); }
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float b_[4] = {bb[j].x, bb[j].y, bb[j].z, bb[j].w};
+      const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float z = v[4 * j + i] + b_[i];
+        const float gg = g[4 * j + i];
+        q[4 * j + i] = gg * z * inv;
+        v[4 * j + i] = s_[i] * gg * inv - z * k;
+      }
+    }
+    store_row_chunk_f16(gtile, 128, t, c0, v);
+    dsc[cq] += warp_colsum32(q, lane);
+  }
+}
+// fp32 accumulator rows -> global with red.add (thread t owns row t): dst row pitch `ld` floats
+__device__ __forceinline__ void flush_acc_rows(uint32_t tmem_row, float* __restrict__ dst, int ld, int t) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_row + c0, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      red_add_f4(dst + (long long)t * ld + c0 + 4 * j, make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+  }
+}
+// accumulator rows -> fp32 staging tile (stage_off layout, 64 KB)
+__device__ __forceinline__ void acc_to_stage(uint32_t tmem_row, uint8_t* stage, int t) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < H; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_row + c0, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(stage + stage_off(t, c0 + 4 * j)) =
+          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  }
+}
+
 }  // namespace mgn

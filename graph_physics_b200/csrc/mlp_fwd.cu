@@ -31,7 +31,7 @@ struct FwdParams {
   const float* b3;
   const float* b4;
   const float* scale;
-  __half* save_h1;            // node: optional fp16 saves of the hidden activations
+  __half* save_h1;            // optional fp16 saves of the hidden activations (row = tile row index)
   __half* save_h2;
   __half* save_h3;
 };
@@ -49,12 +49,18 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
   constexpr uint32_t K0_STEPS = EDGE ? 8 : 16;
   constexpr uint32_t W1_BYTES = EDGE ? TILE_BYTES : 2 * TILE_BYTES;
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];
+  check_smem_alignment(smem);
   uint8_t* sW = smem;
-  __shared__ uint64_t wbar;
-  __shared__ uint64_t mbar[NWG];
-  __shared__ uint32_t tmem_slot;
+  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + W_BYTES + NWG * A_BYTES);
+  uint64_t& wbar = tail->bar[0];
+  uint64_t* mbar = &tail->bar[1];
+  uint32_t& tmem_slot = tail->tmem_slot;
+  const float* sb1 = tail->vec[0];
+  const float* sb2 = tail->vec[1];
+  const float* sb3 = tail->vec[2];
+  const float* sb4 = tail->vec[3];
+  const float* ssc = tail->vec[4];
 
   const int tid = threadIdx.x;
   const int wg = tid >> 7;
@@ -63,6 +69,11 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
   const int lane = tid & 31;
   uint8_t* sA = smem + W_BYTES + wg * A_BYTES;
 
+  copy_vec128(tail->vec[0], p.b1, tid, blockDim.x);
+  copy_vec128(tail->vec[1], p.b2, tid, blockDim.x);
+  copy_vec128(tail->vec[2], p.b3, tid, blockDim.x);
+  copy_vec128(tail->vec[3], p.b4, tid, blockDim.x);
+  copy_vec128(tail->vec[4], p.scale, tid, blockDim.x);
   if (tid == 0) {
     mbar_init(&wbar, 1);
     for (int i = 0; i < NWG; ++i) mbar_init(&mbar[i], 1);
@@ -80,99 +91,123 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
     for (uint32_t o = 0; o < W_BYTES; o += TILE_BYTES)
       bulk_g2s(sW + o, reinterpret_cast<const uint8_t*>(p.W) + o, TILE_BYTES, &wbar);
   }
-  mbar_wait(&wbar, 0);
 
   const long long num_tiles = (p.M + TILE_ROWS - 1) / TILE_ROWS;
+  const long long tile_stride = (long long)gridDim.x * NWG;
   uint32_t phase = 0;
   const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
+  bool w_ready = false;
 
-  for (long long tile = (long long)blockIdx.x * NWG + wg; tile < num_tiles; tile += (long long)gridDim.x * NWG) {
+  for (long long tile = (long long)blockIdx.x * NWG + wg; tile < num_tiles; tile += tile_stride) {
     const long long row0 = tile * TILE_ROWS;
-    const long long grow = row0 + t;            // my row (epilogue mapping)
+    const long long grow = row0 + t;            // my row (epilogue mapping); also row w*32+lane of the warp
     const bool rvalid = grow < p.M;
-
-    // ---- load phase: fp32 rows -> fp16 operand tile
-    if (EDGE) {
-      const int32_t* rm = p.rowmap;
-      load_rows_f32_to_tile(sA, 128, 0, p.in0, w * 32, lane, 1.0f, [&](int r) -> long long {
-        long long g = row0 + r;
-        return g < p.M ? (rm ? (long long)__ldg(rm + g) : g) : -1;
-      });
-    } else {
-      auto rf = [&](int r) -> long long { long long g = row0 + r; return g < p.M ? g : -1; };
-      load_rows_f32_to_tile(sA, 128, 0, p.in0, w * 32, lane, 1.0f, rf);
-      load_rows_f32_to_tile(sA, 128, 128, p.in1, w * 32, lane, 1.0f, rf);
+    int rcv = -1, snd = -1, my_dst = -1;
+    if (rvalid) {
+      my_dst = (EDGE && p.rowmap) ? __ldg(p.rowmap + grow) : (int)grow;
+      if (EDGE) {
+        rcv = __ldg(p.receivers + grow);
+        snd = __ldg(p.senders + grow);
+      }
     }
-    int rcv = 0, snd = 0;
-    if (EDGE && rvalid) {
-      rcv = __ldg(p.receivers + grow);
-      snd = __ldg(p.senders + grow);
+    // next tile of this workgroup: indices for the L2 prefetches issued below
+    const long long ngrow = grow + tile_stride * TILE_ROWS;
+    int nrcv = -1, nsnd = -1, ndst = -1;
+    if (ngrow < p.M) {
+      ndst = (EDGE && p.rowmap) ? __ldg(p.rowmap + ngrow) : (int)ngrow;
+      if (EDGE) {
+        nrcv = __ldg(p.receivers + ngrow);
+        nsnd = __ldg(p.senders + ngrow);
+      }
+    }
+
+    // ---- load phase: fp32 rows -> fp16 operand tile (16 rows in flight per warp)
+    {
+      auto rf = [&](int r) -> long long { return (long long)__shfl_sync(0xffffffffu, my_dst, r & 31); };
+      load_rows_f32_to_tile_b<16>(sA, 128, 0, p.in0, w * 32, 32, lane, rf);
+      if (!EDGE) load_rows_f32_to_tile_b<16>(sA, 128, 128, p.in1, w * 32, 32, lane, rf);
+    }
+    fence_async_smem();
+    fence_before_sync();
+    named_bar(1 + wg, 128);
+    if (!w_ready) {
+      mbar_wait(&wbar, 0);
+      w_ready = true;
+    }
+
+    // ---- layer 1
+    if (t == 0) {
+      fence_after_sync();
+      umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32, 128, 0, 0, 128, K0_STEPS, 0);
+      mma_commit(&mbar[wg]);
+    }
+    if (EDGE) {
+      uint4 pi[16], pj[16];
+      if (rvalid) {
+        const __half* Pi = p.P + (long long)rcv * 256;
+        const __half* Pj = p.P + (long long)snd * 256 + 128;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { pi[j] = ldg_u4(Pi + 8 * j); pj[j] = ldg_u4(Pj + 8 * j); }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
+      }
+      if (ndst >= 0) {
+        prefetch_row_f32(p.in0 + (long long)ndst * H);
+        prefetch_row_f16(p.P + (long long)nrcv * 256);
+        prefetch_row_f16(p.P + (long long)nsnd * 256 + 128);
+      }
+      mbar_wait(&mbar[wg], phase);
+      phase ^= 1;
+      fence_after_sync();
+#pragma unroll
+      for (int cq = 0; cq < 4; ++cq) {
+        float v[32];
+        tmem_ld32(tmem_row + cq * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float a[8], b[8];
+          unpack8(pi[cq * 4 + j], a);
+          unpack8(pj[cq * 4 + j], b);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
+        }
+        store_row_chunk_f16(sA, 128, t, cq * 32, v);
+        if (p.save_h1 != nullptr && rvalid) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(p.save_h1 + grow * H + cq * 32 + 8 * j) =
+                *reinterpret_cast<const uint4*>(sA + tile_off(128, t, cq * 32 + 8 * j));
+        }
+      }
+    } else {
+      if (ndst >= 0) {
+        prefetch_row_f32(p.in0 + (long long)ndst * H);
+        prefetch_row_f32(p.in1 + (long long)ndst * H);
+      }
+      mbar_wait(&mbar[wg], phase);
+      phase ^= 1;
+      fence_after_sync();
+      epi_bias_relu_save(tmem_row, sb1, sA, t, rvalid ? p.save_h1 : nullptr, grow);
     }
     fence_async_smem();
     fence_before_sync();
     named_bar(1 + wg, 128);
 
-    // ---- layers 1..3: product, then bias/ReLU epilogue back into the operand tile
+    // ---- layers 2, 3
 #pragma unroll 1
-    for (int layer = 0; layer < 3; ++layer) {
+    for (int layer = 1; layer < 3; ++layer) {
       if (t == 0) {
         fence_after_sync();
-        if (layer == 0)
-          umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32, 128, 0, 0, 128, K0_STEPS, 0);
-        else
-          umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
         mma_commit(&mbar[wg]);
       }
-      const float* bias = layer == 0 ? p.b1 : (layer == 1 ? p.b2 : p.b3);
-      __half* save = layer == 0 ? p.save_h1 : (layer == 1 ? p.save_h2 : p.save_h3);
       mbar_wait(&mbar[wg], phase);
       phase ^= 1;
       fence_after_sync();
-#pragma unroll 1
-      for (int c0 = 0; c0 < H; c0 += 32) {
-        float v[32];
-        tmem_ld32(tmem_row + c0, v);
-        if (EDGE && layer == 0) {
-          uint4 pi[4], pj[4];
-          if (rvalid) {
-            const __half* Pi = p.P + (long long)rcv * 256 + c0;
-            const __half* Pj = p.P + (long long)snd * 256 + 128 + c0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { pi[j] = ldg_u4(Pi + 8 * j); pj[j] = ldg_u4(Pj + 8 * j); }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
-          }
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float a[8], b[8];
-            unpack8(pi[j], a);
-            unpack8(pj[j], b);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
-          }
-        } else {
-          float4 bb[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bb[j] = ldg_f4(bias + c0 + 4 * j);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
-            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
-            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
-            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
-          }
-        }
-        store_row_chunk_f16(sA, 128, t, c0, v);
-        if (!EDGE && save != nullptr && rvalid) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(save + grow * H + c0 + 8 * j) =
-                *reinterpret_cast<const uint4*>(sA + tile_off(128, t, c0 + 8 * j));
-        }
-      }
+      __half* save = layer == 1 ? p.save_h2 : p.save_h3;
+      epi_bias_relu_save(tmem_row, layer == 1 ? sb2 : sb3, sA, t, rvalid ? save : nullptr, grow);
       fence_async_smem();
       fence_before_sync();
       named_bar(1 + wg, 128);
@@ -184,15 +219,8 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
       umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
       mma_commit(&mbar[wg]);
     }
-    // coalesced-mapping bookkeeping while the product runs
     const int hw = lane >> 4, q = lane & 15;
     const int cbase = w * 32 + hw * 16;       // first row of my half-warp
-    const long long gq = row0 + cbase + q;
-    int my_dst = -1, my_rcv = -1;
-    if (gq < p.M) {
-      my_dst = (EDGE && p.rowmap) ? __ldg(p.rowmap + gq) : (int)gq;
-      if (EDGE) my_rcv = __ldg(p.receivers + gq);
-    }
     mbar_wait(&mbar[wg], phase);
     phase ^= 1;
     fence_after_sync();
@@ -203,7 +231,7 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
       tmem_ld32(tmem_row + c0, v);
       float4 bb[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) bb[j] = ldg_f4(p.b4 + c0 + 4 * j);
+      for (int j = 0; j < 8; ++j) bb[j] = ld_f4(sb4 + c0 + 4 * j);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -216,6 +244,15 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
     float* stage = reinterpret_cast<float*>(sA);   // operand tile is free: reuse as fp32 staging (64 columns)
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
+      // residual rows of this half-warp's 16 rows: issue before the staging pass
+      float4 old[16];
+      int dst[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        dst[i] = __shfl_sync(0xffffffffu, my_dst, hw * 16 + i);
+        old[i] = dst[i] >= 0 ? ld_stream_f4(p.in0 + (long long)dst[i] * H + half * 64 + 4 * q)
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll 1
       for (int cc = 0; cc < 64; cc += 32) {
         const int c0 = half * 64 + cc;
@@ -223,7 +260,7 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
         tmem_ld32(tmem_row + c0, v);
         float4 bb[8], sc[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { bb[j] = ldg_f4(p.b4 + c0 + 4 * j); sc[j] = ldg_f4(p.scale + c0 + 4 * j); }
+        for (int j = 0; j < 8; ++j) { bb[j] = ld_f4(sb4 + c0 + 4 * j); sc[j] = ld_f4(ssc + c0 + 4 * j); }
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -241,34 +278,23 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
       {
         int cur = -1;
         float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-        for (int ib = 0; ib < 16; ib += 8) {
-          float4 old[8];
-          int dst[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            dst[i] = __shfl_sync(0xffffffffu, my_dst, (lane & 16) + ib + i);
-            old[i] = dst[i] >= 0 ? ld_stream_f4(p.in0 + (long long)dst[i] * H + half * 64 + 4 * q)
-                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < 16; ++i) {
+          const int r = cbase + i;
+          const float4 v = *reinterpret_cast<const float4*>(reinterpret_cast<const uint8_t*>(stage) +
+                                                            stage_off_half(r, 4 * q));
+          const int rc = EDGE ? __shfl_sync(0xffffffffu, rcv, hw * 16 + i) : -1;
+          if (dst[i] >= 0) {
+            float4 o = make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w);
+            st_stream_f4(p.out + (long long)dst[i] * H + half * 64 + 4 * q, o);
           }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = cbase + ib + i;
-            const float4 v = *reinterpret_cast<const float4*>(reinterpret_cast<const uint8_t*>(stage) +
-                                                              stage_off_half(r, 4 * q));
-            const int rc = EDGE ? __shfl_sync(0xffffffffu, my_rcv, (lane & 16) + ib + i) : -1;
-            if (dst[i] >= 0) {
-              float4 o = make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w);
-              st_stream_f4(p.out + (long long)dst[i] * H + half * 64 + 4 * q, o);
-            }
-            if (EDGE) {
-              if (rc != cur) {
-                if (cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
-                cur = rc;
-                sum = v;
-              } else {
-                sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
-              }
+          if (EDGE && dst[i] >= 0) {
+            if (rc != cur) {
+              if (cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
+              cur = rc;
+              sum = v;
+            } else {
+              sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
             }
           }
         }
@@ -277,6 +303,7 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
       named_bar(1 + wg, 128);
     }
   }
+  if (!w_ready) mbar_wait(&wbar, 0);   // never exit with the weight copy in flight
 
   fence_before_sync();
   __syncthreads();
@@ -294,13 +321,17 @@ struct PFwdParams {
 };
 
 __global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];
+  check_smem_alignment(smem);
   uint8_t* sW = smem;                   // 64 KB
   uint8_t* sA = smem + 2 * TILE_BYTES;  // 32 KB
-  __shared__ uint64_t wbar, mbar;
-  __shared__ uint32_t tmem_slot;
+  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 3 * TILE_BYTES);
+  uint64_t& wbar = tail->bar[0];
+  uint64_t& mbar = tail->bar[1];
+  uint32_t& tmem_slot = tail->tmem_slot;
+  const float* sb1 = tail->vec[0];
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  copy_vec128(tail->vec[0], p.b1, tid, blockDim.x);
   if (tid == 0) {
     mbar_init(&wbar, 1);
     mbar_init(&mbar, 1);
@@ -322,8 +353,12 @@ __global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const long long row0 = tile * TILE_ROWS;
-    load_rows_f32_to_tile(sA, 128, 0, p.x, w * 32, lane, 1.0f,
-                          [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; });
+    load_rows_f32_to_tile_b<16>(sA, 128, 0, p.x, w * 32, 32, lane,
+                                [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; });
+    {
+      const long long ng = row0 + (long long)gridDim.x * TILE_ROWS + tid;
+      if (ng < p.N) prefetch_row_f32(p.x + ng * H);
+    }
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
@@ -344,7 +379,7 @@ __global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
       if (c0 < 128) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          float4 bb = ldg_f4(p.b1 + c0 + 4 * j);
+          float4 bb = ld_f4(sb1 + c0 + 4 * j);
           v[4 * j] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
         }
       }
@@ -429,16 +464,16 @@ extern "C" int mgn_pack_block(const float* eW1, const float* eW2, const float* e
   return MGN_OK;
 }
 
-static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 2 * 32768 + 1024;
-static constexpr int NODE_FWD_SMEM = 5 * 32768 + 2 * 32768 + 1024;
-static constexpr int P_FWD_SMEM = 3 * 32768 + 1024;
+static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 2 * 32768 + TAIL_BYTES;
+static constexpr int NODE_FWD_SMEM = 5 * 32768 + 2 * 32768 + TAIL_BYTES;
+static constexpr int P_FWD_SMEM = 3 * 32768 + TAIL_BYTES;
 
 // GraphNetBlock edge update + aggregation (layers.py:687-698).  e_in/e_out [E,128] fp32 in
 // the caller's edge order when rowmap (= CSR perm) is given, else already in CSR order.
 extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
                             const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                             const void* packed, const float* b2, const float* b3, const float* b4,
-                            const float* scale, void* stream_) {
+                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
@@ -451,6 +486,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   p.senders = senders; p.receivers = receivers; p.aggr = aggr;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
+  p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_FWD_SMEM));

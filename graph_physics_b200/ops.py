@@ -53,15 +53,18 @@ def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
 
 def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor, senders: torch.Tensor,
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
-             e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None):
+             e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None):
+    """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
+    used by the parity tests only -- the backward kernel recomputes them)."""
     E = e_in.shape[0]
+    s1, s2, s3 = saves if saves is not None else (None, None, None)
     if e_out is None:
         e_out = torch.empty_like(e_in)
     if aggr is None:
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
     L.check(L.lib().mgn_edge_fwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
                                  L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
-                                 L.p(scale), L.stream()))
+                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.stream()))
     return e_out, aggr
 
 
@@ -74,3 +77,70 @@ def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, 
     L.check(L.lib().mgn_node_fwd(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
                                  L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.stream()))
     return x_out
+
+
+# ------------------------------------------------------------------ backward
+# flat gradient block of one GraphNetBlock, in state-dict order (csrc/mlp_fwd_abi.cuh GB_*)
+GRAD_LAYOUT = (
+    ("edge_block.0.weight", (H, 3 * H)), ("edge_block.0.bias", (H,)),
+    ("edge_block.2.weight", (H, H)), ("edge_block.2.bias", (H,)),
+    ("edge_block.4.weight", (H, H)), ("edge_block.4.bias", (H,)),
+    ("edge_block.6.weight", (H, H)), ("edge_block.6.bias", (H,)),
+    ("edge_block.7.scale", (H,)),
+    ("node_block.0.weight", (H, 2 * H)), ("node_block.0.bias", (H,)),
+    ("node_block.2.weight", (H, H)), ("node_block.2.bias", (H,)),
+    ("node_block.4.weight", (H, H)), ("node_block.4.bias", (H,)),
+    ("node_block.6.weight", (H, H)), ("node_block.6.bias", (H,)),
+    ("node_block.7.scale", (H,)),
+)
+GRAD_BLOCK_FLOATS = sum(int(torch.Size(s).numel()) for _, s in GRAD_LAYOUT)   # 181,504
+
+
+def split_grad_block(flat: torch.Tensor):
+    """flat [GRAD_BLOCK_FLOATS] -> {name: view} in GRAD_LAYOUT order (no copies)."""
+    out, off = {}, 0
+    for name, shape in GRAD_LAYOUT:
+        n = int(torch.Size(shape).numel())
+        out[name] = flat[off:off + n].view(shape)
+        off += n
+    return out
+
+
+def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, packed, b2, b3, b4, scale,
+             grad_block, g_e=None, gP=None):
+    """-> (g_e [E,128], gP [N,256] fp32).  g_eout may be None (zero upstream edge gradient)."""
+    E = e_in.shape[0]
+    if g_e is None:
+        g_e = torch.empty_like(e_in)
+    if gP is None:
+        gP = torch.empty((num_nodes, 2 * H), dtype=torch.float32, device=e_in.device)
+    L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(g_eout), L.p(g_aggr),
+                                 L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(gP), L.p(packed), L.p(b2),
+                                 L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
+    return g_e, gP
+
+
+def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None):
+    """-> (g_x direct part, g_aggr, dz1 fp16)."""
+    N = g_xout.shape[0]
+    if g_x is None:
+        g_x = torch.empty_like(g_xout)
+    if g_aggr is None:
+        g_aggr = torch.empty_like(g_xout)
+    if dz1 is None:
+        dz1 = torch.empty((N, H), dtype=torch.float16, device=g_xout.device)
+    h1, h2, h3 = saves
+    L.check(L.lib().mgn_node_bwd(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
+                                 L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
+    return g_x, g_aggr, dz1
+
+
+def p_bwd(gP, x, g_x, packed, grad_block):
+    """g_x += gP [W_i ; W_j] (in place); dW_i, dW_j, db1 into grad_block."""
+    L.check(L.lib().mgn_p_bwd(L.i64(x.shape[0]), L.p(gP), L.p(x), L.p(g_x), L.p(packed), L.p(grad_block),
+                              L.stream()))
+    return g_x
+
+
+def node_wgrad1(dz1, x, aggr, grad_block):
+    L.check(L.lib().mgn_node_wgrad1(L.i64(x.shape[0]), L.p(dz1), L.p(x), L.p(aggr), L.p(grad_block), L.stream()))

@@ -38,17 +38,39 @@ def rms_norm(x: torch.Tensor, scale: torch.Tensor, eps: float = 1e-8) -> torch.T
     return scale * (x / (rms + eps))
 
 
+def r16(t: torch.Tensor) -> torch.Tensor:
+    """fp16 rounding with a straight-through gradient.  Used only by the `emulate_fp16`
+    variants below, which restate WHERE the sm_100a kernels round their tensor-core operands
+    (weights, e, x, aggr, P and the hidden activations are fp16 operands; accumulation,
+    bias, RMSNorm, the segmented sum and both residual streams are fp32)."""
+    return t + (t.detach().half().to(t.dtype) - t.detach())
+
+
 def mlp(x: torch.Tensor, p: Dict[str, torch.Tensor], prefix: str,
-        nb_of_layers: int = 4, layer_norm: bool = True) -> torch.Tensor:
+        nb_of_layers: int = 4, layer_norm: bool = True, emulate_fp16: bool = False,
+        first_layer_extra: Optional[torch.Tensor] = None, masks=None) -> torch.Tensor:
     """build_mlp (layers.py:77-113): Linear,ReLU,(Linear,ReLU)*(L-2),Linear,[RMSNorm];
-    Sequential indices 0,2,4,... are the Linear layers, 2L-1 the norm."""
+    Sequential indices 0,2,4,... are the Linear layers, 2L-1 the norm.
+
+    emulate_fp16: operands of every Linear are rounded to fp16 (straight-through).
+    first_layer_extra: the kernels' split of edge layer 1 -- the first Linear sees only the
+    edge-latent columns of W1 and the per-node partial products are added (emulation only).
+    masks: optional list of 0/1 tensors; ReLU i is replaced by multiplication with masks[i]
+    (lets a test differentiate THROUGH THE SAME ACTIVE SET as the device kernels, whose
+    fp32-accumulated pre-activations can differ in sign from fp64 ones when they are ~0)."""
     h = x
     for i in range(nb_of_layers):
         w = p[f"{prefix}.{2 * i}.weight"]
         b = p[f"{prefix}.{2 * i}.bias"]
-        h = torch.nn.functional.linear(h, w, b)
+        if emulate_fp16:
+            w = r16(w)
+            h = r16(h)
+        if i == 0 and first_layer_extra is not None:
+            h = torch.nn.functional.linear(h, w[:, :h.shape[-1]]) + first_layer_extra
+        else:
+            h = torch.nn.functional.linear(h, w, b)
         if i < nb_of_layers - 1:
-            h = torch.relu(h)
+            h = torch.relu(h) if masks is None else h * masks[i]
     if layer_norm:
         h = rms_norm(h, p[f"{prefix}.{2 * nb_of_layers - 1}.scale"])
     return h
@@ -56,7 +78,8 @@ def mlp(x: torch.Tensor, p: Dict[str, torch.Tensor], prefix: str,
 
 def graph_net_block(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
                     p: Dict[str, torch.Tensor], prefix: str = "",
-                    nb_of_layers: int = 4, layer_norm: bool = True):
+                    nb_of_layers: int = 4, layer_norm: bool = True, emulate_fp16: bool = False,
+                    edge_masks=None, node_masks=None):
     """GraphNetBlock.forward (layers.py:667-701).
 
     row = edge_index[0] (sender j), col = edge_index[1] (receiver i);
@@ -65,9 +88,26 @@ def graph_net_block(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.
          MessagePassing(aggr="add", flow="source_to_target") -> scatter-sum)
     x_ = node_block(cat[x, a])                         (layers.py:744-746)
     returns (x + x_, e + e_)                           (layers.py:698-699)
+
+    emulate_fp16=True restates the kernels' rounding points (see r16): the same function
+    of the same parameters, with fp16 tensor-core operands and the algebraic split of edge
+    layer 1 into per-node partial products P = [x W_i^T + b1 | x W_j^T] stored in fp16.
     """
     pre = prefix + "." if prefix and not prefix.endswith(".") else prefix
     row, col = edge_index[0], edge_index[1]
+    if emulate_fp16:
+        hd = x.shape[-1]
+        w1 = r16(p[pre + "edge_block.0.weight"])
+        x16 = r16(x)
+        p_i = r16(torch.nn.functional.linear(x16, w1[:, hd:2 * hd], p[pre + "edge_block.0.bias"]))
+        p_j = r16(torch.nn.functional.linear(x16, w1[:, 2 * hd:3 * hd]))
+        extra = p_i.index_select(0, col) + p_j.index_select(0, row)
+        e_ = mlp(edge_attr, p, pre + "edge_block", nb_of_layers, layer_norm, True, first_layer_extra=extra,
+                 masks=edge_masks)
+        aggr = torch.zeros_like(x).index_add_(0, col, e_)
+        x_ = mlp(torch.cat([x, aggr], dim=-1), p, pre + "node_block", nb_of_layers, layer_norm, True,
+                 masks=node_masks)
+        return x + x_, edge_attr + e_
     x_i = x.index_select(0, col)
     x_j = x.index_select(0, row)
     e_ = mlp(torch.cat([edge_attr, x_i, x_j], dim=-1), p, pre + "edge_block", nb_of_layers, layer_norm)
@@ -78,11 +118,11 @@ def graph_net_block(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.
 
 def processor(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
               p: Dict[str, torch.Tensor], num_steps: int, prefix: str = "processor_list",
-              return_all: bool = False):
+              return_all: bool = False, emulate_fp16: bool = False):
     """The hot loop `for block in self.processor_list` (processors.py:130-131)."""
     xs, es = [], []
     for k in range(num_steps):
-        x, edge_attr = graph_net_block(x, edge_index, edge_attr, p, f"{prefix}.{k}")
+        x, edge_attr = graph_net_block(x, edge_index, edge_attr, p, f"{prefix}.{k}", emulate_fp16=emulate_fp16)
         if return_all:
             xs.append(x)
             es.append(edge_attr)

@@ -1,0 +1,123 @@
+"""GPU: backward of one message-passing step (fused sm_100a kernels called through the C ABI)
+vs autograd of the CPU oracle.
+
+BASELINE.json states no gradient tolerance.  Two are used (DESIGN.md "Numerics"):
+ * TOL_GRAD = 5e-3 relative L2 against the oracle evaluated in fp64 WITH the kernels' operand
+   rounding points (oracle `emulate_fp16=True`) and differentiated through the SAME ReLU active
+   set as the device (masks = [h > 0] of the hidden activations the forward kernels computed):
+   this isolates the backward kernels' own error.
+ * TOL_GRAD_EXACT = 0.15 against the exact fp64 oracle.  A ReLU network's gradient is
+   discontinuous in the pre-activations: any 10-bit-mantissa forward (fp16 here, TF32 in the
+   reference, train.py:28) flips the ReLU mask of the ~4e-4 fraction of units whose
+   pre-activation is within rounding error of 0, which moves the gradient by sqrt(fraction)
+   ~ 1.5-3.5 % per MLP although the forward agrees to 3e-4.  The fp64 emulation alone (no GPU)
+   shows the same deviation (tests/test_oracle_golden.py::test_relu_mask_sensitivity)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mgn_oracle as mo
+from oracle.synth import processor_inputs
+
+pytestmark = pytest.mark.gpu
+TOL_GRAD = 5e-3
+TOL_GRAD_EXACT = 0.15
+
+
+def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
+    from graph_physics_b200 import graph as G, ops
+    dev = "cuda"
+    ei = torch.as_tensor(ei_np, dtype=torch.int64, device=dev)
+    csr = G.build_csr(ei, n)
+    pre = "processor_list.0."
+    g = {k: v.to(dev) for k, v in p.items()}
+    ew = [g[pre + f"edge_block.{i}.weight"] for i in (0, 2, 4, 6)]
+    nw = [g[pre + f"node_block.{i}.weight"] for i in (0, 2, 4, 6)]
+    eb = [g[pre + f"edge_block.{i}.bias"] for i in (0, 2, 4, 6)]
+    nb = [g[pre + f"node_block.{i}.bias"] for i in (0, 2, 4, 6)]
+    esc, nsc = g[pre + "edge_block.7.scale"], g[pre + "node_block.7.scale"]
+    packed = ops.pack_block(ew, nw)
+    xd, ed = x0.to(dev), e0.to(dev)
+    perm = csr.perm.long()
+    if use_rowmap:
+        e_in, rowmap = ed, csr.perm
+        ge = None if ge1 is None else ge1.to(dev)
+    else:
+        e_in, rowmap = ed.index_select(0, perm).contiguous(), None
+        ge = None if ge1 is None else ge1.to(dev).index_select(0, perm).contiguous()
+    P = ops.p_fwd(xd, packed, eb[0])
+    E = ed.shape[0]
+    esaves = tuple(torch.zeros((E, 128), dtype=torch.float16, device=dev) for _ in range(3))
+    e_out, aggr = ops.edge_fwd(e_in, rowmap, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3], esc,
+                               saves=esaves)
+    saves = tuple(torch.empty((n, 128), dtype=torch.float16, device=dev) for _ in range(3))
+    x_out = ops.node_fwd(xd, aggr, packed, nb[0], nb[1], nb[2], nb[3], nsc, saves=saves)
+    grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
+    g_x, g_aggr, dz1 = ops.node_bwd(gx1.to(dev), saves, packed, nb[3], nsc, grad)
+    ops.node_wgrad1(dz1, xd, aggr, grad)
+    g_e, gP = ops.edge_bwd(e_in, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3],
+                           esc, grad)
+    ops.p_bwd(gP, xd, g_x, packed, grad)
+    torch.cuda.synchronize()
+    if not use_rowmap:
+        back = torch.empty_like(g_e)
+        back[perm] = g_e
+        g_e = back
+    emasks = []
+    for hs in esaves:      # CSR position -> caller edge order
+        m = torch.empty_like(hs, dtype=torch.float64)
+        m[perm] = (hs > 0).double()
+        emasks.append(m.cpu())
+    nmasks = [(hs > 0).double().cpu() for hs in saves]
+    return (g_x.cpu(), g_e.cpu(), {k: v.cpu() for k, v in ops.split_grad_block(grad).items()}, emasks, nmasks)
+
+
+def _oracle(ei_np, x0, e0, gx1, ge1, p, emulate, emasks=None, nmasks=None):
+    p64 = {k: v.double().requires_grad_(True) for k, v in p.items()}
+    x = x0.double().requires_grad_(True)
+    e = e0.double().requires_grad_(True)
+    x1, e1 = mo.graph_net_block(x, torch.as_tensor(ei_np, dtype=torch.int64), e, p64, "processor_list.0",
+                                emulate_fp16=emulate, edge_masks=emasks if emulate else None,
+                                node_masks=nmasks if emulate else None)
+    loss = (x1 * gx1.double()).sum()
+    if ge1 is not None:
+        loss = loss + (e1 * ge1.double()).sum()
+    loss.backward()
+    return x.grad, e.grad, {k[len("processor_list.0."):]: v.grad for k, v in p64.items()}
+
+
+def _check(ei, n, e, seed, with_ge, use_rowmap=True):
+    p = mo.init_params(1, hidden=128, seed=seed)
+    x0, e0, _ = processor_inputs(n, e, 128, seed=seed + 1)
+    g = torch.Generator().manual_seed(seed + 7)
+    gx1 = torch.randn(n, 128, generator=g)
+    ge1 = torch.randn(e, 128, generator=g) * 0.3 if with_ge else None
+    g_x, g_e, grads, emasks, nmasks = _step_fwd_bwd(ei, n, x0, e0, gx1, ge1, p, use_rowmap)
+    out = {}
+    for emulate, tol in ((True, TOL_GRAD), (False, TOL_GRAD_EXACT)):
+        rx, re, rgrads = _oracle(ei, x0, e0, gx1, ge1, p, emulate, emasks, nmasks)
+        errs = {"g_x": mo.rel_l2(g_x, rx), "g_e": mo.rel_l2(g_e, re)}
+        for k, v in grads.items():
+            errs[k] = mo.rel_l2(v, rgrads[k])
+        bad = {k: v for k, v in errs.items() if not v < tol}
+        assert not bad, f"emulate={emulate}: rel-L2 over {tol}: {bad}\nall: {errs}"
+        out[emulate] = errs
+    print("max rel-L2 vs fp16-operand oracle %.2e, vs exact oracle %.2e" %
+          (max(out[True].values()), max(out[False].values())))
+    return out
+
+
+@pytest.mark.parametrize("with_ge,use_rowmap", [(True, True), (False, True), (True, False)])
+def test_cylinder_step_bwd(golden_dir, with_ge, use_rowmap):
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    ei = z["edge_index"].astype(np.int64)
+    _check(ei, 1923, ei.shape[1], 0, with_ge, use_rowmap)
+
+
+@pytest.mark.parametrize("n,e", [(4, 8), (5, 1), (130, 129), (300, 1000), (1000, 257), (700, 40000)])
+def test_ragged_random_graphs_bwd(n, e):
+    g = torch.Generator().manual_seed(n * 1000 + e)
+    ei = torch.randint(0, n, (2, e), generator=g).numpy()
+    _check(ei, n, e, 3, True)
