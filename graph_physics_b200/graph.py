@@ -200,6 +200,14 @@ class CSRGraph:
     receivers: torch.Tensor   # [E] int32, CSR order (non-decreasing)
     identity: bool            # perm == arange (caller order already receiver-sorted)
 
+    @property
+    def perm_long(self) -> torch.Tensor:
+        pl = getattr(self, "_perm_long", None)
+        if pl is None:
+            pl = self.perm.long()
+            object.__setattr__(self, "_perm_long", pl)
+        return pl
+
 
 def build_csr(edge_index: torch.Tensor, num_nodes: int) -> CSRGraph:
     L.require_device(edge_index)

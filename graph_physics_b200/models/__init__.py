@@ -1,0 +1,3 @@
+"""Mirror of the `graphphysics.models` surface for the MeshGraphNet path."""
+from .layers import GraphNetBlock, RMSNorm, build_mlp  # noqa: F401
+from .processors import EncodeProcessDecode, Graph  # noqa: F401

@@ -1,0 +1,96 @@
+"""Drop-in `graphphysics.models.layers` surface for the MeshGraphNet path: RMSNorm,
+build_mlp and GraphNetBlock with the reference's signatures, attribute names and
+state-dict keys (graphphysics/models/layers.py:18-113, 630-746), without torch_geometric.
+
+GraphNetBlock.forward runs on the fused sm_100a kernels (graph_physics_b200.processor);
+it needs CUDA tensors on a B200 and raises otherwise -- there is no eager fallback.
+RMSNorm / build_mlp are ordinary torch modules: they hold the parameters (so AdamW,
+state_dict, Lightning checkpoints keep working) and serve the encoder / decoder MLPs,
+which are outside the processor hot path.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .. import processor as _proc
+
+
+class RMSNorm(nn.Module):
+    """y = scale * x / (||x||_2 * d^-1/2 + eps)  (reference layers.py:18-74; eps is added to
+    the RMS, no mean subtraction; `p` selects partial RMSNorm as in the reference)."""
+
+    def __init__(self, d, p=-1.0, eps=1e-8, bias=False):
+        super().__init__()
+        self.eps = eps
+        self.d = d
+        self.p = p
+        self.bias = bias
+        self.scale = nn.Parameter(torch.ones(d))
+        self.register_parameter("scale", self.scale)
+        if self.bias:
+            self.offset = nn.Parameter(torch.zeros(d))
+            self.register_parameter("offset", self.offset)
+
+    def forward(self, x):
+        if self.p < 0.0 or self.p > 1.0:
+            norm_x = x.norm(2, dim=-1, keepdim=True)
+            d_x = self.d
+        else:
+            partial_size = int(self.d * self.p)
+            partial_x, _ = torch.split(x, [partial_size, self.d - partial_size], dim=-1)
+            norm_x = partial_x.norm(2, dim=-1, keepdim=True)
+            d_x = partial_size
+        rms_x = norm_x * d_x ** (-1.0 / 2)
+        x_normed = x / (rms_x + self.eps)
+        if self.bias:
+            return self.scale * x_normed + self.offset
+        return self.scale * x_normed
+
+
+def build_mlp(in_size: int, hidden_size: int, out_size: int, nb_of_layers: int = 4,
+              layer_norm: bool = True) -> nn.Module:
+    """Linear, ReLU, (Linear, ReLU) * (L-2), Linear, [RMSNorm] as an nn.Sequential with the
+    reference's module indices (layers.py:77-113)."""
+    assert nb_of_layers >= 2, "The MLP must have at least 2 layers (input and output)."
+    layers = [nn.Linear(in_size, hidden_size), nn.ReLU()]
+    for _ in range(nb_of_layers - 2):
+        layers.extend([nn.Linear(hidden_size, hidden_size), nn.ReLU()])
+    layers.append(nn.Linear(hidden_size, out_size))
+    module = nn.Sequential(*layers)
+    if layer_norm:
+        module = nn.Sequential(*module, RMSNorm(out_size))
+    return module
+
+
+def block_param_list(block: "GraphNetBlock"):
+    """The 18 parameters of a block in ops.GRAD_LAYOUT (= state-dict) order."""
+    eb, nb = block.edge_block, block.node_block
+    return [eb[0].weight, eb[0].bias, eb[2].weight, eb[2].bias, eb[4].weight, eb[4].bias, eb[6].weight,
+            eb[6].bias, eb[7].scale,
+            nb[0].weight, nb[0].bias, nb[2].weight, nb[2].bias, nb[4].weight, nb[4].bias, nb[6].weight,
+            nb[6].bias, nb[7].scale]
+
+
+class GraphNetBlock(nn.Module):
+    """One message-passing step (reference layers.py:630-746):
+       e_ = edge_block(cat[e, x[col], x[row]]); a = scatter-sum of e_ at col;
+       x_ = node_block(cat[x, a]); returns (x + x_, e + e_), edges in the caller's order."""
+
+    def __init__(self, hidden_size: int, nb_of_layers: int = 4, layer_norm: bool = True):
+        super().__init__()
+        self.hidden_size = hidden_size
+        self.nb_of_layers = nb_of_layers
+        self.layer_norm = layer_norm
+        self.edge_block = build_mlp(3 * hidden_size, hidden_size, hidden_size, nb_of_layers, layer_norm)
+        self.node_block = build_mlp(2 * hidden_size, hidden_size, hidden_size, nb_of_layers, layer_norm)
+
+    def check_supported(self):
+        if self.hidden_size != 128 or self.nb_of_layers != 4 or not self.layer_norm:
+            raise ValueError("graph_physics_b200.GraphNetBlock: the sm_100a kernels are built for hidden_size=128, "
+                             "nb_of_layers=4, layer_norm=True (the configuration EncodeProcessDecode uses); "
+                             "there is no eager fallback")
+
+    def forward(self, x, edge_index, edge_attr, size=None):
+        self.check_supported()
+        return _proc.run_processor(x, edge_index, edge_attr, [block_param_list(self)])

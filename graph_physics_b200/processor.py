@@ -1,0 +1,209 @@
+"""The MeshGraphNet processor loop (`for block in self.processor_list`,
+graphphysics/models/processors.py:130-131) as ONE autograd node over the fused sm_100a
+kernels of libmgn_b200.so.
+
+Per step k (GraphNetBlock.forward, graphphysics/models/layers.py:667-701):
+  forward   P_k = p_fwd(x_k) ; e_{k+1}, aggr_k = edge_fwd(e_k, P_k) ; x_{k+1} = node_fwd(x_k, aggr_k)
+  backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, gP ; p_bwd -> g_x += ...
+Saved per step: x_k, e_k (the residual streams themselves), aggr_k, P_k (fp16) and the node
+MLP's three hidden activations (fp16).  The edge MLP's hidden activations are recomputed.
+
+Edge latents run in receiver-sorted (CSR) order inside the loop; they are permuted once on
+entry and once on exit.  Gradients are multiplied by a power of two on entry to the backward
+sweep (and divided on exit) so that the fp16 tensor-core operands keep their precision; the
+sweep is linear in the gradient, so this is exact up to fp32 rounding.
+
+There is no CPU / eager fallback: everything here raises unless the tensors are on an
+sm_100 device and the library is built.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from . import graph as G
+from . import ops
+
+H = ops.H
+PARAM_NAMES = tuple(n for n, _ in ops.GRAD_LAYOUT)          # 18 per block, state-dict order
+_E_W = (0, 2, 4, 6)
+_E_B = (1, 3, 5, 7)
+_N_W = (9, 11, 13, 15)
+_N_B = (10, 12, 14, 16)
+
+# ---- instrumentation used by bench.py (kernel launch counter, per-kernel CUDA events)
+LAUNCHES = 0
+EVENTS: Optional[dict] = None      # name -> list of (start, end) torch.cuda.Event pairs when enabled
+
+
+def _timed(name, fn, *a, **kw):
+    global LAUNCHES
+    LAUNCHES += 1
+    if EVENTS is not None and name in EVENTS:
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        r = fn(*a, **kw)
+        e.record()
+        EVENTS[name].append((s, e))
+        return r
+    return fn(*a, **kw)
+
+
+_csr_cache: dict = {}
+
+
+def csr_for(edge_index: torch.Tensor, num_nodes: int) -> G.CSRGraph:
+    """Receiver-sorted CSR of `edge_index`, cached on the tensor's identity and version (the
+    topology is constant along a trajectory; the reference caches K-hop edges the same way,
+    graphphysics/dataset/dataset.py:149-168)."""
+    key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, int(num_nodes),
+           edge_index.device.index)
+    hit = _csr_cache.get(key)
+    if hit is not None:
+        return hit
+    if len(_csr_cache) > 16:
+        _csr_cache.clear()
+    csr = G.build_csr(edge_index, num_nodes)
+    _csr_cache[key] = csr
+    return csr
+
+
+def _check_inputs(x, e, params, num_steps):
+    L.require_device(x)
+    if x.dtype != torch.float32 or e.dtype != torch.float32:
+        raise ValueError("graph_physics_b200 processor takes fp32 latents")
+    if x.dim() != 2 or x.shape[1] != H or e.dim() != 2 or e.shape[1] != H:
+        raise ValueError(f"graph_physics_b200 processor supports hidden_size={H} only; got x {tuple(x.shape)}, "
+                         f"edge_attr {tuple(e.shape)}")
+    if len(params) != 18 * num_steps:
+        raise ValueError("expected 18 parameters per GraphNetBlock (nb_of_layers=4, layer_norm=True)")
+
+
+class _ProcessorFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x0, e0, csr, num_steps, *params):
+        ctx.set_materialize_grads(False)
+        K = int(num_steps)
+        _check_inputs(x0, e0, params, K)
+        dev = x0.device
+        N, E = x0.shape[0], e0.shape[0]
+        need_grad = any(ctx.needs_input_grad)   # False under torch.no_grad() / all-frozen inputs
+        prm = [p.detach().contiguous() for p in params]
+        packed = torch.empty((K, ops.packed_block_bytes()), dtype=torch.uint8, device=dev)
+        for k in range(K):
+            b = prm[18 * k:18 * (k + 1)]
+            _timed("pack", ops.pack_block, [b[i] for i in _E_W], [b[i] for i in _N_W], out=packed[k])
+        x = x0.detach().contiguous()
+        if csr.identity:
+            e = e0.detach().contiguous()
+        else:
+            e = e0.detach().index_select(0, csr.perm_long)
+        xs, es, aggrs, Ps, saves = [x], [e], [], [], []
+        if not need_grad:   # inference: ping-pong buffers, nothing kept
+            P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
+            aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
+            x_bufs = [torch.empty_like(x) for _ in range(min(K, 2))]
+            e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))]
+        for k in range(K):
+            b = prm[18 * k:18 * (k + 1)]
+            if need_grad:
+                P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
+                aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
+                e_out = torch.empty_like(e)
+                x_out = torch.empty_like(x)
+                sv = tuple(torch.empty((N, H), dtype=torch.float16, device=dev) for _ in range(3))
+            else:
+                e_out, x_out, sv = e_bufs[k & 1], x_bufs[k & 1], None
+            _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
+            _timed("edge_fwd", ops.edge_fwd, e, None, P, csr.senders, csr.receivers, N, packed[k], b[3], b[5], b[7],
+                   b[8], e_out=e_out, aggr=aggr)
+            _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
+                   saves=sv)
+            if need_grad:
+                aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); es.append(e_out)
+            x, e = x_out, e_out
+        if csr.identity:
+            e_ret = e
+        else:
+            e_ret = torch.empty_like(e)
+            e_ret.index_copy_(0, csr.perm_long, e)
+        if need_grad:
+            ctx.csr, ctx.K, ctx.packed, ctx.prm = csr, K, packed, prm
+            ctx.xs, ctx.es, ctx.aggrs, ctx.Ps, ctx.saves = xs, es, aggrs, Ps, saves
+        return x, e_ret
+
+    @staticmethod
+    def backward(ctx, g_x, g_e):
+        csr, K, packed, prm = ctx.csr, ctx.K, ctx.packed, ctx.prm
+        xs, es = ctx.xs, ctx.es
+        dev = xs[0].device
+        N, E = xs[0].shape[0], es[0].shape[0]
+        if g_x is None and g_e is None:
+            return (None,) * (4 + 18 * K)
+        # ---- power-of-two gradient scale (device-side, no host sync)
+        amax = torch.zeros((), dtype=torch.float32, device=dev)
+        if g_x is not None:
+            amax = torch.maximum(amax, g_x.detach().abs().max())
+        if g_e is not None:
+            amax = torch.maximum(amax, g_e.detach().abs().max())
+        s = torch.exp2(torch.floor(torch.log2(64.0 / amax.clamp_min(1e-30)))).clamp(2.0 ** -100, 2.0 ** 100)
+        inv_s = 1.0 / s
+        gx = (g_x.detach() * s) if g_x is not None else torch.zeros((N, H), dtype=torch.float32, device=dev)
+        gx = gx.contiguous()
+        if g_e is not None:
+            ge = g_e.detach() if csr.identity else g_e.detach().index_select(0, csr.perm_long)
+            ge = (ge * s).contiguous()
+        else:
+            ge = None
+        grads = torch.zeros((K, ops.GRAD_BLOCK_FLOATS), dtype=torch.float32, device=dev)
+        gx_new = torch.empty_like(gx)
+        g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
+        dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
+        gP = torch.empty((N, 2 * H), dtype=torch.float32, device=dev)
+        ge_bufs = [torch.empty((E, H), dtype=torch.float32, device=dev) for _ in range(2 if K > 1 else 1)]
+        for k in range(K - 1, -1, -1):
+            b = prm[18 * k:18 * (k + 1)]
+            _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
+                   g_aggr=g_aggr, dz1=dz1)
+            _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
+            ge_out = ge_bufs[k & 1] if len(ge_bufs) > 1 else ge_bufs[0]
+            _timed("edge_bwd", ops.edge_bwd, es[k], None, ge, g_aggr, ctx.Ps[k], csr.senders, csr.receivers, N,
+                   packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_out, gP=gP)
+            _timed("p_bwd", ops.p_bwd, gP, xs[k], gx_new, packed[k], grads[k])
+            gx, gx_new = gx_new, gx
+            ge = ge_out
+            # release what this step saved
+            ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None
+            xs[k + 1] = None; es[k + 1] = None
+        grads.mul_(inv_s)
+        g_x0 = gx * inv_s if ctx.needs_input_grad[0] else None
+        g_e0 = None
+        if ctx.needs_input_grad[1]:
+            ge = ge * inv_s
+            if csr.identity:
+                g_e0 = ge
+            else:
+                g_e0 = torch.empty_like(ge)
+                g_e0.index_copy_(0, csr.perm_long, ge)
+        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None]
+        for k in range(K):
+            views = ops.split_grad_block(grads[k])
+            for i, name in enumerate(PARAM_NAMES):
+                out.append(views[name] if ctx.needs_input_grad[4 + 18 * k + i] else None)
+        return tuple(out)
+
+
+def run_processor(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
+                  block_params: Sequence[Sequence[torch.Tensor]], csr: Optional[G.CSRGraph] = None):
+    """x [N,128], edge_index [2,E] int64, edge_attr [E,128] (caller's edge order),
+    block_params: per GraphNetBlock the 18 tensors in ops.GRAD_LAYOUT order.
+    Returns (x_K, edge_attr_K) with edge_attr_K in the caller's edge order."""
+    L.require_device(x)
+    if csr is None:
+        csr = csr_for(edge_index, x.shape[0])
+    if csr.num_edges != edge_attr.shape[0] or csr.num_nodes != x.shape[0]:
+        raise ValueError("edge_index / edge_attr / x sizes disagree")
+    flat = [t for blk in block_params for t in blk]
+    return _ProcessorFn.apply(x, edge_attr, csr, len(block_params), *flat)

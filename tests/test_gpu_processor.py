@@ -1,0 +1,135 @@
+"""GPU: the 15-step processor through the reference-facing module API
+(graph_physics_b200.models.EncodeProcessDecode / GraphNetBlock) vs the committed fixture that
+the reference's own source produced (tests/golden/ref_cylinder_h128_s15.npz) and vs the CPU oracle.
+
+Tolerances (BASELINE.json north_star): relative L2 <= 1e-3 per processor step, <= 5e-3 after 15
+steps.  Gradients after 15 steps: see tests/test_gpu_bwd_step.py for the tight per-step check; here
+the 15-step gradient is compared with the exact fp32 reference run, where ReLU-mask flips of
+near-zero pre-activations (inherent to any 10-bit-mantissa forward, TF32 included) accumulate."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mgn_oracle as mo
+from oracle.synth import processor_inputs
+
+pytestmark = pytest.mark.gpu
+TOL_STEP, TOL_15 = 1e-3, 5e-3
+TOL_GRAD_15 = 0.35
+
+
+def _load(model, params):
+    sd = model.state_dict()
+    assert set(sd) == set(params), (set(sd) ^ set(params))
+    model.load_state_dict({k: v.clone() for k, v in params.items()})
+
+
+def _cyl(golden_dir):
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    return torch.as_tensor(z["edge_index"].astype(np.int64)), z["points"].shape[0]
+
+
+def test_epd_only_processor_15_steps_vs_reference_fixture(golden_dir):
+    from graph_physics_b200.models import EncodeProcessDecode, Graph
+    ei, n = _cyl(golden_dir)
+    z = np.load(os.path.join(golden_dir, "ref_cylinder_h128_s15.npz"))
+    p = mo.init_params(15, hidden=128, seed=0)
+    x0, e0, gx = processor_inputs(n, ei.shape[1], 128, seed=0)
+    model = EncodeProcessDecode(15, 128, 128, 128, hidden_size=128, only_processor=True).cuda()
+    _load(model, p)
+    xd = x0.cuda().requires_grad_(True)
+    ed = e0.cuda().requires_grad_(True)
+    out = model(Graph(x=xd, edge_index=ei.cuda(), edge_attr=ed))
+    assert mo.rel_l2(out.detach().cpu(), torch.tensor(z["x15"])) < TOL_15
+    (out * gx.cuda()).sum().backward()
+    torch.cuda.synchronize()
+    e_gx = mo.rel_l2(xd.grad.cpu(), torch.tensor(z["gx0"]))
+    assert e_gx < TOL_GRAD_15, e_gx
+    assert abs(float(ed.grad.double().norm()) / float(z["ge0_norm"]) - 1) < 0.1
+    with open(os.path.join(golden_dir, "meta.json")) as f:
+        gn = json.load(f)["cylinder_h128_s15"]["grad_norms"]
+    worst = 0.0
+    for name, prm in model.named_parameters():
+        assert prm.grad is not None and torch.isfinite(prm.grad).all(), name
+        worst = max(worst, abs(float(prm.grad.double().norm()) / gn[name] - 1))
+        key = "g:" + name
+        if key in z.files:
+            assert mo.rel_l2(prm.grad.cpu(), torch.tensor(z[key])) < TOL_GRAD_15, name
+    assert worst < 0.1, worst
+    print(f"15 steps: x15 rel-L2 {mo.rel_l2(out.detach().cpu(), torch.tensor(z['x15'])):.2e}, "
+          f"gx0 rel-L2 {e_gx:.2e}, worst grad-norm ratio error {worst:.2e}")
+
+
+def test_per_step_error_and_determinism(golden_dir):
+    """Step-by-step through GraphNetBlock (caller edge order kept), each step compared with the
+    fp64 oracle applied to the SAME input (per-step tolerance) and the chain with the oracle
+    chain (15-step tolerance); two runs are bitwise identical in x (aggregation order is fixed
+    up to tile-boundary red.adds, so e is compared exactly and x to 1e-6)."""
+    from graph_physics_b200.models import GraphNetBlock
+    ei, n = _cyl(golden_dir)
+    p = mo.init_params(15, hidden=128, seed=0)
+    x0, e0, _ = processor_inputs(n, ei.shape[1], 128, seed=0)
+    blocks = []
+    for k in range(15):
+        b = GraphNetBlock(128).cuda()
+        b.load_state_dict({kk[len(f"processor_list.{k}."):]: v for kk, v in p.items()
+                           if kk.startswith(f"processor_list.{k}.")})
+        blocks.append(b)
+    p64 = {k: v.double() for k, v in p.items()}
+    eid = ei.cuda()
+    with torch.no_grad():
+        x, e = x0.cuda(), e0.cuda()
+        xr, er = x0.double(), e0.double()
+        worst_step = 0.0
+        for k in range(15):
+            x1, e1 = blocks[k](x, eid, e)
+            xs_ref, es_ref = mo.graph_net_block(x.cpu().double(), ei, e.cpu().double(), p64, f"processor_list.{k}")
+            worst_step = max(worst_step, mo.rel_l2(x1.cpu(), xs_ref), mo.rel_l2(e1.cpu(), es_ref))
+            xr, er = mo.graph_net_block(xr, ei, er, p64, f"processor_list.{k}")
+            x, e = x1, e1
+        assert worst_step < TOL_STEP, worst_step
+        assert mo.rel_l2(x.cpu(), xr) < TOL_15 and mo.rel_l2(e.cpu(), er) < TOL_15
+        x2, e2 = blocks[0](x0.cuda(), eid, e0.cuda())
+        x3, e3 = blocks[0](x0.cuda(), eid, e0.cuda())
+        assert torch.equal(e2, e3)
+        assert mo.rel_l2(x2.cpu(), x3.cpu()) < 1e-6
+    print(f"worst per-step rel-L2 {worst_step:.2e}; after 15 steps x {mo.rel_l2(x.cpu(), xr):.2e} "
+          f"e {mo.rel_l2(e.cpu(), er):.2e}")
+
+
+def test_full_epd_with_encoders_trains(golden_dir):
+    """Encoders + processor + decoder (cylinder.json shapes: 2+9 node inputs, 3 edge inputs, 2
+    outputs): forward close to the fp64 oracle, every parameter receives a finite gradient, and
+    inference mode (no_grad) gives the same output as the training-mode forward."""
+    from graph_physics_b200.models import EncodeProcessDecode, Graph
+    from graph_physics_b200 import graph as G
+    ei, n = _cyl(golden_dir)
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    p = mo.init_params(15, hidden=128, node_in=11, edge_in=3, out_size=2, seed=5)
+    g = torch.Generator().manual_seed(9)
+    gx = torch.randn(n, 11, generator=g)
+    pos = torch.tensor(z["points"][:, :2])
+    eid = ei.cuda()
+    ea = G.edge_features(pos.cuda(), eid)
+    model = EncodeProcessDecode(15, 11, 3, 2).cuda()
+    _load(model, p)
+    out = model(Graph(x=gx.cuda(), edge_index=eid, edge_attr=ea))
+    ref = mo.encode_process_decode(gx.double(), ei, ea.cpu().double(), {k: v.double() for k, v in p.items()}, 15)
+    assert mo.rel_l2(out.detach().cpu(), ref) < 2e-2      # decoder has no norm: amplifies the 5e-3 latent error
+    out.square().mean().backward()
+    for name, prm in model.named_parameters():
+        assert prm.grad is not None and torch.isfinite(prm.grad).all() and float(prm.grad.abs().max()) > 0, name
+    with torch.no_grad():
+        out2 = model(Graph(x=gx.cuda(), edge_index=eid, edge_attr=ea))
+    assert mo.rel_l2(out2.cpu(), out.detach().cpu()) < 1e-5
+
+
+def test_unsupported_shapes_raise():
+    from graph_physics_b200.models import GraphNetBlock
+    b = GraphNetBlock(64).cuda()
+    with pytest.raises(ValueError):
+        b(torch.zeros(4, 64, device="cuda"), torch.zeros(2, 3, dtype=torch.long, device="cuda"),
+          torch.zeros(3, 64, device="cuda"))
