@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py -- MGN processor edges/s, forward + backward, H=128, 15 message-passing steps
+(BASELINE.json metric) on N GPUs of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): per GPU a block-diagonal batch of 32 copies of
+the reference's own CylinderFlow test mesh (tests/mock_vtu/cylinder_0.vtu: 1,923 nodes, 11,070
+directed edges; committed as tests/golden/cylinder_mesh.npz) -> N=61,536, E=354,240; processor only
+(`EncodeProcessDecode(only_processor=True)`), default nn.Linear init, x0/e0 ~ RMSNorm(N(0,1)),
+upstream gradient N(0,1)/sqrt(N*H).  One step = one forward + backward through the 15 blocks.
+Data-parallel over meshes for N > 1 (weak scaling: 32 meshes per GPU) with an NCCL all-reduce of
+each block's gradient as soon as that block's backward is done.
+
+One JSON line is printed by rank 0 (contract in the task description): `value` = device-resident
+edges/s over all GPUs; `e2e` = same through the public module API with host inputs (pinned H2D of
+x0/e0/upstream gradient every step, D2H of the scalar loss); `roofline` for the dominant kernel
+(edge_bwd) from CUDA events recorded on the launch stream inside the timed region; `cpu_baseline`
+= the CPU oracle (port of the reference's PyTorch path) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H, STEPS_MP = 128, 15
+METRIC = "mgn_processor_edges_per_s_fwd_bwd_h128_15steps"
+BYTES_EDGE_STEP, BYTES_NODE_STEP = 2568, 7168          # SURVEY.md 8(d), fwd+bwd per step
+FLOPS_EDGE_STEP, FLOPS_NODE_STEP = 589824, 491520
+EDGE_BWD_BYTES_EDGE, EDGE_BWD_BYTES_NODE = 1540, 2048  # the dominant kernel's share
+
+
+def load_mesh():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "cylinder_mesh.npz"))
+    return torch.as_tensor(z["edge_index"].astype(np.int64)), int(z["points"].shape[0])
+
+
+def synth_inputs(n, e, seed):
+    """x0, e0 ~ RMSNorm(N(0,1)) (what the encoders emit), upstream gradient N(0,1)/sqrt(N*H)."""
+    g = torch.Generator().manual_seed(1000 + seed)
+
+    def rms(t):
+        return t / (t.norm(dim=-1, keepdim=True) * H ** -0.5 + 1e-8)
+    x0 = rms(torch.randn(n, H, generator=g))
+    e0 = rms(torch.randn(e, H, generator=g))
+    gx = torch.randn(n, H, generator=g) / (n * H) ** 0.5
+    return x0, e0, gx
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        return float(m["hbm_gbs"]), float(m.get("bf16_tflops_sustained", m["bf16_tflops"])), "measured"
+    except Exception:
+        return 6650.0, 1590.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+                for nm, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU oracle leg
+def cpu_oracle_run(copies, reps, warmup, threads):
+    """fwd+bwd through the 15 blocks with the CPU oracle (oracle/mgn_oracle.py: the same ATen ops as
+    the reference's PyTorch path) on `copies` meshes.  Returns (edges/s, seconds per pass, E)."""
+    from oracle import mgn_oracle as mo
+    torch.set_num_threads(threads)
+    ei1, n1 = load_mesh()
+    offs = (torch.arange(copies) * n1).view(1, copies, 1)
+    ei = (ei1.view(2, 1, -1) + offs).reshape(2, -1)
+    n, e = n1 * copies, ei.shape[1]
+    p = mo.init_params(STEPS_MP, hidden=H, seed=0)
+    for v in p.values():
+        v.requires_grad_(True)
+    x0, e0, gx = synth_inputs(n, e, 0)
+    ts = []
+    for it in range(warmup + reps):
+        for v in p.values():
+            v.grad = None
+        xi, ei_ = x0.clone().requires_grad_(True), e0.clone().requires_grad_(True)
+        t0 = time.perf_counter()
+        x, _ = mo.processor(xi, ei, ei_, p, STEPS_MP)
+        x.backward(gx)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            ts.append(dt)
+    t = float(np.median(ts))
+    return e / t, t, e
+
+
+# ------------------------------------------------------------------ reference arm (CPU)
+def run_reference(args):
+    """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be
+    imported here or on the GPU box (torch_geometric absent, no network), so the timed
+    code is the oracle port of its PyTorch ops, with all host threads, on a bounded sample (one
+    mesh of the 32-mesh batch).  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    copies = args.cpu_copies
+    eps, t, e = cpu_oracle_run(copies, args.steps, args.warmup, threads)
+    sample = f"{copies} of 32 meshes per step ({e} edges), oracle port of the reference's PyTorch ops, fp32"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": eps, "unit": "edges/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus, copies_note=sample),
+        "cpu_baseline": {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": eps, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus, copies=32, copies_note=None):
+    cfg = {"workload": f"BASELINE configs[1]: {copies} x CylinderFlow mesh (1923 nodes, 11070 directed edges) per GPU, "
+                       "block-diagonal batch; MGN processor (only_processor=True), H=128, 15 steps, fwd+bwd",
+           "nodes_per_gpu": 1923 * copies, "edges_per_gpu": 11070 * copies, "hidden": H, "mp_steps": STEPS_MP,
+           "parallelism": f"dp{n_gpus}",
+           "numerics": "fp16 tensor-core operands, fp32 accumulation, fp32 residual streams / RMSNorm / aggregation",
+           "l2": "inputs larger than L2: each of the 15 saved edge-latent versions is 181 MB (L2 126 MB)"}
+    if copies_note:
+        cfg["sample"] = copies_note
+    return cfg
+
+
+# ------------------------------------------------------------------ B200 arm
+def run_b200(args):
+    import torch.distributed as dist
+
+    from graph_physics_b200 import _lib as L
+    from graph_physics_b200 import graph as G
+    from graph_physics_b200 import parallel, processor as proc
+    from graph_physics_b200.models import EncodeProcessDecode, Graph
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    L.require_device()
+
+    copies = args.copies
+    ei1, n1 = load_mesh()
+    ei = G.tile_batch(ei1.to(dev), n1, copies)
+    N, E = n1 * copies, ei.shape[1]
+    torch.manual_seed(0)                                   # same weights on every rank
+    model = EncodeProcessDecode(STEPS_MP, H, H, H, hidden_size=H, only_processor=True).to(dev)
+    params = list(model.parameters())
+    x0_h, e0_h, gx_h = synth_inputs(N, E, rank)
+    x0_h, e0_h, gx_h = x0_h.pin_memory(), e0_h.pin_memory(), gx_h.pin_memory()
+    x0, e0, gx = x0_h.to(dev), e0_h.to(dev), gx_h.to(dev)
+    sync = parallel.GradSync(average=True).install() if world > 1 else None
+
+    def step_resident():
+        for p in params:
+            p.grad = None
+        out = model(Graph(x=x0, edge_index=ei, edge_attr=e0))
+        out.backward(gx)
+        if sync is not None:
+            sync.wait()
+
+    xd, ed, gd = torch.empty_like(x0), torch.empty_like(e0), torch.empty_like(gx)
+    loss_h = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        for p in params:
+            p.grad = None
+        xd.copy_(x0_h, non_blocking=True)
+        ed.copy_(e0_h, non_blocking=True)
+        gd.copy_(gx_h, non_blocking=True)
+        out = model(Graph(x=xd, edge_index=ei, edge_attr=ed))
+        loss = (out * gd).sum()
+        loss.backward()
+        if sync is not None:
+            sync.wait()
+        loss_h.copy_(loss.detach(), non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, with_events=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        proc.EVENTS = {"edge_bwd": []} if with_events else None
+        l0 = proc.LAUNCHES
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        barrier()
+        ms = s.elapsed_time(e)
+        launches = proc.LAUNCHES - l0
+        ev = proc.EVENTS
+        proc.EVENTS = None
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches, ev
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms, launches, ev = timed(step_resident, args.steps, args.warmup, with_events=True)
+    clk = clocks.stop() if rank == 0 else None
+    ms_e2e, _, _ = timed(step_e2e, max(2, min(args.steps, 5)), 2)
+    e2e_steps = max(2, min(args.steps, 5))
+
+    if rank == 0:
+        hbm, tf, which = peaks()
+        ms_step = ms / args.steps
+        value = world * E / (ms_step * 1e-3)
+        durs = [a.elapsed_time(b) for a, b in ev["edge_bwd"]]
+        edge_bwd_ms = float(np.mean(durs)) if durs else float("nan")
+        alg_bytes = E * EDGE_BWD_BYTES_EDGE + N * EDGE_BWD_BYTES_NODE
+        ach = alg_bytes / (edge_bwd_ms * 1e-3) / 1e9
+        step_bytes = STEPS_MP * (E * BYTES_EDGE_STEP + N * BYTES_NODE_STEP)
+        step_flops = STEPS_MP * (E * FLOPS_EDGE_STEP + N * FLOPS_NODE_STEP)
+        line = {
+            "metric": METRIC, "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16",
+            "data": "synthetic", "config": workload_config(world, copies),
+            "e2e": {"value": world * E / (ms_e2e / e2e_steps * 1e-3), "unit": "edges/s",
+                    "h2d_bytes_per_step": int(x0_h.numel() + e0_h.numel() + gx_h.numel()) * 4,
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / e2e_steps},
+            "gpu_launches": launches,
+            "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "edge_bwd_kernel", "achieved": ach, "peak": hbm, "unit": "GB/s",
+                         "frac": ach / hbm, "traffic": None, "peak_source": which,
+                         "ms_per_launch": edge_bwd_ms, "launches_timed": len(durs),
+                         "algorithmic_bytes_per_launch": alg_bytes},
+            "step_roofline": {"hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / hbm,
+                              "tensor_frac": step_flops / (ms_step * 1e-3) / 1e12 / tf,
+                              "algorithmic_GB_per_step": step_bytes / 1e9, "algorithmic_TFLOP_per_step": step_flops / 1e12,
+                              "edge_bwd_share_of_step": edge_bwd_ms * STEPS_MP / ms_step},
+        }
+        if args.cpu_seconds > 0:
+            threads = os.cpu_count() or 1
+            eps, t, e_cpu = cpu_oracle_run(args.cpu_copies, 2, 1, threads)
+            line["cpu_baseline"] = {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port",
+                                    "sample": f"{args.cpu_copies} of {copies} meshes ({e_cpu} edges), 15 steps fwd+bwd, "
+                                              f"fp32 oracle port, median of 2 after 1 warm-up, {t:.2f} s per pass"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--copies", type=int, default=32, help="meshes per GPU")
+    ap.add_argument("--cpu-copies", type=int, default=1, help="meshes in the CPU sample")
+    ap.add_argument("--cpu-seconds", type=float, default=1.0, help="0 disables the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,79 @@
+"""Multi-GPU plumbing for the processor path (one process per GPU, torch.distributed).
+
+The reference is single-process / single-GPU (train.py:233-235 `devices=1`); everything here is new.
+
+* Batches of meshes (BASELINE.json configs 2-3) are independent units: `shard_meshes` gives each
+  rank a contiguous share of the batch, the forward/backward needs NO data-path collective, and the
+  replicated weights' gradients are summed with one all-reduce per GraphNetBlock, launched as soon as
+  that block's backward is enqueued (`GradSync`, hooked into processor.GRAD_SYNC) so it overlaps the
+  remaining blocks' backward over NVLink.
+* `allreduce_module_grads` covers parameters outside the fused processor (encoders / decoder).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import processor as _proc
+
+
+def shard_meshes(num_meshes: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """[begin, end) of the meshes rank `rank` owns: contiguous, sizes differ by at most one."""
+    if not (0 <= rank < world_size):
+        raise ValueError("rank out of range")
+    base, rem = divmod(num_meshes, world_size)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+class GradSync:
+    """Sum (or average) each block's flat gradient over the group, asynchronously.
+
+        sync = GradSync(group=None, average=True); sync.install()
+        loss.backward(); sync.wait()        # gradients are reduced when wait() returns
+    """
+
+    def __init__(self, group=None, average: bool = True):
+        self.group = group
+        self.average = average
+        self.handles: List = []
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+
+    def __call__(self, flat: torch.Tensor, k: int):
+        if self.world == 1:
+            return
+        if self.average:
+            flat.mul_(1.0 / self.world)
+        self.handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+
+    def install(self):
+        _proc.GRAD_SYNC = self
+        return self
+
+    def uninstall(self):
+        if _proc.GRAD_SYNC is self:
+            _proc.GRAD_SYNC = None
+
+    def wait(self):
+        for h in self.handles:
+            h.wait()
+        self.handles.clear()
+
+
+def allreduce_module_grads(params, group=None, average: bool = True) -> Optional[torch.Tensor]:
+    """One flat all-reduce over the .grad of `params` (those that have one); returns the flat buffer."""
+    ps = [p for p in params if p.grad is not None]
+    if not ps or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return None
+    flat = torch.cat([p.grad.reshape(-1) for p in ps])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    if average:
+        flat.mul_(1.0 / dist.get_world_size(group))
+    off = 0
+    for p in ps:
+        n = p.grad.numel()
+        p.grad.copy_(flat[off:off + n].view_as(p.grad))
+        off += n
+    return flat

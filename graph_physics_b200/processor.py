@@ -36,6 +36,9 @@ _N_B = (10, 12, 14, 16)
 # ---- instrumentation used by bench.py (kernel launch counter, per-kernel CUDA events)
 LAUNCHES = 0
 EVENTS: Optional[dict] = None      # name -> list of (start, end) torch.cuda.Event pairs when enabled
+# data-parallel hook (graph_physics_b200.parallel): called as GRAD_SYNC(flat_block_grad, k) right after
+# block k's backward has been enqueued, so the all-reduce overlaps the remaining blocks' backward
+GRAD_SYNC = None
 
 
 def _timed(name, fn, *a, **kw):
@@ -174,10 +177,12 @@ class _ProcessorFn(torch.autograd.Function):
             _timed("p_bwd", ops.p_bwd, gP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx
             ge = ge_out
+            grads[k].mul_(inv_s)
+            if GRAD_SYNC is not None:
+                GRAD_SYNC(grads[k], k)
             # release what this step saved
             ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None
             xs[k + 1] = None; es[k + 1] = None
-        grads.mul_(inv_s)
         g_x0 = gx * inv_s if ctx.needs_input_grad[0] else None
         g_e0 = None
         if ctx.needs_input_grad[1]:
