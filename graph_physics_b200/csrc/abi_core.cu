@@ -30,3 +30,12 @@ extern "C" int mgn_check_device(void) {
   }
   return MGN_OK;
 }
+
+// developer timeline buffer (see mlp_common.cuh Timeline); pass null to switch it off
+long long* g_mgn_timeline_host = nullptr;
+int g_mgn_timeline_cap_host = 0;
+extern "C" int mgn_debug_set_timeline(long long* buf, int cap) {
+  g_mgn_timeline_host = buf;
+  g_mgn_timeline_cap_host = cap;
+  return MGN_OK;
+}

@@ -51,3 +51,7 @@ static inline int mgn_num_sms() {
 }
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// developer timeline buffer (abi_core.cu); kernels receive it through their parameter struct
+extern long long* g_mgn_timeline_host;
+extern int g_mgn_timeline_cap_host;

@@ -14,11 +14,11 @@
 // All products run on tcgen05 (fp16 operands, fp32 accumulation in TMEM).  Weight gradients of
 // three layers stay resident in TMEM for the whole kernel (3 x 128 columns) next to one 128-column
 // working accumulator; the fourth (edge layer 1) is formed per tile in the working accumulator and
-// summed in the registers of a second warpgroup.  Weight tiles stream through two 32 KB shared
-// memory slots (bulk async copies from L2), the remaining five slots hold the activation /
-// gradient tiles of the current 128-row tile.  Gradients arrive pre-scaled by a power of two
-// (see processor.py) so that fp16 operands keep their precision; everything here is linear in g.
-#include "mlp_common.cuh"
+// summed in registers (32 per thread).  Weight tiles stream through two 32 KB shared-memory slots
+// (bulk async copies from L2), the remaining five slots hold the activation / gradient tiles of the
+// current 128-row tile.  512 threads per tile (mlp_v2.cuh mapping).  Gradients arrive pre-scaled by
+// a power of two (processor.py) so that fp16 operands keep their precision; all of this is linear in g.
+#include "mlp_v2.cuh"
 #include "mlp_fwd_abi.cuh"
 
 using namespace mgn;
@@ -28,6 +28,47 @@ static constexpr uint32_t SLOT = 32768;
 __device__ __forceinline__ void load_w_slot(uint8_t* slot, const __half* W, int widx, uint64_t* bar) {
   mbar_arrive_expect_tx(bar, SLOT);
   bulk_g2s(slot, reinterpret_cast<const uint8_t*>(W) + (size_t)widx * SLOT, SLOT, bar);
+}
+
+// RMSNorm backward for one thread's 32 columns (layers.py:49-74 differentiated):
+//   y = scale * z * inv, inv = 1 / (||z|| d^-1/2 + eps);  dz = scale*g*inv - z * (sum_c scale*g*z) * inv^2 / (d r)
+// acc = z - bias (TMEM), gtile row holds the upstream gradient g (fp16) and is overwritten with fp16(dz).
+// Returns this warp's column sum (over its 32 rows) of g*z*inv for column c0+lane (= dL/dscale part).
+__device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb)[8], const float4 (&sc)[8],
+                                               uint8_t* gtile, float* red, const Map& m) {
+  float z[32], g[32];
+  tmem_ld32(taddr, z);
+  load_row_chunk_f16(gtile, 128, m.row, m.c0, g);
+  tmem_ld_wait();
+  float ss = 0.f, dot = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float b_[4] = {bb[j].x, bb[j].y, bb[j].z, bb[j].w};
+    const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      z[4 * j + i] += b_[i];
+      ss += z[4 * j + i] * z[4 * j + i];
+      dot += s_[i] * g[4 * j + i] * z[4 * j + i];
+    }
+  }
+  ss = row_sum4(ss, red, m);
+  dot = row_sum4(dot, red, m);
+  const float r = sqrtf(ss) * INV_SQRT_H;
+  const float inv = 1.0f / (r + RMS_EPS);
+  const float k = r > 0.f ? dot * inv * inv / ((float)H * r) : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float zz = z[4 * j + i], gg = g[4 * j + i];
+      z[4 * j + i] = s_[i] * gg * inv - zz * k;     // dL/dz
+      g[4 * j + i] = gg * zz * inv;                 // dL/dscale term
+    }
+  }
+  store_row_chunk_f16(gtile, 128, m.row, m.c0, z);
+  return warp_colsum32(g, m.lane);
 }
 
 // ===================================================================================== edge
@@ -48,349 +89,337 @@ struct EdgeBwdParams {
   const float* b4;
   const float* scale;
   float* grad;              // flat gradient block (GB_* offsets), accumulated with red.add
+  long long* dbg;
+  int dbg_cap;
 };
 
-__global__ void __launch_bounds__(256, 1) edge_bwd_kernel(const EdgeBwdParams p) {
+__global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sWA = smem;
   uint8_t* sWB = smem + SLOT;
   uint8_t* sE = smem + 2 * SLOT;
   uint8_t* sH1 = smem + 3 * SLOT;
-  uint8_t* sH2 = smem + 4 * SLOT;
-  uint8_t* sH3 = smem + 5 * SLOT;
+  uint8_t* sH2 = smem + 4 * SLOT;   // during layer 1: staging of the gathered P_i rows
+  uint8_t* sH3 = smem + 5 * SLOT;   // during layer 1: staging of the gathered P_j rows
   uint8_t* sG = smem + 6 * SLOT;
-  uint8_t* stage = sH3;   // 64 KB fp32 staging = sH3 + sG (both dead by then)
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 7 * SLOT);
+  uint8_t* stage = sH3;             // 64 KB fp32 staging = sH3 + sG (both dead by then)
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 7 * SLOT);
   uint64_t& bar_wA = tail->bar[0];
   uint64_t& bar_wB = tail->bar[1];
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_dwe = tail->bar[3];
-  uint64_t& bar_wfree = tail->bar[4];
   uint32_t& tmem_slot = tail->tmem_slot;
-  const float* sb2 = tail->vec[1];
-  const float* sb3 = tail->vec[2];
-  const float* sb4 = tail->vec[3];
-  const float* ssc = tail->vec[4];
+  const Map m = make_map();
 
-  const int tid = threadIdx.x;
-  const int wg = tid >> 7;
-  const int t = tid & 127;
-  const int w = t >> 5;
-  const int lane = tid & 31;
-
-  copy_vec128(tail->vec[1], p.b2, tid, blockDim.x);
-  copy_vec128(tail->vec[2], p.b3, tid, blockDim.x);
-  copy_vec128(tail->vec[3], p.b4, tid, blockDim.x);
-  copy_vec128(tail->vec[4], p.scale, tid, blockDim.x);
-  if (tid == 0) {
+  if (m.tid == 0) {
     mbar_init(&bar_wA, 1);
     mbar_init(&bar_wB, 1);
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_dwe, 1);
-    mbar_init(&bar_wfree, 128);
     mbar_init_fence();
   }
-  if ((tid >> 5) == 0) tmem_alloc<512>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t lane_off = (uint32_t)(w * 32) << 16;
   const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
+  const uint32_t qoff = m.lane_off + m.c0;
   const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
-
-  if (wg == 1) {
-    // ---------------- register accumulator of dWe = sum over tiles of dz1^T e16
-    float acc[128];
+  const uint32_t uWA = smem_u32(sWA), uWB = smem_u32(sWB), uE = smem_u32(sE), uH1 = smem_u32(sH1),
+                 uH2 = smem_u32(sH2), uH3 = smem_u32(sH3), uG = smem_u32(sG);
+  const uint64_t pol_stream = policy_evict_first();
+  const uint64_t pol_keep = policy_evict_last();
+  uint32_t phase = 0;
+  float dwe[32];                    // this thread's part of dWe = sum over tiles of dz1^T e16
 #pragma unroll
-    for (int j = 0; j < 128; ++j) acc[j] = 0.f;
-    uint32_t it = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      mbar_wait(&bar_dwe, it & 1);
-      fence_after_sync();
-#pragma unroll
-      for (int cq = 0; cq < 4; ++cq) {
-        float v[32];
-        tmem_ld32(tm_W + lane_off + cq * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) acc[cq * 32 + j] += v[j];
-      }
-      fence_before_sync();
-      mbar_arrive(&bar_wfree);
+  for (int j = 0; j < 32; ++j) dwe[j] = 0.f;
+  float dsc = 0.f;
+  float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
+  if (m.tid == 0) {
+    load_w_slot(sWA, p.W, 0, &bar_wA);
+    load_w_slot(sWB, p.W, 1, &bar_wB);
+  }
+  auto mma_wait = [&]() {
+    mbar_wait(&bar_mma, phase);
+    phase ^= 1;
+    fence_after_sync();
+  };
+  auto tile_ready = [&]() {
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+  };
+  // coalesced-mapping indices (lane i < 8 <-> tile row 8*warp + i), requested one tile ahead
+  struct Idx { int dst, rcv, snd; };
+  auto load_idx = [&](long long tile_) -> Idx {
+    Idx ix{-1, -1, -1};
+    const long long g = tile_ * TILE_ROWS + m.warp * 8 + (m.lane & 7);
+    if (tile_ < num_tiles && g < p.E) {
+      ix.dst = p.rowmap ? __ldg(p.rowmap + g) : (int)g;
+      ix.rcv = __ldg(p.receivers + g);
+      ix.snd = __ldg(p.senders + g);
     }
-    float* dst = p.grad + GB_E_W1 + (long long)t * 384;
+    return ix;
+  };
+  Idx nxt = load_idx(blockIdx.x);
+  Timeline tl;
+  tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
+  const int hw = m.lane >> 4, q = m.lane & 15;
+
+  uint32_t it = 0;
+  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    tl.stamp();   // 0
+    const Idx cur = nxt;
+    auto dst_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); };
+    auto rcv_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.rcv, i); };
+
+    // ---- load: e -> sE, g = g_eout + g_aggr[recv] -> sG, gathered P_i / P_j rows -> sH2 / sH3 (all coalesced)
+    load8_f32_to_tile(sE, 128, 0, p.e_in, m, dst_of, pol_stream);
+    if (p.g_eout) load8_sum2_to_tile(sG, p.g_eout, p.g_aggr, m, dst_of, rcv_of, pol_stream, pol_keep);
+    else load8_f32_to_tile(sG, 128, 0, p.g_aggr, m, rcv_of, pol_keep);
+    {
+      uint4 vi[4], vj[4];
 #pragma unroll
-    for (int j = 0; j < 32; ++j)
-      red_add_f4(dst + 4 * j, make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]));
-  } else {
-    // ---------------- compute warpgroup
-    const uint32_t uWA = smem_u32(sWA), uWB = smem_u32(sWB), uE = smem_u32(sE), uH1 = smem_u32(sH1),
-                   uH2 = smem_u32(sH2), uH3 = smem_u32(sH3), uG = smem_u32(sG);
-    uint32_t phase = 0;
-    float dsc[4] = {0.f, 0.f, 0.f, 0.f};
-    float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
-    if (t == 0) {
-      load_w_slot(sWA, p.W, 0, &bar_wA);
-      load_w_slot(sWB, p.W, 1, &bar_wB);
+      for (int i = 0; i < 4; ++i) {
+        const int rc = __shfl_sync(0xffffffffu, cur.rcv, 2 * i + hw);
+        const int sn = __shfl_sync(0xffffffffu, cur.snd, 2 * i + hw);
+        vi[i] = rc >= 0 ? ld_u4_hint(p.P + (long long)rc * 256 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
+        vj[i] = rc >= 0 ? ld_u4_hint(p.P + (long long)sn * 256 + 128 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t off = tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q);
+        *reinterpret_cast<uint4*>(sH2 + off) = vi[i];
+        *reinterpret_cast<uint4*>(sH3 + off) = vj[i];
+      }
     }
-    auto mma_wait = [&]() {
-      mbar_wait(&bar_mma, phase);
-      phase ^= 1;
+    nxt = load_idx(tile + gridDim.x);
+    tile_ready();
+    tl.stamp();   // 1 loads done
+
+    // ---- R1: z1 = e We^T + P_i[recv] + P_j[send]
+    if (m.tid == 0) {
+      if (it == 0) mbar_wait(&bar_wA, 0);
       fence_after_sync();
-    };
-    auto tile_ready = [&]() {
-      fence_async_smem();
-      fence_before_sync();
-      named_bar(1, 128);
-    };
-    const int hw = lane >> 4, q = lane & 15;
-    uint32_t it = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const long long row0 = tile * TILE_ROWS;
-      const long long grow = row0 + t;
-      const bool rvalid = grow < p.E;
-      int rcv = -1, snd = -1, my_dst = -1;
-      if (rvalid) {
-        rcv = __ldg(p.receivers + grow);
-        snd = __ldg(p.senders + grow);
-        my_dst = p.rowmap ? __ldg(p.rowmap + grow) : (int)grow;
-      }
-      // next tile's indices (used only for L2 prefetches, consumed after the first product is issued)
-      const long long ngrow = grow + (long long)gridDim.x * TILE_ROWS;
-      int nrcv = -1, nsnd = -1, ndst = -1;
-      if (ngrow < p.E) {
-        nrcv = __ldg(p.receivers + ngrow);
-        nsnd = __ldg(p.senders + ngrow);
-        ndst = p.rowmap ? __ldg(p.rowmap + ngrow) : (int)ngrow;
-      }
-
-      // ---- load: e -> sE (fp16), g = g_eout + g_aggr[recv] -> sG (fp16)
-      load_rows_f32_to_tile_b<16>(sE, 128, 0, p.e_in, w * 32, 32, lane, [&](int r) -> long long {
-        return (long long)__shfl_sync(0xffffffffu, my_dst, r & 31);
-      });
-      if (p.g_eout) {
-        load_rows_sum2_to_tile<8>(sG, 0, p.g_eout, p.g_aggr, w * 32, 32, lane,
-                                  [&](int r) -> long long { return (long long)__shfl_sync(0xffffffffu, my_dst, r & 31); },
-                                  [&](int r) -> long long { return (long long)__shfl_sync(0xffffffffu, rcv, r & 31); });
-      } else {
-        load_rows_f32_to_tile_b<16>(sG, 128, 0, p.g_aggr, w * 32, 32, lane, [&](int r) -> long long {
-          return (long long)__shfl_sync(0xffffffffu, rcv, r & 31);
-        });
-      }
-      tile_ready();
-
-      // ---- R1: z1 = e We^T + P_i[recv] + P_j[send]
-      if (t == 0) {
-        if (it == 0) mbar_wait(&bar_wA, 0);
-        else mbar_wait(&bar_wfree, (it - 1) & 1);
-        fence_after_sync();
-        umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
-        mma_commit(&bar_mma);
-      }
-      {
-        uint4 pi[16], pj[16];
-        if (rvalid) {
-          const __half* Pi = p.P + (long long)rcv * 256;
-          const __half* Pj = p.P + (long long)snd * 256 + 128;
+      umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
+      mma_commit(&bar_mma);
+    }
+    mma_wait();
+    if (m.tid == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
+    {
+      float v[32], a[32], b[32];
+      tmem_ld32(tm_W + qoff, v);
+      load_row_chunk_f16(sH2, 128, m.row, m.c0, a);
+      load_row_chunk_f16(sH3, 128, m.row, m.c0, b);
+      tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { pi[j] = ldg_u4(Pi + 8 * j); pj[j] = ldg_u4(Pj + 8 * j); }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
-        }
-        // prefetch the next tile's rows into L2
-        if (ndst >= 0) {
-          prefetch_row_f32(p.e_in + (long long)ndst * H);
-          if (p.g_eout) prefetch_row_f32(p.g_eout + (long long)ndst * H);
-          prefetch_row_f32(p.g_aggr + (long long)nrcv * H);
-          prefetch_row_f16(p.P + (long long)nrcv * 256);
-          prefetch_row_f16(p.P + (long long)nsnd * 256 + 128);
-        }
-        mma_wait();
-        if (t == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
-#pragma unroll
-        for (int cq = 0; cq < 4; ++cq) {
-          float v[32];
-          tmem_ld32(tm_W + lane_off + cq * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float a[8], b[8];
-            unpack8(pi[cq * 4 + j], a);
-            unpack8(pj[cq * 4 + j], b);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
-          }
-          store_row_chunk_f16(sH1, 128, t, cq * 32, v);
-        }
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + a[j] + b[j], 0.f);
+      store_row_chunk_f16(sH1, 128, m.row, m.c0, v);
+    }
+    tile_ready();
+    tl.stamp();   // 2 R1 done
+    // L2 prefetch of the next tile's streamed rows (its indices were requested during the load phase)
+    {
+      const int nd = __shfl_sync(0xffffffffu, nxt.dst, m.lane & 7);
+      const int nr = __shfl_sync(0xffffffffu, nxt.rcv, m.lane & 7);
+      const int part = m.lane >> 3;           // 4 lanes per row: one 128-byte line each
+      if (nd >= 0) {
+        prefetch_l2(reinterpret_cast<const char*>(p.e_in + (long long)nd * H) + 128 * part);
+        if (p.g_eout) prefetch_l2(reinterpret_cast<const char*>(p.g_eout + (long long)nd * H) + 128 * part);
+        prefetch_l2(reinterpret_cast<const char*>(p.g_aggr + (long long)nr * H) + 128 * part);
       }
-      tile_ready();
-      // ---- R2
-      if (t == 0) {
+    }
+    // ---- R2
+    {
+      if (m.tid == 0) {
         if (it == 0) mbar_wait(&bar_wB, 0);
         fence_after_sync();
         umma_tile(tm_W, uH1, 128, 0, uWB, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
       }
+      float4 bb[8];
+      load_vec32(p.b2, m.c0, bb);
       mma_wait();
-      if (t == 0) load_w_slot(sWB, p.W, 3, &bar_wB);     // W4 -> B
-      epi_bias_relu(tm_W + lane_off, sb2, sH2, t);
+      if (m.tid == 0) load_w_slot(sWB, p.W, 3, &bar_wB);     // W4 -> B
+      epi_bias_relu_q(tm_W + qoff, bb, sH2, m, nullptr, 0);
       tile_ready();
-      // ---- R3
-      if (t == 0) {
+    }
+    // ---- R3
+    {
+      if (m.tid == 0) {
         mbar_wait(&bar_wA, 1);
         fence_after_sync();
         umma_tile(tm_W, uH2, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
       }
+      float4 bb[8];
+      load_vec32(p.b3, m.c0, bb);
       mma_wait();
-      epi_bias_relu(tm_W + lane_off, sb3, sH3, t);
+      epi_bias_relu_q(tm_W + qoff, bb, sH3, m, nullptr, 0);
       tile_ready();
-      // ---- R4 + RMSNorm backward
-      if (t == 0) {
+    }
+    tl.stamp();   // 3 R2, R3 done
+    // ---- R4 + RMSNorm backward
+    {
+      if (m.tid == 0) {
         mbar_wait(&bar_wB, 1);
         fence_after_sync();
         umma_tile(tm_W, uH3, 128, 0, uWB, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
       }
+      float4 bb[8], sc[8];
+      load_vec32(p.b4, m.c0, bb);
+      load_vec32(p.scale, m.c0, sc);
       mma_wait();
-      epi_rmsnorm_bwd(tm_W + lane_off, sb4, ssc, sG, t, lane, dsc);
+      dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);
       tile_ready();
-      // ---- D4: g_h3 = dz4 W4 ; dW4 += dz4^T h3
-      if (t == 0) {
-        fence_after_sync();
-        umma_tile(tm_W, uG, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
-        umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
-        mma_commit(&bar_mma);
-      }
-      tile_colsum_pair(sG, t, db4a, db4b);
-      mma_wait();
-      if (t == 0) load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
-      epi_relu_mask_inplace(tm_W + lane_off, sH3, t);
-      tile_ready();
-      // ---- D3
-      if (t == 0) {
-        fence_after_sync();
-        umma_tile(tm_W, uH3, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
-        umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
-        mma_commit(&bar_mma);
-      }
-      tile_colsum_pair(sH3, t, db3a, db3b);
-      mma_wait();
-      if (t == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
-      epi_relu_mask_inplace(tm_W + lane_off, sH2, t);
-      tile_ready();
-      // ---- D2
-      if (t == 0) {
-        mbar_wait(&bar_wB, 0);
-        fence_after_sync();
-        umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
-        umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
-        mma_commit(&bar_mma);
-      }
-      tile_colsum_pair(sH2, t, db2a, db2b);
-      mma_wait();
-      epi_relu_mask_inplace(tm_W + lane_off, sH1, t);    // sH1 <- dz1
-      tile_ready();
-      // ---- D1: g_e = g_eout + dz1 We ; scatter dz1 while the product runs
-      if (t == 0) {
-        mbar_wait(&bar_wA, 0);
-        fence_after_sync();
-        umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
-        mma_commit(&bar_mma);
-      }
-      {
-        const int cbase = w * 32 + hw * 16;
-        int cur = -1;
-        float sum[8];
+    }
+    tl.stamp();   // 4 R4 + norm done
+    // ---- D4: g_h3 = dz4 W4 ; dW4 += dz4^T h3
+    if (m.tid == 0) {
+      fence_after_sync();
+      umma_tile(tm_W, uG, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sG, m.tid, db4a, db4b);
+    mma_wait();
+    if (m.tid == 0) load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
+    epi_relu_mask_q(tm_W + qoff, sH3, m);
+    tile_ready();
+    // ---- D3
+    if (m.tid == 0) {
+      fence_after_sync();
+      umma_tile(tm_W, uH3, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sH3, m.tid, db3a, db3b);
+    mma_wait();
+    if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
+    epi_relu_mask_q(tm_W + qoff, sH2, m);
+    tile_ready();
+    // ---- D2
+    if (m.tid == 0) {
+      mbar_wait(&bar_wB, 0);
+      fence_after_sync();
+      umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sH2, m.tid, db2a, db2b);
+    mma_wait();
+    epi_relu_mask_q(tm_W + qoff, sH1, m);    // sH1 <- dz1
+    tile_ready();
+    tl.stamp();   // 5 D4..D2 done
+    // ---- D1: g_e = g_eout + dz1 We ; scatter dz1 while the product runs
+    if (m.tid == 0) {
+      mbar_wait(&bar_wA, 0);
+      fence_after_sync();
+      umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
+      mma_commit(&bar_mma);
+    }
+    float4 old[8];
+    int dst[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sum[i] = 0.f;
-#pragma unroll 4
-        for (int i = 0; i < 16; ++i) {
-          const int r = cbase + i;
-          const int rc = __shfl_sync(0xffffffffu, rcv, hw * 16 + i);
-          const int sn = __shfl_sync(0xffffffffu, snd, hw * 16 + i);
-          const uint4 u = *reinterpret_cast<const uint4*>(sH1 + tile_off(128, r, 8 * q));
-          float f[8];
-          unpack8(u, f);
-          if (rc >= 0) {
-            float* dj = p.gP + (long long)sn * 256 + 128 + 8 * q;
-            red_add_f4(dj, make_float4(f[0], f[1], f[2], f[3]));
-            red_add_f4(dj + 4, make_float4(f[4], f[5], f[6], f[7]));
-            if (rc != cur) {
-              if (cur >= 0) {
-                float* di = p.gP + (long long)cur * 256 + 8 * q;
-                red_add_f4(di, make_float4(sum[0], sum[1], sum[2], sum[3]));
-                red_add_f4(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]));
-              }
-              cur = rc;
+    for (int i = 0; i < 8; ++i) {       // upstream edge-gradient rows for the residual add, in flight early
+      dst[i] = __shfl_sync(0xffffffffu, cur.dst, i);
+      old[i] = (dst[i] >= 0 && p.g_eout) ? ld_f4_hint(p.g_eout + (long long)dst[i] * H + 4 * m.lane, pol_stream)
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    {
+      // half-warp hw handles the 4 consecutive rows 8*warp + 4*hw + i; lane q owns 8 columns
+      int curr = -1;
+      float sum[8];
 #pragma unroll
-              for (int k = 0; k < 8; ++k) sum[k] = f[k];
-            } else {
+      for (int i = 0; i < 8; ++i) sum[i] = 0.f;
 #pragma unroll
-              for (int k = 0; k < 8; ++k) sum[k] += f[k];
+      for (int i = 0; i < 4; ++i) {
+        const int r = m.warp * 8 + 4 * hw + i;
+        const int rc = __shfl_sync(0xffffffffu, cur.rcv, 4 * hw + i);
+        const int sn = __shfl_sync(0xffffffffu, cur.snd, 4 * hw + i);
+        const uint4 u = *reinterpret_cast<const uint4*>(sH1 + tile_off(128, r, 8 * q));
+        float f[8];
+        unpack8(u, f);
+        if (rc >= 0) {
+          float* dj = p.gP + (long long)sn * 256 + 128 + 8 * q;
+          red_add_f4_hint(dj, make_float4(f[0], f[1], f[2], f[3]), pol_keep);
+          red_add_f4_hint(dj + 4, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
+          if (rc != curr) {
+            if (curr >= 0) {
+              float* di = p.gP + (long long)curr * 256 + 8 * q;
+              red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
+              red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
             }
+            curr = rc;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sum[k] = f[k];
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sum[k] += f[k];
           }
         }
-        if (cur >= 0) {
-          float* di = p.gP + (long long)cur * 256 + 8 * q;
-          red_add_f4(di, make_float4(sum[0], sum[1], sum[2], sum[3]));
-          red_add_f4(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]));
-        }
       }
-      mma_wait();
-      acc_to_stage(tm_W + lane_off, stage, t);
-      fence_before_sync();
-      named_bar(1, 128);
-      // dWe tile product into the (now free) working accumulator; summed by warpgroup 1
-      if (t == 0) {
-        fence_after_sync();
-        umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
-        mma_commit(&bar_dwe);
+      if (curr >= 0) {
+        float* di = p.gP + (long long)curr * 256 + 8 * q;
+        red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
+        red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
       }
-      // coalesced output: warp per row
-#pragma unroll 1
-      for (int rb = 0; rb < 32; rb += 8) {
-        float4 old[8];
-        int dst[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          dst[i] = __shfl_sync(0xffffffffu, my_dst, rb + i);
-          old[i] = (dst[i] >= 0 && p.g_eout) ? ld_stream_f4(p.g_eout + (long long)dst[i] * H + 4 * lane)
-                                             : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(w * 32 + rb + i, 4 * lane));
-          if (dst[i] >= 0)
-            st_stream_f4(p.g_e + (long long)dst[i] * H + 4 * lane,
-                         make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w));
-        }
-      }
-      // the dWe product reads sH1 / sE: wait before the next tile overwrites them
-      mbar_wait(&bar_dwe, it & 1);
-      named_bar(1, 128);
     }
-    // ---------------- flush the resident weight gradients, bias and scale gradients
-    fence_after_sync();
-    flush_acc_rows(tm_dW4 + lane_off, p.grad + GB_E_W4, 128, t);
-    flush_acc_rows(tm_dW3 + lane_off, p.grad + GB_E_W3, 128, t);
-    flush_acc_rows(tm_dW2 + lane_off, p.grad + GB_E_W2, 128, t);
-    const int cp = t & 63;
-    atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
-    atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
-    atomicAdd(p.grad + GB_E_B3 + 2 * cp, db3a);
-    atomicAdd(p.grad + GB_E_B3 + 2 * cp + 1, db3b);
-    atomicAdd(p.grad + GB_E_B2 + 2 * cp, db2a);
-    atomicAdd(p.grad + GB_E_B2 + 2 * cp + 1, db2b);
+    mma_wait();
+    acc_to_stage_q(tm_W + qoff, stage, m);
+    fence_before_sync();
+    __syncthreads();
+    // dWe tile product into the (now free) working accumulator
+    if (m.tid == 0) {
+      fence_after_sync();
+      umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
+      mma_commit(&bar_dwe);
+    }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) atomicAdd(p.grad + GB_E_SC + 32 * k + lane, dsc[k]);
+    for (int i = 0; i < 8; ++i) {
+      const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
+      if (dst[i] >= 0)
+        st_f4_hint(p.g_e + (long long)dst[i] * H + 4 * m.lane,
+                   make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_stream);
+    }
+    mbar_wait(&bar_dwe, it & 1);
+    fence_after_sync();
+    {
+      float v[32];
+      tmem_ld32(tm_W + qoff, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) dwe[j] += v[j];
+    }
+    fence_before_sync();
+    __syncthreads();      // working accumulator, sE, sH1 and the staging are free for the next tile
+    tl.stamp();   // 6 D1 + output done
   }
+  // ---------------- flush the resident weight gradients, bias and scale gradients
+  fence_after_sync();
+  flush_acc_q(tm_dW4 + qoff, p.grad + GB_E_W4, 128, m);
+  flush_acc_q(tm_dW3 + qoff, p.grad + GB_E_W3, 128, m);
+  flush_acc_q(tm_dW2 + qoff, p.grad + GB_E_W2, 128, m);
+  {
+    float* dst = p.grad + GB_E_W1 + (long long)m.row * 384 + m.c0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      red_add_f4(dst + 4 * j, make_float4(dwe[4 * j], dwe[4 * j + 1], dwe[4 * j + 2], dwe[4 * j + 3]));
+  }
+  const int cp = m.tid & 63;
+  atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
+  atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
+  atomicAdd(p.grad + GB_E_B3 + 2 * cp, db3a);
+  atomicAdd(p.grad + GB_E_B3 + 2 * cp + 1, db3b);
+  atomicAdd(p.grad + GB_E_B2 + 2 * cp, db2a);
+  atomicAdd(p.grad + GB_E_B2 + 2 * cp + 1, db2b);
+  atomicAdd(p.grad + GB_E_SC + m.c0 + m.lane, dsc);
 
   fence_before_sync();
   __syncthreads();
-  if ((tid >> 5) == 0) tmem_dealloc<512>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
 // ===================================================================================== node
@@ -409,7 +438,7 @@ struct NodeBwdParams {
   float* grad;
 };
 
-__global__ void __launch_bounds__(128, 1) node_bwd_kernel(const NodeBwdParams p) {
+__global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW[2] = {smem, smem + SLOT};
@@ -418,32 +447,29 @@ __global__ void __launch_bounds__(128, 1) node_bwd_kernel(const NodeBwdParams p)
   uint8_t* sH3 = smem + 4 * SLOT;
   uint8_t* sG = smem + 5 * SLOT;
   uint8_t* stage = sH3;   // sH3 + sG
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 6 * SLOT);
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 6 * SLOT);
   uint64_t* bar_w = &tail->bar[0];
   uint64_t& bar_mma = tail->bar[2];
   uint32_t& tmem_slot = tail->tmem_slot;
-  const float* sb4 = tail->vec[3];
-  const float* ssc = tail->vec[4];
-  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
-  copy_vec128(tail->vec[3], p.b4, t, blockDim.x);
-  copy_vec128(tail->vec[4], p.scale, t, blockDim.x);
-  if (t == 0) {
+  const Map m = make_map();
+  if (m.tid == 0) {
     mbar_init(&bar_w[0], 1);
     mbar_init(&bar_w[1], 1);
     mbar_init(&bar_mma, 1);
     mbar_init_fence();
   }
-  if (w == 0) tmem_alloc<512>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t lane_off = (uint32_t)(w * 32) << 16;
   const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
+  const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t uW[2] = {smem_u32(sW[0]), smem_u32(sW[1])};
   const uint32_t uH1 = smem_u32(sH1), uH2 = smem_u32(sH2), uH3 = smem_u32(sH3), uG = smem_u32(sG);
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
   const uint32_t my_tiles = (uint32_t)((num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
   const uint32_t total_loads = 5 * my_tiles;
+  const uint64_t pol_keep = policy_evict_last();
   // weight stream: load q carries tile-local weight (q % 5): 0 W4', 1 W3', 2 W2', 3 W1'[:, :128], 4 W1'[:, 128:]
   // packed order is W1'a, W1'b, W2', W3', W4' (slots 0..4)
   auto issue_load = [&](uint32_t qq) {
@@ -465,83 +491,94 @@ __global__ void __launch_bounds__(128, 1) node_bwd_kernel(const NodeBwdParams p)
     fence_before_sync();
     __syncthreads();
   };
-  if (t == 0) {
+  if (m.tid == 0) {
     issue_load(0);
     issue_load(1);
   }
-  float dsc[4] = {0.f, 0.f, 0.f, 0.f};
+  float dsc = 0.f;
   float db1a = 0.f, db1b = 0.f, db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
   uint32_t it = 0;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
     const uint32_t q0 = 5 * it;
-    auto rf = [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; };
-    load_rows_f16_to_tile(sH1, 128, 0, p.h1, w * 32, lane, rf);
-    load_rows_f16_to_tile(sH2, 128, 0, p.h2, w * 32, lane, rf);
-    load_rows_f16_to_tile(sH3, 128, 0, p.h3, w * 32, lane, rf);
-    load_rows_f32_to_tile_b<16>(sG, 128, 0, p.g_xout, w * 32, 32, lane, rf);
+    auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
+    load8_f16_to_tile(sH1, p.h1, m, rf);
+    load8_f16_to_tile(sH2, p.h2, m, rf);
+    load8_f16_to_tile(sH3, p.h3, m, rf);
+    load8_f32_to_tile(sG, 128, 0, p.g_xout, m, rf, pol_keep);
     tile_ready();
     // ---- R4: z4 = h3 W4'^T, RMSNorm backward
-    if (t == 0) {
-      wait_load(q0);
-      fence_after_sync();
-      umma_tile(tm_W, uH3, 128, 0, uW[q0 & 1], 128, 0, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
+    {
+      if (m.tid == 0) {
+        wait_load(q0);
+        fence_after_sync();
+        umma_tile(tm_W, uH3, 128, 0, uW[q0 & 1], 128, 0, 0, 128, 8, 0);
+        mma_commit(&bar_mma);
+      }
+      float4 bb[8], sc[8];
+      load_vec32(p.b4, m.c0, bb);
+      load_vec32(p.scale, m.c0, sc);
+      mma_wait();
+      dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);
+      tile_ready();
     }
-    mma_wait();
-    epi_rmsnorm_bwd(tm_W + lane_off, sb4, ssc, sG, t, lane, dsc);
-    tile_ready();
     // ---- D4
-    if (t == 0) {
+    if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uG, 128, 0, uW[q0 & 1], 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
-    tile_colsum_pair(sG, t, db4a, db4b);
+    tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
-    if (t == 0) issue_load(q0 + 2);
-    epi_relu_mask_inplace(tm_W + lane_off, sH3, t);
+    if (m.tid == 0) issue_load(q0 + 2);
+    epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
     // ---- D3
-    if (t == 0) {
+    if (m.tid == 0) {
       wait_load(q0 + 1);
       fence_after_sync();
       umma_tile(tm_W, uH3, 128, 0, uW[(q0 + 1) & 1], 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
-    tile_colsum_pair(sH3, t, db3a, db3b);
+    tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
-    if (t == 0) issue_load(q0 + 3);
-    epi_relu_mask_inplace(tm_W + lane_off, sH2, t);
+    if (m.tid == 0) issue_load(q0 + 3);
+    epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
     // ---- D2
-    if (t == 0) {
+    if (m.tid == 0) {
       wait_load(q0 + 2);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uW[(q0 + 2) & 1], 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
-    tile_colsum_pair(sH2, t, db2a, db2b);
+    tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
-    if (t == 0) issue_load(q0 + 4);
-    epi_relu_mask_inplace(tm_W + lane_off, sH1, t);     // sH1 <- dz1'
+    if (m.tid == 0) issue_load(q0 + 4);
+    epi_relu_mask_q(tm_W + qoff, sH1, m);     // sH1 <- dz1'
     tile_ready();
     // ---- D1a: g_x = g_xout + dz1' W1'[:, :128]
-    if (t == 0) {
+    if (m.tid == 0) {
       wait_load(q0 + 3);
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 0, uW[(q0 + 3) & 1], 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_mma);
     }
-    tile_colsum_pair(sH1, t, db1a, db1b);
+    tile_colsum_q(sH1, m.tid, db1a, db1b);
+    float4 old[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const long long g = rf(i);
+      old[i] = g >= 0 ? ld_f4_hint(p.g_xout + g * H + 4 * m.lane, pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     {  // dz1' tile -> global fp16 (half-warp per row)
-      const int hw = lane >> 4, q = lane & 15;
-#pragma unroll 4
-      for (int i = 0; i < 16; ++i) {
-        const int r = w * 32 + 2 * i + hw;
+      const int hw = m.lane >> 4, q = m.lane & 15;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = m.warp * 8 + 2 * i + hw;
         const long long g = row0 + r;
         if (g < p.N)
           *reinterpret_cast<uint4*>(p.dz1 + g * H + 8 * q) =
@@ -549,56 +586,44 @@ __global__ void __launch_bounds__(128, 1) node_bwd_kernel(const NodeBwdParams p)
       }
     }
     mma_wait();
-    if (t == 0) issue_load(q0 + 5);
-    acc_to_stage(tm_W + lane_off, stage, t);
+    if (m.tid == 0) issue_load(q0 + 5);
+    acc_to_stage_q(tm_W + qoff, stage, m);
     fence_before_sync();
     __syncthreads();
     // ---- D1b issued now (working accumulator free); g_x written meanwhile
-    if (t == 0) {
+    if (m.tid == 0) {
       wait_load(q0 + 4);
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 0, uW[(q0 + 4) & 1], 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_mma);
     }
-#pragma unroll 1
-    for (int rb = 0; rb < 32; rb += 8) {
-      float4 old[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long g = row0 + w * 32 + rb + i;
-        old[i] = g < p.N ? ld_stream_f4(p.g_xout + g * H + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long g = row0 + w * 32 + rb + i;
-        const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(w * 32 + rb + i, 4 * lane));
-        if (g < p.N)
-          st_stream_f4(p.g_x + g * H + 4 * lane,
-                       make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w));
-      }
+    for (int i = 0; i < 8; ++i) {
+      const long long g = rf(i);
+      const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
+      if (g >= 0)
+        st_f4_hint(p.g_x + g * H + 4 * m.lane,
+                   make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_keep);
     }
     mma_wait();
-    if (t == 0) issue_load(q0 + 6);
+    if (m.tid == 0) issue_load(q0 + 6);
     __syncthreads();    // all reads of the g_x staging are done
-    acc_to_stage(tm_W + lane_off, stage, t);
+    acc_to_stage_q(tm_W + qoff, stage, m);
     fence_before_sync();
     __syncthreads();
-#pragma unroll 1
-    for (int rb = 0; rb < 32; rb += 8) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long g = row0 + w * 32 + rb + i;
-        const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(w * 32 + rb + i, 4 * lane));
-        if (g < p.N) st_stream_f4(p.g_aggr + g * H + 4 * lane, v);
-      }
+    for (int i = 0; i < 8; ++i) {
+      const long long g = rf(i);
+      const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
+      if (g >= 0) st_f4_hint(p.g_aggr + g * H + 4 * m.lane, v, pol_keep);
     }
     __syncthreads();
   }
   fence_after_sync();
-  flush_acc_rows(tm_dW4 + lane_off, p.grad + GB_N_W4, 128, t);
-  flush_acc_rows(tm_dW3 + lane_off, p.grad + GB_N_W3, 128, t);
-  flush_acc_rows(tm_dW2 + lane_off, p.grad + GB_N_W2, 128, t);
-  const int cp = t & 63;
+  flush_acc_q(tm_dW4 + qoff, p.grad + GB_N_W4, 128, m);
+  flush_acc_q(tm_dW3 + qoff, p.grad + GB_N_W3, 128, m);
+  flush_acc_q(tm_dW2 + qoff, p.grad + GB_N_W2, 128, m);
+  const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_N_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_N_B4 + 2 * cp + 1, db4b);
   atomicAdd(p.grad + GB_N_B3 + 2 * cp, db3a);
@@ -607,11 +632,10 @@ __global__ void __launch_bounds__(128, 1) node_bwd_kernel(const NodeBwdParams p)
   atomicAdd(p.grad + GB_N_B2 + 2 * cp + 1, db2b);
   atomicAdd(p.grad + GB_N_B1 + 2 * cp, db1a);
   atomicAdd(p.grad + GB_N_B1 + 2 * cp + 1, db1b);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) atomicAdd(p.grad + GB_N_SC + 32 * k + lane, dsc[k]);
+  atomicAdd(p.grad + GB_N_SC + m.c0 + m.lane, dsc);
   fence_before_sync();
   __syncthreads();
-  if (w == 0) tmem_dealloc<512>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
 // ===================================================================================== P backward
@@ -625,106 +649,102 @@ struct PBwdParams {
   float* grad;
 };
 
-__global__ void __launch_bounds__(128, 1) p_bwd_kernel(const PBwdParams p) {
+__global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW = smem;                 // 64 KB
   uint8_t* sGP = smem + 2 * SLOT;     // 128 x 256 fp16 = 64 KB ; later the fp32 staging of g_x
   uint8_t* sX = smem + 4 * SLOT;      // 32 KB
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 5 * SLOT);
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 5 * SLOT);
   uint64_t& wbar = tail->bar[0];
   uint64_t& bar_mma = tail->bar[1];
   uint32_t& tmem_slot = tail->tmem_slot;
-  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
-  if (t == 0) {
+  const Map m = make_map();
+  if (m.tid == 0) {
     mbar_init(&wbar, 1);
     mbar_init(&bar_mma, 1);
     mbar_init_fence();
   }
-  if (w == 0) tmem_alloc<512>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t lane_off = (uint32_t)(w * 32) << 16;
+  const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t tm_W = tmem_slot, tm_dWi = tmem_slot + 128, tm_dWj = tmem_slot + 256;
-  if (t == 0) {
+  if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, 2 * SLOT);
     bulk_g2s(sW, p.Wcat, SLOT, &wbar);
     bulk_g2s(sW + SLOT, reinterpret_cast<const uint8_t*>(p.Wcat) + SLOT, SLOT, &wbar);
   }
-  mbar_wait(&wbar, 0);
   const uint32_t uW = smem_u32(sW), uGP = smem_u32(sGP), uX = smem_u32(sX);
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
+  const uint64_t pol_once = policy_evict_first(), pol_keep = policy_evict_last();
   uint32_t phase = 0, it = 0;
   float db1a = 0.f, db1b = 0.f;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
-    auto rf = [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; };
-    // gP rows are 256 floats: two 128-column halves of a row live 128 floats apart
-    load_rows_f32_to_tile_b<16>(sGP, 128, 0, p.gP, w * 32, 32, lane,
-                                [&](int r) -> long long { long long g = row0 + r; return g < p.N ? 2 * g : -1; });
-    load_rows_f32_to_tile_b<16>(sGP, 128, 128, p.gP, w * 32, 32, lane,
-                                [&](int r) -> long long { long long g = row0 + r; return g < p.N ? 2 * g + 1 : -1; });
-    load_rows_f32_to_tile_b<16>(sX, 128, 0, p.x, w * 32, 32, lane, rf);
+    auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
+    // gP rows are 256 floats: the two 128-column halves of a row are rows 2g, 2g+1 of a [2N,128] view
+    load8_f32_to_tile(sGP, 128, 0, p.gP, m, [&](int i) -> long long { const long long g = rf(i); return g < 0 ? -1 : 2 * g; },
+                      pol_once);
+    load8_f32_to_tile(sGP, 128, 128, p.gP, m,
+                      [&](int i) -> long long { const long long g = rf(i); return g < 0 ? -1 : 2 * g + 1; }, pol_once);
+    load8_f32_to_tile(sX, 128, 0, p.x, m, rf, pol_keep);
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
-    if (t == 0) {
+    if (m.tid == 0) {
+      if (it == 0) mbar_wait(&wbar, 0);
       fence_after_sync();
       // g_x part: [128 x 256] x [256 x 128]; B = MN-major view of the 256-row weight tile
       umma_tile(tm_W, uGP, 128, 0, uW, 256, 1, 0, 128, 16, 0);
       // dW_i, dW_j: A = MN-major views of the two column halves of the gP tile
-      {
-        const uint32_t idesc = make_idesc(128, 128, 1, 1);
-        for (uint32_t ks = 0; ks < 8; ++ks) {
-          mma_f16(tm_dWi, desc_mnmajor(uGP, 128, ks, 0), desc_mnmajor(uX, 128, ks, 0), idesc, (ks > 0 || it > 0) ? 1u : 0u);
-        }
-        for (uint32_t ks = 0; ks < 8; ++ks) {
-          mma_f16(tm_dWj, desc_mnmajor(uGP, 128, ks, 128), desc_mnmajor(uX, 128, ks, 0), idesc, (ks > 0 || it > 0) ? 1u : 0u);
-        }
-      }
+      const uint32_t idesc = make_idesc(128, 128, 1, 1);
+      for (uint32_t ks = 0; ks < 8; ++ks)
+        mma_f16(tm_dWi, desc_mnmajor(uGP, 128, ks, 0), desc_mnmajor(uX, 128, ks, 0), idesc, (ks > 0 || it > 0) ? 1u : 0u);
+      for (uint32_t ks = 0; ks < 8; ++ks)
+        mma_f16(tm_dWj, desc_mnmajor(uGP, 128, ks, 128), desc_mnmajor(uX, 128, ks, 0), idesc,
+                (ks > 0 || it > 0) ? 1u : 0u);
       mma_commit(&bar_mma);
     }
-    tile_colsum_pair(sGP, t, db1a, db1b);       // columns 0..127 = dP_i
+    tile_colsum_q(sGP, m.tid, db1a, db1b);       // columns 0..127 = dP_i
+    float4 old[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const long long g = rf(i);
+      old[i] = g >= 0 ? ld_f4_hint(p.g_x + g * H + 4 * m.lane, pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     mbar_wait(&bar_mma, phase);
     phase ^= 1;
     fence_after_sync();
-    acc_to_stage(tm_W + lane_off, sGP, t);
+    __syncthreads();      // every thread's column sums over the fp16 gP tile are done: it becomes the staging
+    acc_to_stage_q(tm_W + qoff, sGP, m);
     fence_before_sync();
     __syncthreads();
-#pragma unroll 1
-    for (int rb = 0; rb < 32; rb += 8) {
-      float4 old[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long g = row0 + w * 32 + rb + i;
-        old[i] = g < p.N ? ld_f4(p.g_x + g * H + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long g = row0 + w * 32 + rb + i;
-        const float4 v = *reinterpret_cast<const float4*>(sGP + stage_off(w * 32 + rb + i, 4 * lane));
-        if (g < p.N)
-          *reinterpret_cast<float4*>(p.g_x + g * H + 4 * lane) =
-              make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w);
-      }
+    for (int i = 0; i < 8; ++i) {
+      const long long g = rf(i);
+      const float4 v = *reinterpret_cast<const float4*>(sGP + stage_off(m.warp * 8 + i, 4 * m.lane));
+      if (g >= 0)
+        st_f4_hint(p.g_x + g * H + 4 * m.lane,
+                   make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_keep);
     }
     __syncthreads();
   }
   fence_after_sync();
   // dW_i -> edge_block.0.weight[:, 128:256], dW_j -> [:, 256:384]
-  flush_acc_rows(tm_dWi + lane_off, p.grad + GB_E_W1 + 128, 384, t);
-  flush_acc_rows(tm_dWj + lane_off, p.grad + GB_E_W1 + 256, 384, t);
-  const int cp = t & 63;
+  flush_acc_q(tm_dWi + qoff, p.grad + GB_E_W1 + 128, 384, m);
+  flush_acc_q(tm_dWj + qoff, p.grad + GB_E_W1 + 256, 384, m);
+  const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B1 + 2 * cp, db1a);
   atomicAdd(p.grad + GB_E_B1 + 2 * cp + 1, db1b);
   fence_before_sync();
   __syncthreads();
-  if (w == 0) tmem_dealloc<512>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
 // ===================================================================================== node layer-1 wgrad
-// dW1' [128, 256] += dz1'^T [x | aggr]
+// dW1' [128, 256] += dz1'^T [x | aggr].  Two 96 KB operand sets: the loads of tile i+1 run under the MMAs of tile i.
 struct NodeWgrad1Params {
   long long N;
   const __half* dz1;        // [N,128] fp16
@@ -733,64 +753,68 @@ struct NodeWgrad1Params {
   float* grad;
 };
 
-__global__ void __launch_bounds__(128, 1) node_wgrad1_kernel(const NodeWgrad1Params p) {
+__global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Params p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
-  uint8_t* sG = smem;                 // 32 KB
-  uint8_t* sU = smem + SLOT;          // 128 x 256 fp16 = 64 KB
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 3 * SLOT);
-  uint64_t& bar_mma = tail->bar[0];
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 6 * SLOT);
+  uint64_t* bar_set = &tail->bar[0];    // [2]: MMAs reading operand set b have completed
   uint32_t& tmem_slot = tail->tmem_slot;
-  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
-  if (t == 0) {
-    mbar_init(&bar_mma, 1);
+  const Map m = make_map();
+  if (m.tid == 0) {
+    mbar_init(&bar_set[0], 1);
+    mbar_init(&bar_set[1], 1);
     mbar_init_fence();
   }
-  if (w == 0) tmem_alloc<256>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<256>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t lane_off = (uint32_t)(w * 32) << 16;
+  const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t tm = tmem_slot;
-  const uint32_t uG = smem_u32(sG), uU = smem_u32(sU);
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
-  uint32_t phase = 0, it = 0;
+  const uint64_t pol_keep = policy_evict_last();
+  uint32_t it = 0;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
-    auto rf = [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; };
-    load_rows_f16_to_tile(sG, 128, 0, p.dz1, w * 32, lane, rf);
-    load_rows_f32_to_tile_b<16>(sU, 128, 0, p.x, w * 32, 32, lane, rf);
-    load_rows_f32_to_tile_b<16>(sU, 128, 128, p.aggr, w * 32, 32, lane, rf);
+    const uint32_t b = it & 1;
+    uint8_t* sG = smem + b * 3 * SLOT;          // 32 KB
+    uint8_t* sU = sG + SLOT;                    // 128 x 256 fp16 = 64 KB
+    auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
+    if (it >= 2) mbar_wait(&bar_set[b], ((it >> 1) - 1) & 1);
+    load8_f16_to_tile(sG, p.dz1, m, rf);
+    load8_f32_to_tile(sU, 128, 0, p.x, m, rf, pol_keep);
+    load8_f32_to_tile(sU, 128, 128, p.aggr, m, rf, pol_keep);
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
-    if (t == 0) {
+    if (m.tid == 0) {
       fence_after_sync();
+      const uint32_t uG = smem_u32(sG), uU = smem_u32(sU);
       const uint32_t idesc = make_idesc(128, 128, 1, 1);
       for (uint32_t ks = 0; ks < 8; ++ks)
         mma_f16(tm, desc_mnmajor(uG, 128, ks, 0), desc_mnmajor(uU, 128, ks, 0), idesc, (ks > 0 || it > 0) ? 1u : 0u);
       for (uint32_t ks = 0; ks < 8; ++ks)
         mma_f16(tm + 128, desc_mnmajor(uG, 128, ks, 0), desc_mnmajor(uU, 128, ks, 128), idesc,
                 (ks > 0 || it > 0) ? 1u : 0u);
-      mma_commit(&bar_mma);
+      mma_commit(&bar_set[b]);
     }
-    mbar_wait(&bar_mma, phase);
-    phase ^= 1;
-    fence_after_sync();
-    __syncthreads();
   }
-  flush_acc_rows(tm + lane_off, p.grad + GB_N_W1, 256, t);
-  flush_acc_rows(tm + 128 + lane_off, p.grad + GB_N_W1 + 128, 256, t);
+  // wait for the last commit of each set (commits complete in order; waiting both is simplest)
+  if (it >= 1) mbar_wait(&bar_set[(it - 1) & 1], ((it - 1) >> 1) & 1);
+  if (it >= 2) mbar_wait(&bar_set[it & 1], ((it - 2) >> 1) & 1);
+  fence_after_sync();
+  flush_acc_q(tm + qoff, p.grad + GB_N_W1, 256, m);
+  flush_acc_q(tm + 128 + qoff, p.grad + GB_N_W1 + 128, 256, m);
   fence_before_sync();
   __syncthreads();
-  if (w == 0) tmem_dealloc<256>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
 }
 
 // ===================================================================================== C ABI
 static constexpr int EDGE_BWD_SMEM = 7 * SLOT + TAIL_BYTES;
 static constexpr int NODE_BWD_SMEM = 6 * SLOT + TAIL_BYTES;
 static constexpr int P_BWD_SMEM = 5 * SLOT + TAIL_BYTES;
-static constexpr int NODE_WGRAD1_SMEM = 3 * SLOT + TAIL_BYTES;
+static constexpr int NODE_WGRAD1_SMEM = 6 * SLOT + TAIL_BYTES;
 
 extern "C" int64_t mgn_grad_block_floats(void) { return GB_FLOATS; }
 
@@ -811,13 +835,14 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32
   p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.gP = gP;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale; p.grad = grad_block;
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(edge_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
-  edge_bwd_kernel<<<grid, 256, EDGE_BWD_SMEM, stream>>>(p);
+  edge_bwd_kernel<<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -840,7 +865,7 @@ extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, cons
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  node_bwd_kernel<<<grid, 128, NODE_BWD_SMEM, stream>>>(p);
+  node_bwd_kernel<<<grid, NT, NODE_BWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -858,7 +883,7 @@ extern "C" int mgn_p_bwd(int64_t N, const float* gP, const float* x, float* g_x,
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  p_bwd_kernel<<<grid, 128, P_BWD_SMEM, stream>>>(p);
+  p_bwd_kernel<<<grid, NT, P_BWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -875,7 +900,7 @@ extern "C" int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  node_wgrad1_kernel<<<grid, 128, NODE_WGRAD1_SMEM, stream>>>(p);
+  node_wgrad1_kernel<<<grid, NT, NODE_WGRAD1_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

@@ -147,6 +147,60 @@ __device__ __forceinline__ void copy_vec128(float* dst, const float* __restrict_
     for (int i = tid; i < 128; i += nthreads) dst[i] = __ldg(src + i);
 }
 
+// ------------------------------------------------------------------ L2 eviction policies
+// Streams that are read or written once (edge latents, gradients) are tagged evict_first so that
+// they do not push the per-node arrays that every edge gathers (P, aggr, g_aggr, gP) out of L2.
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ float4 ld_f4_hint(const float* p, uint64_t pol) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_u4_hint(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ void st_f4_hint(float* p, float4 v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_u4_hint(void* p, uint4 v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void red_add_f4_hint(float* p, float4 v, uint64_t pol) {
+  asm volatile("red.global.add.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w), "l"(pol) : "memory");
+}
+
+// ------------------------------------------------------------------ developer timeline (tools/timeline.py)
+// When a buffer is registered (mgn_debug_set_timeline; host globals below), thread 0 of block 0 records clock64()
+// at the phase boundaries of its tiles.  Null (the default) costs one predicated load per stamp.
+struct Timeline {
+  long long* buf;
+  int n, cap;
+  __device__ __forceinline__ void init(bool on, long long* b, int c) {
+    buf = on ? b : nullptr;
+    cap = on ? c : 0;
+    n = 0;
+  }
+  __device__ __forceinline__ void stamp() {
+    if (buf != nullptr && n < cap) buf[n++] = clock64();
+  }
+};
+
 // ------------------------------------------------------------------ prefetch / misc
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // one 512-byte fp32 row = 4 lines

@@ -11,7 +11,7 @@
 // as fp16 rows in the layer-1 epilogue, so the per-edge tensor work is e W_e^T only.
 // All products run on tcgen05 (fp16 operands, fp32 accumulation in TMEM); residual
 // streams, RMSNorm and the segmented sum are fp32.
-#include "mlp_common.cuh"
+#include "mlp_v2.cuh"
 
 using namespace mgn;
 
@@ -34,16 +34,12 @@ struct FwdParams {
   __half* save_h1;            // optional fp16 saves of the hidden activations (row = tile row index)
   __half* save_h2;
   __half* save_h3;
+  long long* dbg;             // developer timeline (null = off)
+  int dbg_cap;
 };
 
-__device__ __forceinline__ uint32_t stage_off_half(uint32_t row, uint32_t col) {  // 64 fp32 columns per row
-  uint32_t chunk = col >> 2;
-  return row * 256 + (((chunk & 8u) | ((chunk ^ row) & 7u)) << 4) + ((col & 3) << 2);
-}
-
 template <bool EDGE>
-__global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdParams p) {
-  constexpr int NWG = EDGE ? 2 : 1;
+__global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   constexpr uint32_t W_BYTES = EDGE ? 4 * TILE_BYTES : 5 * TILE_BYTES;
   constexpr uint32_t A_BYTES = EDGE ? TILE_BYTES : 2 * TILE_BYTES;
   constexpr uint32_t K0_STEPS = EDGE ? 8 : 16;
@@ -52,262 +48,250 @@ __global__ void __launch_bounds__(EDGE ? 256 : 128, 1) mlp_fwd_kernel(const FwdP
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW = smem;
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + W_BYTES + NWG * A_BYTES);
+  uint8_t* sA = smem + W_BYTES;
+  // fp32 staging of the block output: its own 64 KB for the edge kernel, the (dead) operand tile for the node kernel
+  uint8_t* stage = EDGE ? smem + W_BYTES + A_BYTES : sA;
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + W_BYTES + A_BYTES + (EDGE ? 2 * TILE_BYTES : 0));
   uint64_t& wbar = tail->bar[0];
-  uint64_t* mbar = &tail->bar[1];
+  uint64_t& mbar = tail->bar[1];
   uint32_t& tmem_slot = tail->tmem_slot;
-  const float* sb1 = tail->vec[0];
-  const float* sb2 = tail->vec[1];
-  const float* sb3 = tail->vec[2];
-  const float* sb4 = tail->vec[3];
-  const float* ssc = tail->vec[4];
+  const Map m = make_map();
 
-  const int tid = threadIdx.x;
-  const int wg = tid >> 7;
-  const int t = tid & 127;          // row owned in the epilogues
-  const int w = t >> 5;             // warp within the workgroup
-  const int lane = tid & 31;
-  uint8_t* sA = smem + W_BYTES + wg * A_BYTES;
-
-  copy_vec128(tail->vec[0], p.b1, tid, blockDim.x);
-  copy_vec128(tail->vec[1], p.b2, tid, blockDim.x);
-  copy_vec128(tail->vec[2], p.b3, tid, blockDim.x);
-  copy_vec128(tail->vec[3], p.b4, tid, blockDim.x);
-  copy_vec128(tail->vec[4], p.scale, tid, blockDim.x);
-  if (tid == 0) {
+  if (m.tid == 0) {
     mbar_init(&wbar, 1);
-    for (int i = 0; i < NWG; ++i) mbar_init(&mbar[i], 1);
+    mbar_init(&mbar, 1);
     mbar_init_fence();
   }
-  if ((tid >> 5) == 0) tmem_alloc<256>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<128>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_acc = tmem_slot + wg * 128;
-  const uint32_t tmem_row = tmem_acc + ((uint32_t)(w * 32) << 16);
+  const uint32_t tmem_acc = tmem_slot;
+  const uint32_t taddr = tmem_acc + m.lane_off + m.c0;
 
-  if (tid == 0) {
+  if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, W_BYTES);
     for (uint32_t o = 0; o < W_BYTES; o += TILE_BYTES)
       bulk_g2s(sW + o, reinterpret_cast<const uint8_t*>(p.W) + o, TILE_BYTES, &wbar);
   }
 
   const long long num_tiles = (p.M + TILE_ROWS - 1) / TILE_ROWS;
-  const long long tile_stride = (long long)gridDim.x * NWG;
   uint32_t phase = 0;
   const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
   bool w_ready = false;
-
-  for (long long tile = (long long)blockIdx.x * NWG + wg; tile < num_tiles; tile += tile_stride) {
-    const long long row0 = tile * TILE_ROWS;
-    const long long grow = row0 + t;            // my row (epilogue mapping); also row w*32+lane of the warp
-    const bool rvalid = grow < p.M;
-    int rcv = -1, snd = -1, my_dst = -1;
-    if (rvalid) {
-      my_dst = (EDGE && p.rowmap) ? __ldg(p.rowmap + grow) : (int)grow;
-      if (EDGE) {
-        rcv = __ldg(p.receivers + grow);
-        snd = __ldg(p.senders + grow);
-      }
-    }
-    // next tile of this workgroup: indices for the L2 prefetches issued below
-    const long long ngrow = grow + tile_stride * TILE_ROWS;
-    int nrcv = -1, nsnd = -1, ndst = -1;
-    if (ngrow < p.M) {
-      ndst = (EDGE && p.rowmap) ? __ldg(p.rowmap + ngrow) : (int)ngrow;
-      if (EDGE) {
-        nrcv = __ldg(p.receivers + ngrow);
-        nsnd = __ldg(p.senders + ngrow);
-      }
-    }
-
-    // ---- load phase: fp32 rows -> fp16 operand tile (16 rows in flight per warp)
-    {
-      auto rf = [&](int r) -> long long { return (long long)__shfl_sync(0xffffffffu, my_dst, r & 31); };
-      load_rows_f32_to_tile_b<16>(sA, 128, 0, p.in0, w * 32, 32, lane, rf);
-      if (!EDGE) load_rows_f32_to_tile_b<16>(sA, 128, 128, p.in1, w * 32, 32, lane, rf);
-    }
+  auto mma_wait = [&]() {
+    mbar_wait(&mbar, phase);
+    phase ^= 1;
+    fence_after_sync();
+  };
+  auto tile_ready = [&]() {
     fence_async_smem();
     fence_before_sync();
-    named_bar(1 + wg, 128);
+    __syncthreads();
+  };
+
+  const uint64_t pol_stream = policy_evict_first();   // edge / node latent streams: touched once or twice
+  const uint64_t pol_keep = policy_evict_last();      // per-node arrays gathered by every edge
+  // Index registers run one tile ahead (the loads for tile i+1 are issued during tile i), so no
+  // thread waits on an index before it can issue its tile's row loads.
+  struct Idx { int rcv_o, snd_o, dst_c, rcv_c; };
+  auto load_idx = [&](long long tile_) -> Idx {
+    Idx ix{0, 0, -1, -1};
+    if (tile_ >= num_tiles) return ix;
+    const long long r0 = tile_ * TILE_ROWS;
+    if (EDGE && r0 + m.row < p.M) {
+      ix.rcv_o = __ldg(p.receivers + r0 + m.row);
+      ix.snd_o = __ldg(p.senders + r0 + m.row);
+    }
+    const long long g = r0 + m.warp * 8 + (m.lane & 7);
+    if (g < p.M) {
+      ix.dst_c = (EDGE && p.rowmap) ? __ldg(p.rowmap + g) : (int)g;
+      if (EDGE) ix.rcv_c = __ldg(p.receivers + g);
+    }
+    return ix;
+  };
+  Idx nxt = load_idx(blockIdx.x);
+  Timeline tl;
+  tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
+
+  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    tl.stamp();   // 0 tile start
+    const long long row0 = tile * TILE_ROWS;
+    const long long grow = row0 + m.row;          // epilogue (row-owner) mapping
+    const bool rvalid = grow < p.M;
+    const Idx cur = nxt;
+    const int rcv_o = cur.rcv_o, snd_o = cur.snd_o, dst_c = cur.dst_c, rcv_c = cur.rcv_c;
+
+    // ---- load phase: fp32 rows -> fp16 operand tile
+    {
+      auto rf = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, dst_c, i); };
+      load8_f32_to_tile(sA, 128, 0, p.in0, m, rf, pol_stream);
+      if (!EDGE) load8_f32_to_tile(sA, 128, 128, p.in1, m, rf, pol_stream);
+    }
+    nxt = load_idx(tile + gridDim.x);
+    tile_ready();
     if (!w_ready) {
       mbar_wait(&wbar, 0);
       w_ready = true;
     }
+    tl.stamp();   // 1 operand tile ready
 
     // ---- layer 1
-    if (t == 0) {
+    if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32, 128, 0, 0, 128, K0_STEPS, 0);
-      mma_commit(&mbar[wg]);
+      mma_commit(&mbar);
     }
     if (EDGE) {
-      uint4 pi[16], pj[16];
+      uint4 pi[4], pj[4];
       if (rvalid) {
-        const __half* Pi = p.P + (long long)rcv * 256;
-        const __half* Pj = p.P + (long long)snd * 256 + 128;
+        const __half* Pi = p.P + (long long)rcv_o * 256 + m.c0;
+        const __half* Pj = p.P + (long long)snd_o * 256 + 128 + m.c0;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) { pi[j] = ldg_u4(Pi + 8 * j); pj[j] = ldg_u4(Pj + 8 * j); }
+        for (int j = 0; j < 4; ++j) { pi[j] = ld_u4_hint(Pi + 8 * j, pol_keep); pj[j] = ld_u4_hint(Pj + 8 * j, pol_keep); }
       } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
+        for (int j = 0; j < 4; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
       }
-      if (ndst >= 0) {
-        prefetch_row_f32(p.in0 + (long long)ndst * H);
-        prefetch_row_f16(p.P + (long long)nrcv * 256);
-        prefetch_row_f16(p.P + (long long)nsnd * 256 + 128);
+      mma_wait();
+      tl.stamp();   // 2 layer-1 product done
+      float v[32];
+      tmem_ld32(taddr, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float a[8], b[8];
+        unpack8(pi[j], a);
+        unpack8(pj[j], b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
       }
-      mbar_wait(&mbar[wg], phase);
-      phase ^= 1;
-      fence_after_sync();
+      store_row_chunk_f16(sA, 128, m.row, m.c0, v);
+      if (p.save_h1 != nullptr && rvalid) {
 #pragma unroll
-      for (int cq = 0; cq < 4; ++cq) {
-        float v[32];
-        tmem_ld32(tmem_row + cq * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float a[8], b[8];
-          unpack8(pi[cq * 4 + j], a);
-          unpack8(pj[cq * 4 + j], b);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
-        }
-        store_row_chunk_f16(sA, 128, t, cq * 32, v);
-        if (p.save_h1 != nullptr && rvalid) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(p.save_h1 + grow * H + cq * 32 + 8 * j) =
-                *reinterpret_cast<const uint4*>(sA + tile_off(128, t, cq * 32 + 8 * j));
-        }
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(p.save_h1 + grow * H + m.c0 + 8 * j) =
+              *reinterpret_cast<const uint4*>(sA + tile_off(128, m.row, m.c0 + 8 * j));
       }
     } else {
-      if (ndst >= 0) {
-        prefetch_row_f32(p.in0 + (long long)ndst * H);
-        prefetch_row_f32(p.in1 + (long long)ndst * H);
-      }
-      mbar_wait(&mbar[wg], phase);
-      phase ^= 1;
-      fence_after_sync();
-      epi_bias_relu_save(tmem_row, sb1, sA, t, rvalid ? p.save_h1 : nullptr, grow);
+      float4 bb[8];
+      load_vec32(p.b1, m.c0, bb);
+      mma_wait();
+      epi_bias_relu_q(taddr, bb, sA, m, rvalid ? p.save_h1 : nullptr, grow);
     }
-    fence_async_smem();
-    fence_before_sync();
-    named_bar(1 + wg, 128);
+    tile_ready();
+    tl.stamp();   // 3 layer-1 epilogue done (edge) 
+    // L2 prefetch of the next tile's rows (one 128-byte line per thread and stream); its indices
+    // were requested a whole layer ago
+    {
+      const long long ng = grow + (long long)gridDim.x * TILE_ROWS;
+      if (ng < p.M) {
+        if (!(EDGE && p.rowmap)) prefetch_l2(reinterpret_cast<const char*>(p.in0 + ng * H) + 128 * m.cq);
+        if (EDGE) {
+          const char* pr = reinterpret_cast<const char*>(
+              p.P + (long long)((m.cq & 2) ? nxt.snd_o : nxt.rcv_o) * 256 + ((m.cq & 2) ? 128 : 0));
+          prefetch_l2(pr + 128 * (m.cq & 1));
+        } else {
+          prefetch_l2(reinterpret_cast<const char*>(p.in1 + ng * H) + 128 * m.cq);
+        }
+      }
+    }
 
     // ---- layers 2, 3
 #pragma unroll 1
     for (int layer = 1; layer < 3; ++layer) {
-      if (t == 0) {
+      if (m.tid == 0) {
         fence_after_sync();
         umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
-        mma_commit(&mbar[wg]);
+        mma_commit(&mbar);
       }
-      mbar_wait(&mbar[wg], phase);
-      phase ^= 1;
-      fence_after_sync();
+      float4 bb[8];
+      load_vec32(layer == 1 ? p.b2 : p.b3, m.c0, bb);
+      mma_wait();
+      tl.stamp();   // 4, 6 product done
       __half* save = layer == 1 ? p.save_h2 : p.save_h3;
-      epi_bias_relu_save(tmem_row, layer == 1 ? sb2 : sb3, sA, t, rvalid ? save : nullptr, grow);
-      fence_async_smem();
-      fence_before_sync();
-      named_bar(1 + wg, 128);
+      epi_bias_relu_q(taddr, bb, sA, m, rvalid ? save : nullptr, grow);
+      tile_ready();
+      tl.stamp();   // 5, 7 epilogue done
     }
 
     // ---- layer 4 + RMSNorm + residual (+ segmented sum over receivers)
-    if (t == 0) {
+    if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
-      mma_commit(&mbar[wg]);
+      mma_commit(&mbar);
     }
-    const int hw = lane >> 4, q = lane & 15;
-    const int cbase = w * 32 + hw * 16;       // first row of my half-warp
-    mbar_wait(&mbar[wg], phase);
-    phase ^= 1;
-    fence_after_sync();
-    float ss = 0.f;
-#pragma unroll 1
-    for (int c0 = 0; c0 < H; c0 += 32) {
-      float v[32];
-      tmem_ld32(tmem_row + c0, v);
-      float4 bb[8];
+    float4 old[8];
+    int dst[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) bb[j] = ld_f4(sb4 + c0 + 4 * j);
+    for (int i = 0; i < 8; ++i) {       // residual rows (coalesced mapping), in flight during the product
+      dst[i] = __shfl_sync(0xffffffffu, dst_c, i);
+      old[i] = dst[i] >= 0 ? ld_f4_hint(p.in0 + (long long)dst[i] * H + 4 * m.lane, pol_stream)
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    mma_wait();
+    tl.stamp();   // 8 layer-4 product done (residual rows requested before)
+    {
+      float v[32];
+      tmem_ld32(taddr, v);
+      float4 bb[8];
+      load_vec32(p.b4, m.c0, bb);
       tmem_ld_wait();
+      float ss = 0.f;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float a0 = v[4 * j] + bb[j].x, a1 = v[4 * j + 1] + bb[j].y, a2 = v[4 * j + 2] + bb[j].z,
-              a3 = v[4 * j + 3] + bb[j].w;
-        ss += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+        v[4 * j] += bb[j].x; v[4 * j + 1] += bb[j].y; v[4 * j + 2] += bb[j].z; v[4 * j + 3] += bb[j].w;
+        ss += v[4 * j] * v[4 * j] + v[4 * j + 1] * v[4 * j + 1] + v[4 * j + 2] * v[4 * j + 2] + v[4 * j + 3] * v[4 * j + 3];
+      }
+      // (the barriers inside row_sum4 also order the product's reads of sA before the node kernel's staging writes)
+      float4 sc[8];
+      load_vec32(p.scale, m.c0, sc);
+      ss = row_sum4(ss, tail->red, m);
+      const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 o;
+        o.x = sc[j].x * (v[4 * j + 0] * inv);
+        o.y = sc[j].y * (v[4 * j + 1] * inv);
+        o.z = sc[j].z * (v[4 * j + 2] * inv);
+        o.w = sc[j].w * (v[4 * j + 3] * inv);
+        *reinterpret_cast<float4*>(stage + stage_off(m.row, m.c0 + 4 * j)) = o;
       }
     }
-    const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
-    float* stage = reinterpret_cast<float*>(sA);   // operand tile is free: reuse as fp32 staging (64 columns)
-#pragma unroll 1
-    for (int half = 0; half < 2; ++half) {
-      // residual rows of this half-warp's 16 rows: issue before the staging pass
-      float4 old[16];
-      int dst[16];
+    fence_before_sync();
+    __syncthreads();
+    tl.stamp();   // 9 norm + staging done
+    {
+      int cur = -1;
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        dst[i] = __shfl_sync(0xffffffffu, my_dst, hw * 16 + i);
-        old[i] = dst[i] >= 0 ? ld_stream_f4(p.in0 + (long long)dst[i] * H + half * 64 + 4 * q)
-                             : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-#pragma unroll 1
-      for (int cc = 0; cc < 64; cc += 32) {
-        const int c0 = half * 64 + cc;
-        float v[32];
-        tmem_ld32(tmem_row + c0, v);
-        float4 bb[8], sc[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { bb[j] = ld_f4(sb4 + c0 + 4 * j); sc[j] = ld_f4(ssc + c0 + 4 * j); }
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float4 o;
-          o.x = sc[j].x * ((v[4 * j + 0] + bb[j].x) * inv);
-          o.y = sc[j].y * ((v[4 * j + 1] + bb[j].y) * inv);
-          o.z = sc[j].z * ((v[4 * j + 2] + bb[j].z) * inv);
-          o.w = sc[j].w * ((v[4 * j + 3] + bb[j].w) * inv);
-          *reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(stage) + stage_off_half(t, cc + 4 * j)) = o;
-        }
-      }
-      fence_before_sync();
-      named_bar(1 + wg, 128);
-      // coalesced phase: half-warp per row, 16 rows per half-warp, 64 columns
-      {
-        int cur = -1;
-        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int r = cbase + i;
-          const float4 v = *reinterpret_cast<const float4*>(reinterpret_cast<const uint8_t*>(stage) +
-                                                            stage_off_half(r, 4 * q));
-          const int rc = EDGE ? __shfl_sync(0xffffffffu, rcv, hw * 16 + i) : -1;
-          if (dst[i] >= 0) {
-            float4 o = make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w);
-            st_stream_f4(p.out + (long long)dst[i] * H + half * 64 + 4 * q, o);
-          }
-          if (EDGE && dst[i] >= 0) {
+      for (int i = 0; i < 8; ++i) {
+        const float4 y = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
+        const int rc = EDGE ? __shfl_sync(0xffffffffu, rcv_c, i) : -1;
+        if (dst[i] >= 0) {
+          st_f4_hint(p.out + (long long)dst[i] * H + 4 * m.lane,
+                     make_float4(old[i].x + y.x, old[i].y + y.y, old[i].z + y.z, old[i].w + y.w), pol_stream);
+          if (EDGE) {
             if (rc != cur) {
-              if (cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
+              if (cur >= 0) red_add_f4_hint(p.aggr + (long long)cur * H + 4 * m.lane, sum, pol_keep);
               cur = rc;
-              sum = v;
+              sum = y;
             } else {
-              sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+              sum.x += y.x; sum.y += y.y; sum.z += y.z; sum.w += y.w;
             }
           }
         }
-        if (EDGE && cur >= 0) red_add_f4(p.aggr + (long long)cur * H + half * 64 + 4 * q, sum);
       }
-      named_bar(1 + wg, 128);
+      if (EDGE && cur >= 0) red_add_f4_hint(p.aggr + (long long)cur * H + 4 * m.lane, sum, pol_keep);
     }
+    __syncthreads();      // staging / operand tile free for the next tile
+    tl.stamp();   // 10 output done
   }
   if (!w_ready) mbar_wait(&wbar, 0);   // never exit with the weight copy in flight
 
   fence_before_sync();
   __syncthreads();
-  if ((tid >> 5) == 0) tmem_dealloc<256>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<128>(tmem_slot);
 }
 
 // ---------------------------------------------------------------------------------
@@ -320,49 +304,55 @@ struct PFwdParams {
   __half* P;             // [N,256]
 };
 
-__global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
+__global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW = smem;                   // 64 KB
   uint8_t* sA = smem + 2 * TILE_BYTES;  // 32 KB
-  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + 3 * TILE_BYTES);
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 3 * TILE_BYTES);
   uint64_t& wbar = tail->bar[0];
   uint64_t& mbar = tail->bar[1];
   uint32_t& tmem_slot = tail->tmem_slot;
-  const float* sb1 = tail->vec[0];
-  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  copy_vec128(tail->vec[0], p.b1, tid, blockDim.x);
-  if (tid == 0) {
+  const Map m = make_map();
+  if (m.tid == 0) {
     mbar_init(&wbar, 1);
     mbar_init(&mbar, 1);
     mbar_init_fence();
   }
-  if (w == 0) tmem_alloc<256>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<256>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem_acc = tmem_slot;
-  const uint32_t tmem_row = tmem_acc + ((uint32_t)(w * 32) << 16);
-  if (tid == 0) {
+  if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, 2 * TILE_BYTES);
     bulk_g2s(sW, p.Wcat, TILE_BYTES, &wbar);
     bulk_g2s(sW + TILE_BYTES, reinterpret_cast<const uint8_t*>(p.Wcat) + TILE_BYTES, TILE_BYTES, &wbar);
   }
-  mbar_wait(&wbar, 0);
+  float4 bb[8];
+  load_vec32(p.b1, m.c0, bb);
+  const uint64_t pol_keep = policy_evict_last();
+  bool w_ready = false;
   uint32_t phase = 0;
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const long long row0 = tile * TILE_ROWS;
-    load_rows_f32_to_tile_b<16>(sA, 128, 0, p.x, w * 32, 32, lane,
-                                [&](int r) -> long long { long long g = row0 + r; return g < p.N ? g : -1; });
+    load8_f32_to_tile(sA, 128, 0, p.x, m, [&](int i) -> long long {
+      const long long g = row0 + m.warp * 8 + i;
+      return g < p.N ? g : -1;
+    }, pol_keep);
     {
-      const long long ng = row0 + (long long)gridDim.x * TILE_ROWS + tid;
-      if (ng < p.N) prefetch_row_f32(p.x + ng * H);
+      const long long ng = row0 + (long long)gridDim.x * TILE_ROWS + m.row;
+      if (ng < p.N) prefetch_l2(reinterpret_cast<const char*>(p.x + ng * H) + 128 * m.cq);
     }
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (!w_ready) {
+      mbar_wait(&wbar, 0);
+      w_ready = true;
+    }
+    if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tmem_acc, smem_u32(sA), 128, 0, smem_u32(sW), 256, 0, 0, 256, 8, 0);
       mma_commit(&mbar);
@@ -370,17 +360,16 @@ __global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
     mbar_wait(&mbar, phase);
     phase ^= 1;
     fence_after_sync();
-    const long long grow = row0 + tid;
-#pragma unroll 1
-    for (int c0 = 0; c0 < 256; c0 += 32) {
+    const long long grow = row0 + m.row;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
       float v[32];
-      tmem_ld32(tmem_row + c0, v);
+      tmem_ld32(tmem_acc + m.lane_off + half * 128 + m.c0, v);
       tmem_ld_wait();
-      if (c0 < 128) {
+      if (half == 0) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          float4 bb = ld_f4(sb1 + c0 + 4 * j);
-          v[4 * j] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+          v[4 * j] += bb[j].x; v[4 * j + 1] += bb[j].y; v[4 * j + 2] += bb[j].z; v[4 * j + 3] += bb[j].w;
         }
       }
       if (grow < p.N) {
@@ -391,16 +380,17 @@ __global__ void __launch_bounds__(128, 1) p_fwd_kernel(const PFwdParams p) {
           pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
           pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]);
           pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
-          *reinterpret_cast<uint4*>(p.P + grow * 256 + c0 + 8 * j) = pk;
+          st_u4_hint(p.P + grow * 256 + half * 128 + m.c0 + 8 * j, pk, pol_keep);
         }
       }
     }
     fence_before_sync();
     __syncthreads();
   }
+  if (!w_ready) mbar_wait(&wbar, 0);
   fence_before_sync();
   __syncthreads();
-  if (w == 0) tmem_dealloc<256>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
 }
 
 // ---------------------------------------------------------------------------------
@@ -464,7 +454,7 @@ extern "C" int mgn_pack_block(const float* eW1, const float* eW2, const float* e
   return MGN_OK;
 }
 
-static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 2 * 32768 + TAIL_BYTES;
+static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 32768 + 2 * 32768 + TAIL_BYTES;
 static constexpr int NODE_FWD_SMEM = 5 * 32768 + 2 * 32768 + TAIL_BYTES;
 static constexpr int P_FWD_SMEM = 3 * 32768 + TAIL_BYTES;
 
@@ -487,14 +477,15 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_FWD_SMEM));
     attr = true;
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
-  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(tiles, 2));
-  mlp_fwd_kernel<true><<<grid, 256, EDGE_FWD_SMEM, stream>>>(p);
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
+  mlp_fwd_kernel<true><<<grid, NT, EDGE_FWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -511,13 +502,14 @@ extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float*
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
   p.b1 = b1; p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_FWD_SMEM));
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  mlp_fwd_kernel<false><<<grid, 128, NODE_FWD_SMEM, stream>>>(p);
+  mlp_fwd_kernel<false><<<grid, NT, NODE_FWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -535,7 +527,7 @@ extern "C" int mgn_p_fwd(int64_t N, const float* x, const void* packed, const fl
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  p_fwd_kernel<<<grid, 128, P_FWD_SMEM, stream>>>(p);
+  p_fwd_kernel<<<grid, NT, P_FWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

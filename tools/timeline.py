@@ -1,0 +1,59 @@
+"""Developer tool: per-phase cycle counts of block 0 of the edge forward kernel (Timeline stamps)."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from graph_physics_b200 import _lib as L, graph as G, ops  # noqa: E402
+
+z = np.load(os.path.join(ROOT, "tests", "golden", "cylinder_mesh.npz"))
+n1 = z["points"].shape[0]
+ei = G.tile_batch(torch.as_tensor(z["edge_index"].astype(np.int64)).cuda(), n1, 32)
+N, E = n1 * 32, ei.shape[1]
+csr = G.build_csr(ei, N)
+dev = "cuda"
+torch.manual_seed(0)
+ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+b = [torch.randn(128, device=dev) * 0.05 for _ in range(8)]
+sc = torch.ones(128, device=dev)
+packed = ops.pack_block(ew, nw)
+x = torch.randn(N, 128, device=dev)
+e = torch.randn(E, 128, device=dev)
+e2, x2 = torch.empty_like(e), torch.empty_like(x)
+P = ops.p_fwd(x, packed, b[0])
+aggr = torch.empty(N, 128, device=dev)
+cap = 11 * 19 + 8
+buf = torch.zeros(cap, dtype=torch.int64, device=dev)
+which = sys.argv[1] if len(sys.argv) > 1 else "edge"
+
+
+def run():
+    if which == "edge":
+        ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
+    else:
+        ops.node_fwd(x, aggr, packed, b[4], b[5], b[6], b[7], sc, x_out=x2)
+
+
+for _ in range(3):
+    run()
+torch.cuda.synchronize()
+L.check(L.lib().mgn_debug_set_timeline(ctypes.c_void_p(buf.data_ptr()), ctypes.c_int(cap)))
+run()
+torch.cuda.synchronize()
+L.check(L.lib().mgn_debug_set_timeline(ctypes.c_void_p(0), ctypes.c_int(0)))
+t = buf.cpu().numpy()
+t = t[t > 0]
+names = ["load", "L1 mma", "L1 epi", "L2 mma", "L2 epi", "L3 mma", "L3 epi", "L4 mma", "norm+stage", "output", "next"]
+per = 11
+ntile = len(t) // per
+print("tiles seen", ntile)
+for k in range(ntile):
+    s = t[k * per:(k + 1) * per]
+    d = np.diff(s)
+    nxt = (t[(k + 1) * per] - s[-1]) if (k + 1) * per < len(t) else 0
+    print(f"tile {k:2d} total {s[-1] - s[0]:6d} | " + " ".join(f"{names[i]}={d[i]}" for i in range(per - 1)) + f" | gap {nxt}")
