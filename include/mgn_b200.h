@@ -70,6 +70,67 @@ int mgn_filter_edges(const int64_t* edge_index, int64_t E, const int64_t* node_i
 int mgn_edge_features(const float* pos, int dim, const int64_t* edge_index, int64_t E, float* out,
                       void* stream);
 
+/* ------------------------------------------------------------------ message-passing step
+ * One GraphNetBlock (graphphysics/models/layers.py:622-746) with hidden_size 128, nb_of_layers 4,
+ * layer_norm (RMSNorm, layers.py:49-74).  Latents are fp32 [rows,128] row-major.  Products run on
+ * tcgen05 with fp16 operands and fp32 accumulation; residual streams, RMSNorm and the aggregation
+ * are fp32.  Edge rows are in receiver-sorted CSR order (mgn_build_csr), or in the caller's order
+ * when `rowmap` (= perm) is given.  The first edge layer is split: the caller runs mgn_p_fwd per
+ * node, the edge kernel adds P[:, :128][receiver] + P[:, 128:][sender] to e We^T.
+ */
+/* bytes of one block's packed fp16 weight tiles (edge We,W2,W3,W4 | [W_i;W_j] | node W1',W2',W3',W4') */
+int64_t mgn_packed_block_bytes(void);
+/* build_mlp weights (layers.py:137-183; fp32, [out,in] row-major: eW1 [128,384], nW1 [128,256],
+ * others [128,128]) -> 128-byte-swizzled fp16 panel tiles in `packed`. */
+int mgn_pack_block(const float* eW1, const float* eW2, const float* eW3, const float* eW4,
+                   const float* nW1, const float* nW2, const float* nW3, const float* nW4,
+                   void* packed, void* stream);
+/* P [N,256] fp16 = [x W_i^T + b1 | x W_j^T]: the x_i / x_j columns of edge_block layer 1
+ * (cat order [edge_attr, x_i, x_j], layers.py:703-719). */
+int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P, void* stream);
+/* edge update + sum aggregation at the receiver (layers.py:687-698): e_out = e_in + edge_block(...),
+ * aggr [N,128] = segmented sum of the PRE-residual messages (zeroed here).  save_h* (optional,
+ * [E,128] fp16) receive the hidden activations. */
+int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
+                 const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                 const void* packed, const float* b2, const float* b3, const float* b4,
+                 const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream);
+/* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
+ * fp16, optional) are the hidden activations mgn_node_bwd needs. */
+int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                 const float* b1, const float* b2, const float* b3, const float* b4,
+                 const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream);
+
+/* ------------------------------------------------------------------ backward of the step
+ * What torch.autograd derives from GraphNetBlock.forward in the reference.  Parameter gradients of
+ * one block accumulate (red.add) into a flat fp32 buffer of mgn_grad_block_floats() floats laid out
+ * in the block's state-dict order (edge_block.0.weight, .0.bias, ..., .7.scale, node_block...);
+ * the caller zeroes it.  Upstream gradients may be pre-scaled by any power of two. */
+int64_t mgn_grad_block_floats(void);
+/* node_block backward from the fp16 hidden saves: g_x = g_xout + dz1 W1'[:, :128],
+ * g_aggr = dz1 W1'[:, 128:], dz1 [N,128] fp16; dW2'..dW4', all biases, dscale. */
+int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                 float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                 const float* scale, float* grad_block, void* stream);
+/* dW1' += dz1^T [x | aggr] */
+int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
+                    void* stream);
+/* edge_block + aggregation backward; recomputes the edge MLP from e_in (no edge saves).
+ * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We; gP [N,256] fp32 (zeroed here) receives
+ * dz1 summed by receiver (cols 0..127) and by sender (cols 128..255). g_eout may be null (= 0). */
+int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, const float* g_eout,
+                 const float* g_aggr, const void* P, const int32_t* senders, const int32_t* receivers,
+                 float* g_e, float* gP, const void* packed, const float* b2, const float* b3,
+                 const float* b4, const float* scale, float* grad_block, void* stream);
+/* backward of mgn_p_fwd: g_x += gP [W_i ; W_j]; dW_i, dW_j, db1 into grad_block */
+int mgn_p_bwd(int64_t N, const float* gP, const float* x, float* g_x, const void* packed,
+              float* grad_block, void* stream);
+
+/* ------------------------------------------------------------------ developer hooks */
+/* per-phase clock64 stamps of CTA 0 of the next edge/node kernels into `buf` (device, `cap`
+ * entries; null disables) -- tools/timeline.py */
+int mgn_debug_set_timeline(long long* buf, int cap);
+
 /* ------------------------------------------------------------------ self test */
 /* one-tile tcgen05 product pinning the shared-memory descriptor conventions (tests only) */
 int mgn_selftest_umma(const void* a, const void* b, float* d, int a_cols, int b_cols, int a_mn, int b_mn,
