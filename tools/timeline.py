@@ -30,10 +30,18 @@ aggr = torch.empty(N, 128, device=dev)
 cap = 11 * 19 + 8
 buf = torch.zeros(cap, dtype=torch.int64, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
+ge_in = torch.randn(E, 128, device=dev)
+g_aggr = torch.randn(N, 128, device=dev)
+ge_out = torch.empty_like(e)
+gP = torch.empty(N, 256, device=dev)
+gblock = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
 
 
 def run():
-    if which == "edge":
+    if which == "edge_bwd":
+        ops.edge_bwd(e, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
+                     g_e=ge_out, gP=gP)
+    elif which == "edge":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
     else:
         ops.node_fwd(x, aggr, packed, b[4], b[5], b[6], b[7], sc, x_out=x2)
@@ -50,6 +58,9 @@ t = buf.cpu().numpy()
 t = t[t > 0]
 names = ["load", "L1 mma", "L1 epi", "L2 mma", "L2 epi", "L3 mma", "L3 epi", "L4 mma", "norm+stage", "output", "next"]
 per = 11
+if which == "edge_bwd":
+    names = ["load", "R1", "R2+R3", "R4+norm", "D4..D2", "D1+out", "next"]
+    per = 7
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
