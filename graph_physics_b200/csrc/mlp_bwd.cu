@@ -20,6 +20,7 @@
 // a power of two (processor.py) so that fp16 operands keep their precision; all of this is linear in g.
 #include "mlp_v2.cuh"
 #include "mlp_fwd_abi.cuh"
+#include <cstdlib>
 
 using namespace mgn;
 
@@ -91,6 +92,7 @@ struct EdgeBwdParams {
   float* grad;              // flat gradient block (GB_* offsets), accumulated with red.add
   long long* dbg;
   int dbg_cap;
+  int dbg_skip;             // developer experiments only (MGN_DEBUG_SKIP): bit mask of memory operations to leave out
 };
 
 __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) {
@@ -150,51 +152,64 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     fence_before_sync();
     __syncthreads();
   };
-  // coalesced-mapping indices (lane i < 8 <-> tile row 8*warp + i), requested one tile ahead
-  struct Idx { int dst, rcv, snd; };
+  // coalesced-mapping indices (lane i < 8 <-> tile row 8*warp + i) and the epilogue-mapping destination row
+  // (own: row m.row of the tile), requested one tile ahead
+  struct Idx { int dst, rcv, snd, own; };
   auto load_idx = [&](long long tile_) -> Idx {
-    Idx ix{-1, -1, -1};
+    Idx ix{-1, -1, -1, -1};
     const long long g = tile_ * TILE_ROWS + m.warp * 8 + (m.lane & 7);
+    const long long go = tile_ * TILE_ROWS + m.row;
     if (tile_ < num_tiles && g < p.E) {
       ix.dst = p.rowmap ? __ldg(p.rowmap + g) : (int)g;
       ix.rcv = __ldg(p.receivers + g);
       ix.snd = __ldg(p.senders + g);
     }
+    if (tile_ < num_tiles && go < p.E) ix.own = p.rowmap ? __ldg(p.rowmap + go) : (int)go;
     return ix;
   };
-  Idx nxt = load_idx(blockIdx.x);
+  const int hw = m.lane >> 4, q = m.lane & 15;
+  // asynchronous gathers of the layer-1 partial products into swizzled staging tiles (half-warp per 256-byte row)
+  auto issue_pi = [&](const Idx& ix) {       // P_i[receiver] -> sH2
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int rc = __shfl_sync(0xffffffffu, ix.rcv, 2 * i + hw);
+      cp_async16(uH2 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q), p.P + (long long)(rc >= 0 ? rc : 0) * 256 + 8 * q,
+                 rc >= 0 ? 16u : 0u, pol_keep);
+    }
+  };
+  auto issue_pj = [&](const Idx& ix) {       // P_j[sender] -> sH3
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int sn = __shfl_sync(0xffffffffu, ix.snd, 2 * i + hw);
+      cp_async16(uH3 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q),
+                 p.P + (long long)(sn >= 0 ? sn : 0) * 256 + 128 + 8 * q, sn >= 0 ? 16u : 0u, pol_keep);
+    }
+  };
+  // g = g_eout + g_aggr[receiver] -> sG (fp16)
+  auto load_g = [&](const Idx& ix) {
+    auto dst_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.dst, i); };
+    auto rcv_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.rcv, i); };
+    if (p.g_eout) load8_sum2_to_tile(sG, p.g_eout, p.g_aggr, m, dst_of, rcv_of, pol_stream, pol_keep);
+    else load8_f32_to_tile(sG, 128, 0, p.g_aggr, m, rcv_of, pol_keep);
+  };
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
-  const int hw = m.lane >> 4, q = m.lane & 15;
+
+  // ---- prologue: everything of the first tile except e
+  Idx cur = load_idx(blockIdx.x);
+  issue_pi(cur);
+  issue_pj(cur);
+  load_g(cur);
+  Idx nxt = load_idx((long long)blockIdx.x + gridDim.x);
 
   uint32_t it = 0;
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     tl.stamp();   // 0
-    const Idx cur = nxt;
-    auto dst_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); };
-    auto rcv_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.rcv, i); };
-
-    // ---- load: e -> sE, g = g_eout + g_aggr[recv] -> sG, gathered P_i / P_j rows -> sH2 / sH3 (all coalesced)
-    load8_f32_to_tile(sE, 128, 0, p.e_in, m, dst_of, pol_stream);
-    if (p.g_eout) load8_sum2_to_tile(sG, p.g_eout, p.g_aggr, m, dst_of, rcv_of, pol_stream, pol_keep);
-    else load8_f32_to_tile(sG, 128, 0, p.g_aggr, m, rcv_of, pol_keep);
-    {
-      uint4 vi[4], vj[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int rc = __shfl_sync(0xffffffffu, cur.rcv, 2 * i + hw);
-        const int sn = __shfl_sync(0xffffffffu, cur.snd, 2 * i + hw);
-        vi[i] = rc >= 0 ? ld_u4_hint(p.P + (long long)rc * 256 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
-        vj[i] = rc >= 0 ? ld_u4_hint(p.P + (long long)sn * 256 + 128 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint32_t off = tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q);
-        *reinterpret_cast<uint4*>(sH2 + off) = vi[i];
-        *reinterpret_cast<uint4*>(sH3 + off) = vj[i];
-      }
-    }
-    nxt = load_idx(tile + gridDim.x);
+    const bool has_next = tile + gridDim.x < num_tiles;
+    // ---- load e -> sE (the rest of this tile was fetched during the previous one)
+    load8_f32_to_tile(sE, 128, 0, p.e_in, m,
+                      [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); }, pol_stream);
+    cp_async_wait_all();
     tile_ready();
     tl.stamp();   // 1 loads done
 
@@ -219,7 +234,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tile_ready();
     tl.stamp();   // 2 R1 done
-    // L2 prefetch of the next tile's streamed rows (its indices were requested during the load phase)
+    // L2 prefetch of the next tile's streamed rows
     {
       const int nd = __shfl_sync(0xffffffffu, nxt.dst, m.lane & 7);
       const int nr = __shfl_sync(0xffffffffu, nxt.rcv, m.lane & 7);
@@ -300,6 +315,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
     epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
+    if (has_next) issue_pj(nxt);          // sH3 is dead: next tile's P_j rows
     // ---- D2
     if (m.tid == 0) {
       mbar_wait(&bar_wB, 0);
@@ -320,13 +336,19 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_mma);
     }
-    float4 old[8];
-    int dst[8];
+    if (has_next) issue_pi(nxt);          // sH2 is dead: next tile's P_i rows
+    f8 old[4];                            // upstream edge gradient of this thread's 32 columns (residual add)
+    {
+      const bool ld = cur.own >= 0 && p.g_eout != nullptr && !(p.dbg_skip & 4);
+      const float* src = p.g_eout + (long long)(ld ? cur.own : 0) * H + m.c0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {       // upstream edge-gradient rows for the residual add, in flight early
-      dst[i] = __shfl_sync(0xffffffffu, cur.dst, i);
-      old[i] = (dst[i] >= 0 && p.g_eout) ? ld_f4_hint(p.g_eout + (long long)dst[i] * H + 4 * m.lane, pol_stream)
-                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < 4; ++j) {
+        if (ld) old[j] = ld_f8_hint(src + 8 * j, pol_stream);
+        else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) old[j].v[k] = 0.f;
+        }
+      }
     }
     {
       // half-warp hw handles the 4 consecutive rows 8*warp + 4*hw + i; lane q owns 8 columns
@@ -344,10 +366,12 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         unpack8(u, f);
         if (rc >= 0) {
           float* dj = p.gP + (long long)sn * 256 + 128 + 8 * q;
-          red_add_f4_hint(dj, make_float4(f[0], f[1], f[2], f[3]), pol_keep);
-          red_add_f4_hint(dj + 4, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
+          if (!(p.dbg_skip & 1)) {
+            red_add_f4_hint(dj, make_float4(f[0], f[1], f[2], f[3]), pol_keep);
+            red_add_f4_hint(dj + 4, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
+          }
           if (rc != curr) {
-            if (curr >= 0) {
+            if (curr >= 0 && !(p.dbg_skip & 2)) {
               float* di = p.gP + (long long)curr * 256 + 8 * q;
               red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
               red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
@@ -361,29 +385,39 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
           }
         }
       }
-      if (curr >= 0) {
+      if (curr >= 0 && !(p.dbg_skip & 2)) {
         float* di = p.gP + (long long)curr * 256 + 8 * q;
         red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
         red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
       }
     }
     mma_wait();
-    acc_to_stage_q(tm_W + qoff, stage, m);
+    {
+      float v[32];
+      tmem_ld32(tm_W + qoff, v);
+      tmem_ld_wait();
+      if (cur.own >= 0 && !(p.dbg_skip & 8)) {
+        float* dst = p.g_e + (long long)cur.own * H + m.c0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[8 * j + k] += old[j].v[k];
+          st_f8_hint(dst + 8 * j, &v[8 * j], pol_stream);
+        }
+      }
+    }
     fence_before_sync();
-    __syncthreads();
-    // dWe tile product into the (now free) working accumulator
+    __syncthreads();      // every thread has read the D1 accumulator
+    // dWe tile product into the working accumulator; the next tile's g is fetched under it (sG is dead)
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_dwe);
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 v = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
-      if (dst[i] >= 0)
-        st_f4_hint(p.g_e + (long long)dst[i] * H + 4 * m.lane,
-                   make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_stream);
-    }
+    tl.stamp();   // 6 D1 + g_e written
+    cur = nxt;
+    if (has_next) load_g(cur);
+    nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mbar_wait(&bar_dwe, it & 1);
     fence_after_sync();
     {
@@ -394,8 +428,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       for (int j = 0; j < 32; ++j) dwe[j] += v[j];
     }
     fence_before_sync();
-    __syncthreads();      // working accumulator, sE, sH1 and the staging are free for the next tile
-    tl.stamp();   // 6 D1 + output done
+    // no barrier here: every thread has seen bar_dwe (the product's reads of sE / sH1 are complete), and the next
+    // tile's tile_ready() orders these TMEM reads before its first product
+    tl.stamp();   // 7 next g loaded, dWe accumulated
   }
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
@@ -836,6 +871,8 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale; p.grad = grad_block;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
+  static const int dbg_skip = getenv("MGN_DEBUG_SKIP") ? atoi(getenv("MGN_DEBUG_SKIP")) : 0;
+  p.dbg_skip = dbg_skip;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(edge_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));

@@ -185,6 +185,27 @@ __device__ __forceinline__ void red_add_f4_hint(float* p, float4 v, uint64_t pol
                "f"(v.w), "l"(pol) : "memory");
 }
 
+// 256-bit global accesses (sm_100): one lane moves a whole 32-byte sector, so a thread that owns 32 consecutive
+// floats of a row (the TMEM epilogue mapping) reads / writes full sectors without a shared-memory transpose
+struct f8 { float v[8]; };
+__device__ __forceinline__ f8 ld_f8_hint(const float* p, uint64_t pol) {
+  f8 r;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]),
+                 "=f"(r.v[7]) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ void st_f8_hint(float* p, const float* v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p), "f"(v[0]),
+               "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]), "l"(pol) : "memory");
+}
+// 16-byte asynchronous global -> shared copy (LDGSTS); src_bytes = 0 zero-fills the destination
+__device__ __forceinline__ void cp_async16(uint32_t dst_saddr, const void* src, uint32_t src_bytes, uint64_t pol) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;" ::"r"(dst_saddr), "l"(src),
+               "r"(src_bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // ------------------------------------------------------------------ developer timeline (tools/timeline.py)
 // When a buffer is registered (mgn_debug_set_timeline; host globals below), thread 0 of block 0 records clock64()
 // at the phase boundaries of its tiles.  Null (the default) costs one predicated load per stamp.
