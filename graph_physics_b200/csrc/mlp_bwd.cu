@@ -75,14 +75,15 @@ __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb
 // ===================================================================================== edge
 struct EdgeBwdParams {
   long long E;
-  const float* e_in;        // [E,128] step input (saved)
+  const float* e_in;        // [E,128] step input (saved); used when e16 is null
+  const __half* e16;        // fp16 tile images of e_in written by edge_fwd (32 KB per 128-row tile), or null
   const int32_t* rowmap;    // CSR position -> row of e_in / g_eout / g_e (null = identity)
   const float* g_eout;      // [E,128] or null (= 0)
   const float* g_aggr;      // [N,128]
   const __half* P;          // [N,256]
   const int32_t* senders;
   const int32_t* receivers;
-  float* g_e;               // [E,128] out
+  float* g_e;               // [E,128] out; holds g_eout on entry when g_eout != null (accumulated in place)
   float* gP;                // [N,256] fp32, zero on entry
   const __half* W;          // packed edge tiles We, W2, W3, W4
   const float* b2;
@@ -105,12 +106,13 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint8_t* sH2 = smem + 4 * SLOT;   // during layer 1: staging of the gathered P_i rows
   uint8_t* sH3 = smem + 5 * SLOT;   // during layer 1: staging of the gathered P_j rows
   uint8_t* sG = smem + 6 * SLOT;
-  uint8_t* stage = sH3;             // 64 KB fp32 staging = sH3 + sG (both dead by then)
+  uint8_t* lin32 = sH2;             // 64 KB row-linear fp32 staging = sH2 + sH3 (dead after D2 / D3)
   Tail2* tail = reinterpret_cast<Tail2*>(smem + 7 * SLOT);
   uint64_t& bar_wA = tail->bar[0];
   uint64_t& bar_wB = tail->bar[1];
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_dwe = tail->bar[3];
+  uint64_t& bar_e = tail->bar[4];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
 
@@ -119,6 +121,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_wB, 1);
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_dwe, 1);
+    mbar_init(&bar_e, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -152,8 +155,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     fence_before_sync();
     __syncthreads();
   };
-  // coalesced-mapping indices (lane i < 8 <-> tile row 8*warp + i) and the epilogue-mapping destination row
-  // (own: row m.row of the tile), requested one tile ahead
+  // Indices, requested one tile ahead.  Coalesced mapping (lane i < 8 <-> tile row 8*warp + i): dst, rcv, snd.
+  // Epilogue mapping (this thread's tile row m.row): own = row of g_e (used with a rowmap only).
   struct Idx { int dst, rcv, snd, own; };
   auto load_idx = [&](long long tile_) -> Idx {
     Idx ix{-1, -1, -1, -1};
@@ -164,41 +167,44 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       ix.rcv = __ldg(p.receivers + g);
       ix.snd = __ldg(p.senders + g);
     }
-    if (tile_ < num_tiles && go < p.E) ix.own = p.rowmap ? __ldg(p.rowmap + go) : (int)go;
+    if (p.rowmap && tile_ < num_tiles && go < p.E) ix.own = __ldg(p.rowmap + go);
     return ix;
   };
   const int hw = m.lane >> 4, q = m.lane & 15;
   // asynchronous gathers of the layer-1 partial products into swizzled staging tiles (half-warp per 256-byte row)
-  auto issue_pi = [&](const Idx& ix) {       // P_i[receiver] -> sH2
+  auto issue_p = [&](const Idx& ix) {        // P_i[receiver] -> sH2, P_j[sender] -> sH3
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int rc = __shfl_sync(0xffffffffu, ix.rcv, 2 * i + hw);
-      cp_async16(uH2 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q), p.P + (long long)(rc >= 0 ? rc : 0) * 256 + 8 * q,
-                 rc >= 0 ? 16u : 0u, pol_keep);
-    }
-  };
-  auto issue_pj = [&](const Idx& ix) {       // P_j[sender] -> sH3
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
       const int sn = __shfl_sync(0xffffffffu, ix.snd, 2 * i + hw);
-      cp_async16(uH3 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q),
-                 p.P + (long long)(sn >= 0 ? sn : 0) * 256 + 128 + 8 * q, sn >= 0 ? 16u : 0u, pol_keep);
+      const uint32_t off = tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q);
+#if 0
+      cp_async16(uH2 + off, p.P + (long long)(rc >= 0 ? rc : 0) * 256 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
+      cp_async16(uH3 + off, p.P + (long long)(rc >= 0 ? sn : 0) * 256 + 128 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
+#else
+      *reinterpret_cast<uint4*>(sH2 + off) = rc >= 0 ? ld_u4_hint(p.P + (long long)rc * 256 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
+      *reinterpret_cast<uint4*>(sH3 + off) = rc >= 0 ? ld_u4_hint(p.P + (long long)sn * 256 + 128 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
+#endif
     }
   };
-  // g = g_eout + g_aggr[receiver] -> sG (fp16)
+  // g = g_eout + g_aggr[receiver] -> sG (fp16), coalesced
   auto load_g = [&](const Idx& ix) {
     auto dst_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.dst, i); };
     auto rcv_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.rcv, i); };
     if (p.g_eout) load8_sum2_to_tile(sG, p.g_eout, p.g_aggr, m, dst_of, rcv_of, pol_stream, pol_keep);
     else load8_f32_to_tile(sG, 128, 0, p.g_aggr, m, rcv_of, pol_keep);
   };
+  // e tile: the forward kernel's fp16 tile image (one 32 KB bulk copy), else converted from the fp32 rows
+  auto issue_e16 = [&](long long tile_) {      // thread 0
+    mbar_arrive_expect_tx(&bar_e, SLOT);
+    bulk_g2s(sE, reinterpret_cast<const uint8_t*>(p.e16) + (size_t)tile_ * SLOT, SLOT, &bar_e);
+  };
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
 
-  // ---- prologue: everything of the first tile except e
+  // ---- prologue: g and e of the first tile
   Idx cur = load_idx(blockIdx.x);
-  issue_pi(cur);
-  issue_pj(cur);
+  if (p.e16 != nullptr && m.tid == 0) issue_e16(blockIdx.x);
   load_g(cur);
   Idx nxt = load_idx((long long)blockIdx.x + gridDim.x);
 
@@ -206,20 +212,24 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     tl.stamp();   // 0
     const bool has_next = tile + gridDim.x < num_tiles;
-    // ---- load e -> sE (the rest of this tile was fetched during the previous one)
-    load8_f32_to_tile(sE, 128, 0, p.e_in, m,
-                      [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); }, pol_stream);
-    cp_async_wait_all();
-    tile_ready();
-    tl.stamp();   // 1 loads done
+    __syncthreads();      // the previous tile's g_e staging (sH2 + sH3) has been read by the bulk copy
+    if (p.e16 == nullptr) {
+      load8_f32_to_tile(sE, 128, 0, p.e_in, m,
+                        [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); }, pol_stream);
+      tile_ready();
+    }
+    tl.stamp();   // 1
 
     // ---- R1: z1 = e We^T + P_i[recv] + P_j[send]
     if (m.tid == 0) {
       if (it == 0) mbar_wait(&bar_wA, 0);
+      if (p.e16 != nullptr) mbar_wait(&bar_e, it & 1);
       fence_after_sync();
       umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
       mma_commit(&bar_mma);
     }
+    issue_p(cur);         // under the product: P_i / P_j rows -> staging
+    __syncthreads();      // the staged P rows are visible to every thread
     mma_wait();
     if (m.tid == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
     {
@@ -240,7 +250,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       const int nr = __shfl_sync(0xffffffffu, nxt.rcv, m.lane & 7);
       const int part = m.lane >> 3;           // 4 lanes per row: one 128-byte line each
       if (nd >= 0) {
-        prefetch_l2(reinterpret_cast<const char*>(p.e_in + (long long)nd * H) + 128 * part);
         if (p.g_eout) prefetch_l2(reinterpret_cast<const char*>(p.g_eout + (long long)nd * H) + 128 * part);
         prefetch_l2(reinterpret_cast<const char*>(p.g_aggr + (long long)nr * H) + 128 * part);
       }
@@ -315,7 +324,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
     epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
-    if (has_next) issue_pj(nxt);          // sH3 is dead: next tile's P_j rows
     // ---- D2
     if (m.tid == 0) {
       mbar_wait(&bar_wB, 0);
@@ -329,29 +337,16 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     epi_relu_mask_q(tm_W + qoff, sH1, m);    // sH1 <- dz1
     tile_ready();
     tl.stamp();   // 5 D4..D2 done
-    // ---- D1: g_e = g_eout + dz1 We ; scatter dz1 while the product runs
+    // ---- dWe = dz1^T e16 into the working accumulator; under it, dz1 is scattered into gP:
+    //      by receiver (cols 0..127, segmented sum over the sorted receivers) and by sender (cols 128..255)
     if (m.tid == 0) {
-      mbar_wait(&bar_wA, 0);
       fence_after_sync();
-      umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
-    }
-    if (has_next) issue_pi(nxt);          // sH2 is dead: next tile's P_i rows
-    f8 old[4];                            // upstream edge gradient of this thread's 32 columns (residual add)
-    {
-      const bool ld = cur.own >= 0 && p.g_eout != nullptr && !(p.dbg_skip & 4);
-      const float* src = p.g_eout + (long long)(ld ? cur.own : 0) * H + m.c0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (ld) old[j] = ld_f8_hint(src + 8 * j, pol_stream);
-        else {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) old[j].v[k] = 0.f;
-        }
-      }
+      umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
+      mma_commit(&bar_dwe);
     }
     {
-      // half-warp hw handles the 4 consecutive rows 8*warp + 4*hw + i; lane q owns 8 columns
+      // half-warp hw handles the 4 consecutive rows 8*warp + 4*hw + i; lane q owns columns 4q..4q+3 and 64+4q..64+4q+3,
+      // so that one red instruction of a half-warp covers 256 contiguous bytes (full sectors)
       int curr = -1;
       float sum[8];
 #pragma unroll
@@ -361,20 +356,27 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         const int r = m.warp * 8 + 4 * hw + i;
         const int rc = __shfl_sync(0xffffffffu, cur.rcv, 4 * hw + i);
         const int sn = __shfl_sync(0xffffffffu, cur.snd, 4 * hw + i);
-        const uint4 u = *reinterpret_cast<const uint4*>(sH1 + tile_off(128, r, 8 * q));
+        const uint2 u0 = *reinterpret_cast<const uint2*>(sH1 + tile_off(128, r, 4 * q));
+        const uint2 u1 = *reinterpret_cast<const uint2*>(sH1 + tile_off(128, r, 64 + 4 * q));
         float f[8];
-        unpack8(u, f);
+        {
+          const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&u0.x));
+          const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&u0.y));
+          const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&u1.x));
+          const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&u1.y));
+          f[0] = a0.x; f[1] = a0.y; f[2] = a1.x; f[3] = a1.y; f[4] = b0.x; f[5] = b0.y; f[6] = b1.x; f[7] = b1.y;
+        }
         if (rc >= 0) {
-          float* dj = p.gP + (long long)sn * 256 + 128 + 8 * q;
+          float* dj = p.gP + (long long)sn * 256 + 128 + 4 * q;
           if (!(p.dbg_skip & 1)) {
             red_add_f4_hint(dj, make_float4(f[0], f[1], f[2], f[3]), pol_keep);
-            red_add_f4_hint(dj + 4, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
+            red_add_f4_hint(dj + 64, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
           }
           if (rc != curr) {
             if (curr >= 0 && !(p.dbg_skip & 2)) {
-              float* di = p.gP + (long long)curr * 256 + 8 * q;
+              float* di = p.gP + (long long)curr * 256 + 4 * q;
               red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
-              red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
+              red_add_f4_hint(di + 64, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
             }
             curr = rc;
 #pragma unroll
@@ -386,38 +388,11 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         }
       }
       if (curr >= 0 && !(p.dbg_skip & 2)) {
-        float* di = p.gP + (long long)curr * 256 + 8 * q;
+        float* di = p.gP + (long long)curr * 256 + 4 * q;
         red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
-        red_add_f4_hint(di + 4, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
+        red_add_f4_hint(di + 64, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
       }
     }
-    mma_wait();
-    {
-      float v[32];
-      tmem_ld32(tm_W + qoff, v);
-      tmem_ld_wait();
-      if (cur.own >= 0 && !(p.dbg_skip & 8)) {
-        float* dst = p.g_e + (long long)cur.own * H + m.c0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) v[8 * j + k] += old[j].v[k];
-          st_f8_hint(dst + 8 * j, &v[8 * j], pol_stream);
-        }
-      }
-    }
-    fence_before_sync();
-    __syncthreads();      // every thread has read the D1 accumulator
-    // dWe tile product into the working accumulator; the next tile's g is fetched under it (sG is dead)
-    if (m.tid == 0) {
-      fence_after_sync();
-      umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_dwe);
-    }
-    tl.stamp();   // 6 D1 + g_e written
-    cur = nxt;
-    if (has_next) load_g(cur);
-    nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mbar_wait(&bar_dwe, it & 1);
     fence_after_sync();
     {
@@ -428,10 +403,53 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       for (int j = 0; j < 32; ++j) dwe[j] += v[j];
     }
     fence_before_sync();
-    // no barrier here: every thread has seen bar_dwe (the product's reads of sE / sH1 are complete), and the next
-    // tile's tile_ready() orders these TMEM reads before its first product
-    tl.stamp();   // 7 next g loaded, dWe accumulated
+    __syncthreads();      // working accumulator and sE are free
+    tl.stamp();   // 6 dWe done
+    // ---- D1: dz1 We; under it: the next tile's e image (bulk) and g (coalesced loads)
+    if (m.tid == 0) {
+      mbar_wait(&bar_wA, 0);
+      fence_after_sync();
+      umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
+      mma_commit(&bar_mma);
+      if (has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);
+    }
+    const Idx done = cur;
+    cur = nxt;
+    if (has_next) load_g(cur);
+    nxt = load_idx(tile + 2 * (long long)gridDim.x);
+    mma_wait();
+    tl.stamp();   // 7 D1 done, next g loaded
+    // ---- g_e = g_eout + dz1 We: accumulator -> lin32 -> one bulk reduction into g_e (which holds g_eout), or a
+    //      bulk store when there is no upstream edge gradient
+    {
+      float v[32];
+      tmem_ld32(tm_W + qoff, v);
+      tmem_ld_wait();
+      store_row32_linear(lin32, m, v);
+    }
+    fence_before_sync();
+    tile_ready();
+    if (!(p.dbg_skip & 8)) {
+      if (p.rowmap == nullptr) {
+        if (m.tid == 0) {
+          const long long row0 = tile * TILE_ROWS;
+          const uint32_t bytes = (uint32_t)(((p.E - row0) < TILE_ROWS ? (p.E - row0) : TILE_ROWS) * 512);
+          float* dst = p.g_e + row0 * H;
+          if (p.g_eout) bulk_red_add_f32(dst, lin32, bytes, pol_stream);
+          else bulk_s2g(dst, lin32, bytes, pol_stream);
+          bulk_commit();
+        }
+      } else if (m.cq == 0 && done.own >= 0) {
+        float* dst = p.g_e + (long long)done.own * H;
+        if (p.g_eout) bulk_red_add_f32(dst, lin32 + m.row * 512, 512, pol_stream);
+        else bulk_s2g(dst, lin32 + m.row * 512, 512, pol_stream);
+        bulk_commit();
+      }
+    }
+    if (m.cq == 0) bulk_wait_read0();     // issuing threads: lin32 has been read (the next tile starts with a barrier)
+    tl.stamp();   // 8 g_e issued
   }
+  if (m.cq == 0) bulk_wait0();
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
   flush_acc_q(tm_dW4 + qoff, p.grad + GB_E_W4, 128, m);
@@ -855,7 +873,8 @@ extern "C" int64_t mgn_grad_block_floats(void) { return GB_FLOATS; }
 
 // Backward of the edge update + aggregation (autograd of layers.py:687-698, 703-719).
 // gP [N,256] is zeroed here and receives the gradients of the per-node partial products.
-extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, const float* g_eout,
+extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
+                            const float* g_eout,
                             const float* g_aggr, const void* P, const int32_t* senders, const int32_t* receivers,
                             float* g_e, float* gP, const void* packed, const float* b2, const float* b3,
                             const float* b4, const float* scale, float* grad_block, void* stream_) {
@@ -863,10 +882,11 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32
   MGN_CHECK_ARG(E >= 0 && N > 0 && gP, "edge_bwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(gP, 0, sizeof(float) * N * 256, stream));
   if (E == 0) return MGN_OK;
-  MGN_CHECK_ARG(e_in && g_aggr && P && senders && receivers && g_e && packed && b2 && b3 && b4 && scale && grad_block,
-                "edge_bwd: null pointer");
+  MGN_CHECK_ARG((e_in || e16) && g_aggr && P && senders && receivers && g_e && packed && b2 && b3 && b4 && scale &&
+                    grad_block, "edge_bwd: null pointer");
+  MGN_CHECK_ARG(g_eout == nullptr || g_eout == g_e, "edge_bwd: g_e must alias g_eout (accumulated in place)");
   EdgeBwdParams p{};
-  p.E = E; p.e_in = e_in; p.rowmap = rowmap; p.g_eout = g_eout; p.g_aggr = g_aggr; p.P = (const __half*)P;
+  p.E = E; p.e_in = e_in; p.e16 = (const __half*)e16; p.rowmap = rowmap; p.g_eout = g_eout; p.g_aggr = g_aggr; p.P = (const __half*)P;
   p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.gP = gP;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale; p.grad = grad_block;

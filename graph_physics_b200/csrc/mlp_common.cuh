@@ -206,6 +206,22 @@ __device__ __forceinline__ void cp_async16(uint32_t dst_saddr, const void* src, 
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// ------------------------------------------------------------------ bulk (TMA) shared -> global
+// Asynchronous, issued by one thread, no LSU / L1 involvement.  Completion is tracked per issuing thread in
+// bulk async-groups: commit, then wait_read (source may be overwritten) or wait_all (writes performed).
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst),
+               "r"(smem_u32(smem_src)), "r"(bytes), "l"(pol) : "memory");
+}
+// global[i] += shared[i] (fp32), performed at L2
+__device__ __forceinline__ void bulk_red_add_f32(float* gdst, const void* smem_src, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.L2::cache_hint.add.f32 [%0], [%1], %2, %3;" ::"l"(gdst),
+               "r"(smem_u32(smem_src)), "r"(bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ------------------------------------------------------------------ developer timeline (tools/timeline.py)
 // When a buffer is registered (mgn_debug_set_timeline; host globals below), thread 0 of block 0 records clock64()
 // at the phase boundaries of its tiles.  Null (the default) costs one predicated load per stamp.

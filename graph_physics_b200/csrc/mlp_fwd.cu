@@ -34,6 +34,7 @@ struct FwdParams {
   __half* save_h1;            // optional fp16 saves of the hidden activations (row = tile row index)
   __half* save_h2;
   __half* save_h3;
+  __half* e16_out;            // edge, optional: fp16 tile images of in0 (32 KB per 128-row tile) for edge_bwd
   long long* dbg;             // developer timeline (null = off)
   int dbg_cap;
 };
@@ -139,7 +140,13 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     // ---- layer 1
     if (m.tid == 0) {
       fence_after_sync();
+      const bool image = EDGE && p.e16_out != nullptr;
+      if (image) {      // the fp16 operand tile as it sits in shared memory is what edge_bwd bulk-loads
+        bulk_s2g(reinterpret_cast<uint8_t*>(p.e16_out) + (size_t)tile * TILE_BYTES, sA, TILE_BYTES, pol_stream);
+        bulk_commit();
+      }
       umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32, 128, 0, 0, 128, K0_STEPS, 0);
+      if (image) bulk_wait_read0();   // the epilogue overwrites sA: commit only after the copy has read it
       mma_commit(&mbar);
     }
     if (EDGE) {
@@ -463,7 +470,8 @@ static constexpr int P_FWD_SMEM = 3 * 32768 + TAIL_BYTES;
 extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
                             const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                             const void* packed, const float* b2, const float* b3, const float* b4,
-                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
+                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
+                            void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
@@ -477,6 +485,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
+  p.e16_out = (__half*)e16_out;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {

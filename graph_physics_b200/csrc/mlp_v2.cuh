@@ -123,6 +123,44 @@ __device__ __forceinline__ void tile_colsum_q(const uint8_t* tile, int tid, floa
   }
 }
 
+// v[32] = 32 consecutive fp32 columns (c0..) of tile row m.row -> LINEAR fp32 tile [128][128] (512-byte rows, the
+// layout bulk copies / bulk reductions to global need).  A plain row-owner store would be a 32-way bank conflict
+// (row pitch 512 B), so lane l writes its 16-byte chunk c to slot c ^ (l & 7); the registers are pre-permuted by a
+// three-stage conditional butterfly (no dynamic register indexing).  v is clobbered.
+__device__ __forceinline__ void store_row32_linear(uint8_t* tile, const Map& m, float (&v)[32]) {
+  const int k = m.lane & 7;
+#pragma unroll
+  for (int b = 1; b < 8; b <<= 1) {
+    const bool sw = (k & b) != 0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c & b) continue;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float lo = v[4 * c + i], hi = v[4 * (c ^ b) + i];
+        v[4 * c + i] = sw ? hi : lo;
+        v[4 * (c ^ b) + i] = sw ? lo : hi;
+      }
+    }
+  }
+  uint8_t* base = tile + m.row * 512 + m.c0 * 4;
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    *reinterpret_cast<float4*>(base + 16 * (c ^ k)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+}
+
+// ReLU backward in place (tile: h -> fp16(acc * [h > 0])) plus an fp32 copy of the result in a linear tile
+__device__ __forceinline__ void epi_relu_mask_q32(uint32_t taddr, uint8_t* tile, uint8_t* lin32, const Map& m) {
+  float v[32], h[32];
+  tmem_ld32(taddr, v);
+  load_row_chunk_f16(tile, 128, m.row, m.c0, h);
+  tmem_ld_wait();
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = h[j] > 0.f ? v[j] : 0.f;
+  store_row_chunk_f16(tile, 128, m.row, m.c0, v);
+  store_row32_linear(lin32, m, v);
+}
+
 // ---- coalesced movers: warp w handles tile rows 8w .. 8w+7; `grow(i)` = global row of the i-th or -1
 template <class RowFn>
 __device__ __forceinline__ void load8_f32_to_tile(uint8_t* tile, uint32_t tile_rows, uint32_t col0,

@@ -53,9 +53,11 @@ def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
 
 def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor, senders: torch.Tensor,
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
-             e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None):
+             e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None,
+             e16_out: Optional[torch.Tensor] = None):
     """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
-    used by the parity tests only -- the backward kernel recomputes them)."""
+    used by the parity tests only -- the backward kernel recomputes them).
+    e16_out: optional `e16_image(E)` buffer receiving the fp16 tile images of e_in that edge_bwd bulk-loads."""
     E = e_in.shape[0]
     s1, s2, s3 = saves if saves is not None else (None, None, None)
     if e_out is None:
@@ -64,8 +66,14 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
     L.check(L.lib().mgn_edge_fwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
                                  L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
-                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.stream()))
+                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.stream()))
     return e_out, aggr
+
+
+def e16_image(num_edges: int, device) -> torch.Tensor:
+    """Buffer for the fp16 tile images of an edge-latent version: one 32 KB swizzled 128 x 128 tile per 128 edges."""
+    tiles = (num_edges + 127) // 128
+    return torch.empty((tiles, 128 * H), dtype=torch.float16, device=device)
 
 
 def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
@@ -107,16 +115,29 @@ def split_grad_block(flat: torch.Tensor):
 
 
 def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, packed, b2, b3, b4, scale,
-             grad_block, g_e=None, gP=None):
-    """-> (g_e [E,128], gP [N,256] fp32).  g_eout may be None (zero upstream edge gradient)."""
-    E = e_in.shape[0]
-    if g_e is None:
-        g_e = torch.empty_like(e_in)
+             grad_block, g_e=None, gP=None, e16=None, inplace=False):
+    """-> (g_e [E,128], gP [N,256] fp32).  g_eout may be None (zero upstream edge gradient).
+    The kernel accumulates into the buffer that holds g_eout; unless `inplace`, that is a copy.
+    e16: the forward kernel's fp16 tile images of e_in (then e_in may be None)."""
+    E = senders.shape[0]
+    dev = g_aggr.device
+    if g_eout is not None:
+        if inplace:
+            g_e = g_eout
+        elif g_e is None:
+            g_e = g_eout.clone()
+        else:
+            g_e.copy_(g_eout)
+        g_src = g_e
+    else:
+        if g_e is None:
+            g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+        g_src = None
     if gP is None:
-        gP = torch.empty((num_nodes, 2 * H), dtype=torch.float32, device=e_in.device)
-    L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(g_eout), L.p(g_aggr),
-                                 L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(gP), L.p(packed), L.p(b2),
-                                 L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
+        gP = torch.empty((num_nodes, 2 * H), dtype=torch.float32, device=dev)
+    L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16), L.p(rowmap), L.p(g_src),
+                                 L.p(g_aggr), L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(gP), L.p(packed),
+                                 L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
     return g_e, gP
 
 

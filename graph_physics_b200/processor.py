@@ -5,8 +5,10 @@ kernels of libmgn_b200.so.
 Per step k (GraphNetBlock.forward, graphphysics/models/layers.py:667-701):
   forward   P_k = p_fwd(x_k) ; e_{k+1}, aggr_k = edge_fwd(e_k, P_k) ; x_{k+1} = node_fwd(x_k, aggr_k)
   backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, gP ; p_bwd -> g_x += ...
-Saved per step: x_k, e_k (the residual streams themselves), aggr_k, P_k (fp16) and the node
+Saved per step: x_k (the residual stream itself), e_k as the fp16 tile images the edge kernel
+built for its first product (the fp32 edge stream is NOT kept), aggr_k, P_k (fp16) and the node
 MLP's three hidden activations (fp16).  The edge MLP's hidden activations are recomputed.
+The edge-gradient stream g_e is one fp32 buffer updated in place by every edge_bwd.
 
 Edge latents run in receiver-sorted (CSR) order inside the loop; they are permuted once on
 entry and once on exit.  Gradients are multiplied by a power of two on entry to the backward
@@ -103,29 +105,30 @@ class _ProcessorFn(torch.autograd.Function):
             e = e0.detach().contiguous()
         else:
             e = e0.detach().index_select(0, csr.perm_long)
-        xs, es, aggrs, Ps, saves = [x], [e], [], [], []
+        xs, aggrs, Ps, saves, e16s = [x], [], [], [], []
+        e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))]     # the fp32 edge stream ping-pongs
         if not need_grad:   # inference: ping-pong buffers, nothing kept
             P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
             aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
             x_bufs = [torch.empty_like(x) for _ in range(min(K, 2))]
-            e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))]
         for k in range(K):
             b = prm[18 * k:18 * (k + 1)]
             if need_grad:
                 P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
                 aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
-                e_out = torch.empty_like(e)
+                e_out = e_bufs[k & 1]
                 x_out = torch.empty_like(x)
                 sv = tuple(torch.empty((N, H), dtype=torch.float16, device=dev) for _ in range(3))
+                e16 = ops.e16_image(E, dev)
             else:
-                e_out, x_out, sv = e_bufs[k & 1], x_bufs[k & 1], None
+                e_out, x_out, sv, e16 = e_bufs[k & 1], x_bufs[k & 1], None, None
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
             _timed("edge_fwd", ops.edge_fwd, e, None, P, csr.senders, csr.receivers, N, packed[k], b[3], b[5], b[7],
-                   b[8], e_out=e_out, aggr=aggr)
+                   b[8], e_out=e_out, aggr=aggr, e16_out=e16)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
                    saves=sv)
             if need_grad:
-                aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); es.append(e_out)
+                aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(e16)
             x, e = x_out, e_out
         if csr.identity:
             e_ret = e
@@ -134,15 +137,17 @@ class _ProcessorFn(torch.autograd.Function):
             e_ret.index_copy_(0, csr.perm_long, e)
         if need_grad:
             ctx.csr, ctx.K, ctx.packed, ctx.prm = csr, K, packed, prm
-            ctx.xs, ctx.es, ctx.aggrs, ctx.Ps, ctx.saves = xs, es, aggrs, Ps, saves
+            # the edge backward needs e_k only as the fp16 tile images: the fp32 versions are not kept
+            ctx.xs, ctx.e16s, ctx.aggrs, ctx.Ps, ctx.saves = xs, e16s, aggrs, Ps, saves
+            ctx.E = E
         return x, e_ret
 
     @staticmethod
     def backward(ctx, g_x, g_e):
         csr, K, packed, prm = ctx.csr, ctx.K, ctx.packed, ctx.prm
-        xs, es = ctx.xs, ctx.es
+        xs, e16s = ctx.xs, ctx.e16s
         dev = xs[0].device
-        N, E = xs[0].shape[0], es[0].shape[0]
+        N, E = xs[0].shape[0], ctx.E
         if g_x is None and g_e is None:
             return (None,) * (4 + 18 * K)
         # ---- power-of-two gradient scale (device-side, no host sync)
@@ -165,28 +170,31 @@ class _ProcessorFn(torch.autograd.Function):
         g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
         gP = torch.empty((N, 2 * H), dtype=torch.float32, device=dev)
-        ge_bufs = [torch.empty((E, H), dtype=torch.float32, device=dev) for _ in range(2 if K > 1 else 1)]
+        if ge is None:      # no upstream edge gradient: the last block writes g_e, the others accumulate into it
+            ge_buf, have_ge = torch.empty((E, H), dtype=torch.float32, device=dev), False
+        else:
+            ge_buf, have_ge = ge, True
         for k in range(K - 1, -1, -1):
             b = prm[18 * k:18 * (k + 1)]
             _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
                    g_aggr=g_aggr, dz1=dz1)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
-            ge_out = ge_bufs[k & 1] if len(ge_bufs) > 1 else ge_bufs[0]
-            _timed("edge_bwd", ops.edge_bwd, es[k], None, ge, g_aggr, ctx.Ps[k], csr.senders, csr.receivers, N,
-                   packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_out, gP=gP)
+            _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
+                   csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, gP=gP, e16=e16s[k],
+                   inplace=True)
+            have_ge = True
             _timed("p_bwd", ops.p_bwd, gP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx
-            ge = ge_out
             grads[k].mul_(inv_s)
             if GRAD_SYNC is not None:
                 GRAD_SYNC(grads[k], k)
             # release what this step saved
-            ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None
-            xs[k + 1] = None; es[k + 1] = None
+            ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None; e16s[k] = None
+            xs[k + 1] = None
         g_x0 = gx * inv_s if ctx.needs_input_grad[0] else None
         g_e0 = None
         if ctx.needs_input_grad[1]:
-            ge = ge * inv_s
+            ge = ge_buf * inv_s
             if csr.identity:
                 g_e0 = ge
             else:

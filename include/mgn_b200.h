@@ -90,11 +90,13 @@ int mgn_pack_block(const float* eW1, const float* eW2, const float* eW3, const f
 int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P, void* stream);
 /* edge update + sum aggregation at the receiver (layers.py:687-698): e_out = e_in + edge_block(...),
  * aggr [N,128] = segmented sum of the PRE-residual messages (zeroed here).  save_h* (optional,
- * [E,128] fp16) receive the hidden activations. */
+ * [E,128] fp16) receive the hidden activations.  e16_out (optional, ceil(E/128) * 32768 bytes)
+ * receives the fp16 operand-tile images of e_in that mgn_edge_bwd bulk-loads instead of e_in. */
 int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
                  const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                  const void* packed, const float* b2, const float* b3, const float* b4,
-                 const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream);
+                 const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
+                 void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
  * fp16, optional) are the hidden activations mgn_node_bwd needs. */
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
@@ -115,13 +117,15 @@ int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2,
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);
-/* edge_block + aggregation backward; recomputes the edge MLP from e_in (no edge saves).
- * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We; gP [N,256] fp32 (zeroed here) receives
- * dz1 summed by receiver (cols 0..127) and by sender (cols 128..255). g_eout may be null (= 0). */
-int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, const float* g_eout,
-                 const float* g_aggr, const void* P, const int32_t* senders, const int32_t* receivers,
-                 float* g_e, float* gP, const void* packed, const float* b2, const float* b3,
-                 const float* b4, const float* scale, float* grad_block, void* stream);
+/* edge_block + aggregation backward; recomputes the edge MLP from e16 (the forward's tile images)
+ * or, if e16 is null, from the fp32 rows e_in (no hidden-activation saves either way).
+ * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We, ACCUMULATED IN PLACE: when g_eout is not null
+ * it must be the same buffer as g_e; when null, g_e is written.  gP [N,256] fp32 (zeroed here)
+ * receives dz1 summed by receiver (cols 0..127) and by sender (cols 128..255). */
+int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
+                 const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
+                 const int32_t* receivers, float* g_e, float* gP, const void* packed, const float* b2,
+                 const float* b3, const float* b4, const float* scale, float* grad_block, void* stream);
 /* backward of mgn_p_fwd: g_x += gP [W_i ; W_j]; dW_i, dW_j, db1 into grad_block */
 int mgn_p_bwd(int64_t N, const float* gP, const float* x, float* g_x, const void* packed,
               float* grad_block, void* stream);

@@ -50,15 +50,21 @@ def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
     P = ops.p_fwd(xd, packed, eb[0])
     E = ed.shape[0]
     esaves = tuple(torch.zeros((E, 128), dtype=torch.float16, device=dev) for _ in range(3))
+    # the processor's path (CSR-ordered edges) hands the backward the forward kernel's fp16 tile images of e;
+    # with a rowmap the backward converts the fp32 rows itself
+    e16 = None if use_rowmap else ops.e16_image(E, dev)
     e_out, aggr = ops.edge_fwd(e_in, rowmap, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3], esc,
-                               saves=esaves)
+                               saves=esaves, e16_out=e16)
     saves = tuple(torch.empty((n, 128), dtype=torch.float16, device=dev) for _ in range(3))
     x_out = ops.node_fwd(xd, aggr, packed, nb[0], nb[1], nb[2], nb[3], nsc, saves=saves)
     grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
     g_x, g_aggr, dz1 = ops.node_bwd(gx1.to(dev), saves, packed, nb[3], nsc, grad)
     ops.node_wgrad1(dz1, xd, aggr, grad)
-    g_e, gP = ops.edge_bwd(e_in, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3],
-                           esc, grad)
+    ge_before = None if ge is None else ge.clone()
+    g_e, gP = ops.edge_bwd(None if e16 is not None else e_in, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, n,
+                           packed, eb[1], eb[2], eb[3], esc, grad, e16=e16)
+    if ge is not None:
+        assert torch.equal(ge, ge_before)       # not in place unless asked
     ops.p_bwd(gP, xd, g_x, packed, grad)
     torch.cuda.synchronize()
     if not use_rowmap:

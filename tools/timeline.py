@@ -28,19 +28,21 @@ e2, x2 = torch.empty_like(e), torch.empty_like(x)
 P = ops.p_fwd(x, packed, b[0])
 aggr = torch.empty(N, 128, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
-cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19
+cap = 11 * 19 + 8 if which != "edge_bwd" else 9 * 19
 ge_in = torch.randn(E, 128, device=dev)
 g_aggr = torch.randn(N, 128, device=dev)
 ge_out = torch.empty_like(e)
 gP = torch.empty(N, 256, device=dev)
 gblock = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
+e16 = ops.e16_image(E, dev)
+ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr, e16_out=e16)
 buf = torch.zeros(cap, dtype=torch.int64, device=dev)
 
 
 def run():
     if which == "edge_bwd":
-        ops.edge_bwd(e, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
-                     g_e=ge_out, gP=gP)
+        ops.edge_bwd(None, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
+                     gP=gP, e16=e16, inplace=True)
     elif which == "edge":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
     else:
@@ -59,8 +61,8 @@ t = t[t > 0]
 names = ["load", "L1 mma", "L1 epi", "L2 mma", "L2 epi", "L3 mma", "L3 epi", "L4 mma", "norm+stage", "output", "next"]
 per = 11
 if which == "edge_bwd":
-    names = ["load e", "R1", "R2+R3", "R4+norm", "D4..D2", "D1+out", "g'+dWe", "next"]
-    per = 8
+    names = ["top", "R1", "R2+R3", "R4+norm", "D4..D2", "dWe", "D1+g'", "g_e", "next"]
+    per = 9
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
