@@ -308,6 +308,22 @@ def run_b200(args):
                                     "sample": f"{args.cpu_copies} of {copies} meshes ({e_cpu} edges), 15 steps fwd+bwd, "
                                               f"fp32 oracle port, median of 2 after 1 warm-up, {t:.2f} s per pass"}
         print(json.dumps(line), flush=True)
+        if os.environ.get("MGN_BENCH_BREAKDOWN"):       # developer aid: per-kernel device time of one extra step (stderr)
+            names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "p_bwd"]
+            proc.EVENTS = {n: [] for n in names}
+            s0, e0_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            step_resident()
+            e0_.record()
+            torch.cuda.synchronize()
+            evs, proc.EVENTS = proc.EVENTS, None
+            tot = 0.0
+            for n in names:
+                d = [a.elapsed_time(b) for a, b in evs[n]]
+                tot += sum(d)
+                print(f"  {n:12s} n={len(d):3d} mean {1e3 * sum(d) / max(len(d), 1):8.1f} us  total {sum(d):7.3f} ms",
+                      file=sys.stderr)
+            print(f"  kernels {tot:.3f} ms of step {s0.elapsed_time(e0_):.3f} ms", file=sys.stderr)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

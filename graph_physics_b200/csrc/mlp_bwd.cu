@@ -83,7 +83,7 @@ struct EdgeBwdParams {
   const __half* P;          // [N,256]
   const int32_t* senders;
   const int32_t* receivers;
-  float* g_e;               // [E,128] out; holds g_eout on entry when g_eout != null (accumulated in place)
+  float* g_e;               // [E,128] out; may be the same buffer as g_eout
   float* gP;                // [N,256] fp32, zero on entry
   const __half* W;          // packed edge tiles We, W2, W3, W4
   const float* b2;
@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_dwe = tail->bar[3];
   uint64_t& bar_e = tail->bar[4];
+  uint64_t& bar_g = tail->bar[5];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
 
@@ -122,6 +123,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_dwe, 1);
     mbar_init(&bar_e, 1);
+    mbar_init(&bar_g, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -171,20 +173,16 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     return ix;
   };
   const int hw = m.lane >> 4, q = m.lane & 15;
-  // asynchronous gathers of the layer-1 partial products into swizzled staging tiles (half-warp per 256-byte row)
-  auto issue_p = [&](const Idx& ix) {        // P_i[receiver] -> sH2, P_j[sender] -> sH3
+  // P_j[sender] rows (a true gather) are staged through sH1, coalesced: half a warp per 256-byte row.  P_i[receiver]
+  // rows are read by the epilogue threads directly: consecutive tile rows share their receiver (CSR order), so a
+  // warp's request touches only a handful of distinct rows.
+  auto stage_pj = [&](const Idx& ix) {       // asynchronous (LDGSTS); cp_async_wait_all() + barrier before use
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int rc = __shfl_sync(0xffffffffu, ix.rcv, 2 * i + hw);
       const int sn = __shfl_sync(0xffffffffu, ix.snd, 2 * i + hw);
-      const uint32_t off = tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q);
-#if 0
-      cp_async16(uH2 + off, p.P + (long long)(rc >= 0 ? rc : 0) * 256 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
-      cp_async16(uH3 + off, p.P + (long long)(rc >= 0 ? sn : 0) * 256 + 128 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
-#else
-      *reinterpret_cast<uint4*>(sH2 + off) = rc >= 0 ? ld_u4_hint(p.P + (long long)rc * 256 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
-      *reinterpret_cast<uint4*>(sH3 + off) = rc >= 0 ? ld_u4_hint(p.P + (long long)sn * 256 + 128 + 8 * q, pol_keep) : make_uint4(0, 0, 0, 0);
-#endif
+      cp_async16(uH1 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q),
+                 p.P + (long long)(rc >= 0 ? sn : 0) * 256 + 128 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
     }
   };
   // g = g_eout + g_aggr[receiver] -> sG (fp16), coalesced
@@ -202,9 +200,15 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
 
+  // developer experiment: de-phase the CTAs (MGN_DEBUG_SKIP bits 16.. = delay unit in 256-cycle steps)
+  if ((p.dbg_skip >> 16) != 0) {
+    const long long t0 = clock64(), d = (long long)(blockIdx.x & 7) * ((p.dbg_skip >> 16) << 8);
+    while (clock64() - t0 < d) {}
+  }
   // ---- prologue: g and e of the first tile
   Idx cur = load_idx(blockIdx.x);
   if (p.e16 != nullptr && m.tid == 0) issue_e16(blockIdx.x);
+  stage_pj(cur);
   load_g(cur);
   Idx nxt = load_idx((long long)blockIdx.x + gridDim.x);
 
@@ -212,7 +216,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     tl.stamp();   // 0
     const bool has_next = tile + gridDim.x < num_tiles;
-    __syncthreads();      // the previous tile's g_e staging (sH2 + sH3) has been read by the bulk copy
     if (p.e16 == nullptr) {
       load8_f32_to_tile(sE, 128, 0, p.e_in, m,
                         [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, cur.dst, i); }, pol_stream);
@@ -228,20 +231,32 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
       mma_commit(&bar_mma);
     }
-    issue_p(cur);         // under the product: P_i / P_j rows -> staging
-    __syncthreads();      // the staged P rows are visible to every thread
-    mma_wait();
-    if (m.tid == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
     {
-      float v[32], a[32], b[32];
+      // under the product: P_j rows -> sH1 (staging, overwritten in place by h1), P_i rows -> registers
+      uint4 pi[4];
+      const long long go = tile * TILE_ROWS + m.row;
+      const bool ok = go < p.E;
+      const __half* si = p.P + (long long)(ok ? __ldg(p.receivers + go) : 0) * 256 + m.c0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) pi[j] = ok ? ld_u4_hint(si + 8 * j, pol_keep) : make_uint4(0, 0, 0, 0);
+      cp_async_wait_all();
+      __syncthreads();      // the staged P_j rows (issued during the previous tile) are visible to every thread
+      mma_wait();
+      if (m.tid == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
+      float v[32], b[32];
       tmem_ld32(tm_W + qoff, v);
-      load_row_chunk_f16(sH2, 128, m.row, m.c0, a);
-      load_row_chunk_f16(sH3, 128, m.row, m.c0, b);
+      load_row_chunk_f16(sH1, 128, m.row, m.c0, b);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + a[j] + b[j], 0.f);
+      for (int j = 0; j < 4; ++j) {
+        float a[8];
+        unpack8(pi[j], a);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[8 * j + k] = fmaxf(v[8 * j + k] + a[k] + b[8 * j + k], 0.f);
+      }
       store_row_chunk_f16(sH1, 128, m.row, m.c0, v);
     }
+    if (m.tid == 0) bulk_wait_read0();    // the previous tile's g_e store has read lin32 (= sH2 + sH3)
     tile_ready();
     tl.stamp();   // 2 R1 done
     // L2 prefetch of the next tile's streamed rows
@@ -337,6 +352,13 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     epi_relu_mask_q(tm_W + qoff, sH1, m);    // sH1 <- dz1
     tile_ready();
     tl.stamp();   // 5 D4..D2 done
+    // upstream rows of this tile for the residual add, straight into the (now dead) sH2 + sH3 as a linear fp32 tile
+    const long long row0 = tile * TILE_ROWS;
+    const uint32_t tile_bytes = (uint32_t)(((p.E - row0) < TILE_ROWS ? (p.E - row0) : TILE_ROWS) * 512);
+    if (m.tid == 0 && p.g_eout != nullptr && p.rowmap == nullptr) {
+      mbar_arrive_expect_tx(&bar_g, tile_bytes);
+      bulk_g2s(lin32, p.g_eout + row0 * H, tile_bytes, &bar_g);
+    }
     // ---- dWe = dz1^T e16 into the working accumulator; under it, dz1 is scattered into gP:
     //      by receiver (cols 0..127, segmented sum over the sorted receivers) and by sender (cols 128..255)
     if (m.tid == 0) {
@@ -418,38 +440,45 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (has_next) load_g(cur);
     nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mma_wait();
+    if (has_next) stage_pj(cur);          // sH1 is dead: the next tile's P_j rows, asynchronously
     tl.stamp();   // 7 D1 done, next g loaded
-    // ---- g_e = g_eout + dz1 We: accumulator -> lin32 -> one bulk reduction into g_e (which holds g_eout), or a
-    //      bulk store when there is no upstream edge gradient
-    {
+    // ---- g_e = g_eout + dz1 We
+    if (p.rowmap == nullptr) {
+      // accumulator added to the upstream tile in lin32 (or written there), then one bulk store of the tile
+      if (p.g_eout != nullptr) mbar_wait(&bar_g, it & 1);
       float v[32];
       tmem_ld32(tm_W + qoff, v);
       tmem_ld_wait();
-      store_row32_linear(lin32, m, v);
-    }
-    fence_before_sync();
-    tile_ready();
-    if (!(p.dbg_skip & 8)) {
-      if (p.rowmap == nullptr) {
-        if (m.tid == 0) {
-          const long long row0 = tile * TILE_ROWS;
-          const uint32_t bytes = (uint32_t)(((p.E - row0) < TILE_ROWS ? (p.E - row0) : TILE_ROWS) * 512);
-          float* dst = p.g_e + row0 * H;
-          if (p.g_eout) bulk_red_add_f32(dst, lin32, bytes, pol_stream);
-          else bulk_s2g(dst, lin32, bytes, pol_stream);
-          bulk_commit();
-        }
-      } else if (m.cq == 0 && done.own >= 0) {
-        float* dst = p.g_e + (long long)done.own * H;
-        if (p.g_eout) bulk_red_add_f32(dst, lin32 + m.row * 512, 512, pol_stream);
-        else bulk_s2g(dst, lin32 + m.row * 512, 512, pol_stream);
+      if (p.g_eout != nullptr) add_row32_linear(lin32, m, v);
+      else store_row32_linear(lin32, m, v);
+      tile_ready();
+      if (m.tid == 0 && !(p.dbg_skip & 8)) {
+        bulk_s2g(p.g_e + row0 * H, lin32, tile_bytes, pol_stream);
         bulk_commit();
       }
+    } else {
+      // caller's edge order: each thread moves its 32 columns of row `own` with 256-bit accesses
+      float v[32];
+      tmem_ld32(tm_W + qoff, v);
+      tmem_ld_wait();
+      if (done.own >= 0) {
+        const long long o = (long long)done.own * H + m.c0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (p.g_eout != nullptr) {
+            const f8 old = ld_f8_hint(p.g_eout + o + 8 * j, pol_stream);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[8 * j + k] += old.v[k];
+          }
+          st_f8_hint(p.g_e + o + 8 * j, &v[8 * j], pol_stream);
+        }
+      }
+      fence_before_sync();
+      __syncthreads();      // every thread has read the accumulator before the next tile's first product
     }
-    if (m.cq == 0) bulk_wait_read0();     // issuing threads: lin32 has been read (the next tile starts with a barrier)
     tl.stamp();   // 8 g_e issued
   }
-  if (m.cq == 0) bulk_wait0();
+  if (m.tid == 0) bulk_wait0();
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
   flush_acc_q(tm_dW4 + qoff, p.grad + GB_E_W4, 128, m);
@@ -884,7 +913,6 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
   if (E == 0) return MGN_OK;
   MGN_CHECK_ARG((e_in || e16) && g_aggr && P && senders && receivers && g_e && packed && b2 && b3 && b4 && scale &&
                     grad_block, "edge_bwd: null pointer");
-  MGN_CHECK_ARG(g_eout == nullptr || g_eout == g_e, "edge_bwd: g_e must alias g_eout (accumulated in place)");
   EdgeBwdParams p{};
   p.E = E; p.e_in = e_in; p.e16 = (const __half*)e16; p.rowmap = rowmap; p.g_eout = g_eout; p.g_aggr = g_aggr; p.P = (const __half*)P;
   p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.gP = gP;

@@ -148,6 +148,31 @@ __device__ __forceinline__ void store_row32_linear(uint8_t* tile, const Map& m, 
   for (int c = 0; c < 8; ++c)
     *reinterpret_cast<float4*>(base + 16 * (c ^ k)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
 }
+// same, adding to what the linear tile already holds (the upstream rows a bulk copy put there)
+__device__ __forceinline__ void add_row32_linear(uint8_t* tile, const Map& m, float (&v)[32]) {
+  const int k = m.lane & 7;
+#pragma unroll
+  for (int b = 1; b < 8; b <<= 1) {
+    const bool sw = (k & b) != 0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c & b) continue;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float lo = v[4 * c + i], hi = v[4 * (c ^ b) + i];
+        v[4 * c + i] = sw ? hi : lo;
+        v[4 * (c ^ b) + i] = sw ? lo : hi;
+      }
+    }
+  }
+  uint8_t* base = tile + m.row * 512 + m.c0 * 4;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    float4* ptr = reinterpret_cast<float4*>(base + 16 * (c ^ k));
+    const float4 o = *ptr;
+    *ptr = make_float4(o.x + v[4 * c], o.y + v[4 * c + 1], o.z + v[4 * c + 2], o.w + v[4 * c + 3]);
+  }
+}
 
 // ReLU backward in place (tile: h -> fp16(acc * [h > 0])) plus an fp32 copy of the result in a linear tile
 __device__ __forceinline__ void epi_relu_mask_q32(uint32_t taddr, uint8_t* tile, uint8_t* lin32, const Map& m) {

@@ -117,22 +117,13 @@ def split_grad_block(flat: torch.Tensor):
 def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, packed, b2, b3, b4, scale,
              grad_block, g_e=None, gP=None, e16=None, inplace=False):
     """-> (g_e [E,128], gP [N,256] fp32).  g_eout may be None (zero upstream edge gradient).
-    The kernel accumulates into the buffer that holds g_eout; unless `inplace`, that is a copy.
+    `inplace` writes g_e over g_eout (each tile is read before it is written).
     e16: the forward kernel's fp16 tile images of e_in (then e_in may be None)."""
     E = senders.shape[0]
     dev = g_aggr.device
-    if g_eout is not None:
-        if inplace:
-            g_e = g_eout
-        elif g_e is None:
-            g_e = g_eout.clone()
-        else:
-            g_e.copy_(g_eout)
-        g_src = g_e
-    else:
-        if g_e is None:
-            g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
-        g_src = None
+    if g_e is None:
+        g_e = g_eout if (inplace and g_eout is not None) else torch.empty((E, H), dtype=torch.float32, device=dev)
+    g_src = g_eout
     if gP is None:
         gP = torch.empty((num_nodes, 2 * H), dtype=torch.float32, device=dev)
     L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16), L.p(rowmap), L.p(g_src),

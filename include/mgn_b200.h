@@ -119,8 +119,8 @@ int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* agg
                     void* stream);
 /* edge_block + aggregation backward; recomputes the edge MLP from e16 (the forward's tile images)
  * or, if e16 is null, from the fp32 rows e_in (no hidden-activation saves either way).
- * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We, ACCUMULATED IN PLACE: when g_eout is not null
- * it must be the same buffer as g_e; when null, g_e is written.  gP [N,256] fp32 (zeroed here)
+ * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We (g_e may be the same buffer as g_eout; g_eout
+ * may be null = no upstream edge gradient).  gP [N,256] fp32 (zeroed here)
  * receives dz1 summed by receiver (cols 0..127) and by sender (cols 128..255). */
 int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
                  const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
