@@ -220,3 +220,26 @@ def run_processor(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Te
         raise ValueError("edge_index / edge_attr / x sizes disagree")
     flat = [t for blk in block_params for t in blk]
     return _ProcessorFn.apply(x, edge_attr, csr, len(block_params), *flat)
+
+
+class CapturedStep:
+    """Capture `fn` (a whole training or inference step: module forward, backward, in-place gradient hooks) into a
+    CUDA graph after `warmup` eager runs and replay it on every call.  Every launch of this package is stream-ordered
+    and never reads device data on the host, so a step captures as is; tensors `fn` reads must be updated in place
+    between replays, and the outputs / .grad tensors of the capture are the ones every replay writes."""
+
+    def __init__(self, fn, warmup: int = 3):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.result = fn()
+
+    def __call__(self):
+        self.graph.replay()
+        return self.result
