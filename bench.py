@@ -221,21 +221,56 @@ def run_b200(args):
         if sync is not None:
             sync.wait()
 
-    xd, ed, gd = torch.empty_like(x0), torch.empty_like(e0), torch.empty_like(gx)
+    # ---- end-to-end arm: every step's inputs come from pinned host memory and its loss goes back to the host.
+    # Two device input slots: the copy stream fills the next step's slot while the current step computes.
     loss_h = torch.empty((), dtype=torch.float32).pin_memory()
 
-    def step_e2e():
-        for p in params:
-            p.grad = None
-        xd.copy_(x0_h, non_blocking=True)
-        ed.copy_(e0_h, non_blocking=True)
-        gd.copy_(gx_h, non_blocking=True)
-        out = model(Graph(x=xd, edge_index=ei, edge_attr=ed))
-        loss = (out * gd).sum()
-        loss.backward()
-        if sync is not None:
-            sync.wait()
-        loss_h.copy_(loss.detach(), non_blocking=True)
+    class E2E:
+        def __init__(self):
+            self.copy_stream = torch.cuda.Stream()
+            self.slots = [tuple(torch.empty_like(t) for t in (x0, e0, gx)) for _ in range(2)]
+            self.ready = [torch.cuda.Event() for _ in range(2)]
+            self.free = [torch.cuda.Event() for _ in range(2)]
+            for ev_ in self.free:
+                ev_.record()
+            self.compute = [self._make(k) for k in range(2)]
+            self.i = 0
+            self._prefetch(0)
+
+        def _make(self, k):
+            xd, ed, gd = self.slots[k]
+
+            def run():
+                for p in params:
+                    p.grad = None
+                out = model(Graph(x=xd, edge_index=ei, edge_attr=ed))
+                loss = (out * gd).sum()
+                loss.backward()
+                if sync is not None:
+                    sync.wait()
+                loss_h.copy_(loss.detach(), non_blocking=True)
+            return run
+
+        def capture(self):
+            self.compute = [proc.CapturedStep(f) for f in self.compute]
+
+        def _prefetch(self, k):
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.free[k])
+                for dst, src in zip(self.slots[k], (x0_h, e0_h, gx_h)):
+                    dst.copy_(src, non_blocking=True)
+                self.ready[k].record(self.copy_stream)
+
+        def __call__(self):
+            k = self.i & 1
+            self._prefetch(k ^ 1)                       # next step's inputs: H2D under this step's kernels
+            cur = torch.cuda.current_stream()
+            cur.wait_event(self.ready[k])
+            self.compute[k]()
+            self.free[k].record(cur)
+            self.i += 1
+
+    step_e2e = E2E()
 
     def barrier():
         if world > 1:
@@ -270,7 +305,9 @@ def run_b200(args):
     step_fn, e2e_fn, graphed = step_resident, step_e2e, False
     if not args.no_cuda_graph:
         try:
-            step_fn, e2e_fn, graphed = proc.CapturedStep(step_resident), proc.CapturedStep(step_e2e), True
+            step_fn = proc.CapturedStep(step_resident)
+            step_e2e.capture()
+            graphed = True
         except Exception as exc:      # capture is an optimisation: report and fall back to eager launches
             if rank == 0:
                 print(f"bench: CUDA-graph capture failed ({type(exc).__name__}: {exc}); timing eager launches",
