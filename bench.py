@@ -211,7 +211,14 @@ def run_b200(args):
     x0_h, e0_h, gx_h = synth_inputs(N, E, rank)
     x0_h, e0_h, gx_h = x0_h.pin_memory(), e0_h.pin_memory(), gx_h.pin_memory()
     x0, e0, gx = x0_h.to(dev), e0_h.to(dev), gx_h.to(dev)
-    sync = parallel.GradSync(average=True).install() if world > 1 else None
+    # data-parallel gradient sum.  Eager launches: the per-block hook of the fused backward (asynchronous all-reduce
+    # of block k as soon as its gradient is complete, overlapping the rest of the sweep).  CUDA-graph replay: NCCL
+    # calls are kept out of the capture; one all-reduce over the flat gradient buffer follows every replay.
+    sync = parallel.GradSync(average=True).install() if (world > 1 and args.no_cuda_graph) else None
+
+    def after_replay():
+        if world > 1 and sync is None:
+            parallel.allreduce_last_grad_blocks(average=True)
 
     def step_resident():
         for p in params:
@@ -267,6 +274,7 @@ def run_b200(args):
             cur = torch.cuda.current_stream()
             cur.wait_event(self.ready[k])
             self.compute[k]()
+            after_replay()
             self.free[k].record(cur)
             self.i += 1
 
@@ -300,19 +308,27 @@ def run_b200(args):
         return ms, launches, ev
 
     # (1) eager pass: per-launch CUDA events of the dominant kernel (roofline) and the launch count
-    ms_eager, launches, ev = timed(step_resident, args.steps, args.warmup, with_events=True)
+    def step_eager():
+        step_resident()
+        after_replay()
+
+    ms_eager, launches, ev = timed(step_eager, args.steps, args.warmup, with_events=True)
     # (2) the timed region of `value`: the same step replayed from a CUDA graph (no host launch gaps)
-    step_fn, e2e_fn, graphed = step_resident, step_e2e, False
+    step_fn, e2e_fn, graphed = step_eager, step_e2e, False
     if not args.no_cuda_graph:
         try:
-            step_fn = proc.CapturedStep(step_resident)
+            cap_step = proc.CapturedStep(step_resident)
+
+            def step_fn():
+                cap_step()
+                after_replay()
             step_e2e.capture()
             graphed = True
         except Exception as exc:      # capture is an optimisation: report and fall back to eager launches
             if rank == 0:
                 print(f"bench: CUDA-graph capture failed ({type(exc).__name__}: {exc}); timing eager launches",
                       file=sys.stderr)
-            step_fn, e2e_fn, graphed = step_resident, step_e2e, False
+            step_fn, e2e_fn, graphed = step_eager, step_e2e, False
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()

@@ -35,9 +35,13 @@ class GradSync:
         loss.backward(); sync.wait()        # gradients are reduced when wait() returns
     """
 
-    def __init__(self, group=None, average: bool = True):
+    def __init__(self, group=None, average: bool = True, overlap: bool = True):
+        """overlap=True: one asynchronous all-reduce per block as soon as its gradient is complete (call wait()).
+        overlap=False: blocking all-reduces enqueued in stream order -- the form a CUDA-graph capture of the step
+        can record (work handles cannot be waited on inside a capture); wait() is then a no-op."""
         self.group = group
         self.average = average
+        self.overlap = overlap
         self.handles: List = []
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
 
@@ -46,7 +50,10 @@ class GradSync:
             return
         if self.average:
             flat.mul_(1.0 / self.world)
-        self.handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        if self.overlap:
+            self.handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        else:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
 
     def install(self):
         _proc.GRAD_SYNC = self
@@ -77,3 +84,14 @@ def allreduce_module_grads(params, group=None, average: bool = True) -> Optional
         p.grad.copy_(flat[off:off + n].view_as(p.grad))
         off += n
     return flat
+
+
+def allreduce_last_grad_blocks(group=None, average: bool = True) -> Optional[torch.Tensor]:
+    """One all-reduce over the flat [K, 181504] gradient buffer of the last fused backward sweep
+    (processor.LAST_GRAD_BLOCKS; the block parameters' .grad are views of it).  Use this after replaying a
+    CUDA-graph capture of the step, where the per-block hook cannot run collectives."""
+    buf = _proc.LAST_GRAD_BLOCKS
+    if buf is None or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return buf
+    dist.all_reduce(buf, op=dist.ReduceOp.AVG if average else dist.ReduceOp.SUM, group=group)
+    return buf

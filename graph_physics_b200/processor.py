@@ -41,6 +41,9 @@ EVENTS: Optional[dict] = None      # name -> list of (start, end) torch.cuda.Eve
 # data-parallel hook (graph_physics_b200.parallel): called as GRAD_SYNC(flat_block_grad, k) right after
 # block k's backward has been enqueued, so the all-reduce overlaps the remaining blocks' backward
 GRAD_SYNC = None
+# the [K, GRAD_BLOCK_FLOATS] buffer the last backward sweep wrote: the parameters' .grad tensors are views of it
+# (autograd keeps the views it is handed), so one collective on this buffer reduces every block's gradients
+LAST_GRAD_BLOCKS: Optional[torch.Tensor] = None
 
 
 def _timed(name, fn, *a, **kw):
@@ -165,7 +168,9 @@ class _ProcessorFn(torch.autograd.Function):
             ge = (ge * s).contiguous()
         else:
             ge = None
+        global LAST_GRAD_BLOCKS
         grads = torch.zeros((K, ops.GRAD_BLOCK_FLOATS), dtype=torch.float32, device=dev)
+        LAST_GRAD_BLOCKS = grads
         gx_new = torch.empty_like(gx)
         g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
@@ -237,7 +242,8 @@ class CapturedStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # thread_local: other threads (autograd workers, the NCCL watchdog) may keep making CUDA calls
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
             self.result = fn()
 
     def __call__(self):

@@ -133,3 +133,38 @@ def test_unsupported_shapes_raise():
     with pytest.raises(ValueError):
         b(torch.zeros(4, 64, device="cuda"), torch.zeros(2, 3, dtype=torch.long, device="cuda"),
           torch.zeros(3, 64, device="cuda"))
+
+
+def test_grads_alias_flat_buffer_and_captured_step_replays(golden_dir):
+    """The block parameters' .grad are views of processor.LAST_GRAD_BLOCKS (what the data-parallel
+    all-reduce after a CUDA-graph replay relies on), and a captured step replays to the same result."""
+    from graph_physics_b200 import processor as proc
+    from graph_physics_b200.models import EncodeProcessDecode, Graph
+    ei, n = _cyl(golden_dir)
+    torch.manual_seed(1)
+    model = EncodeProcessDecode(3, 128, 128, 128, hidden_size=128, only_processor=True).cuda()
+    x0, e0, gx = (t.cuda() for t in processor_inputs(n, ei.shape[1], 128, seed=2))
+    eid = ei.cuda()
+    params = list(model.parameters())
+
+    def step():
+        for p in params:
+            p.grad = None
+        out = model(Graph(x=x0, edge_index=eid, edge_attr=e0))
+        out.backward(gx)
+        return out
+
+    step()
+    torch.cuda.synchronize()
+    buf = proc.LAST_GRAD_BLOCKS
+    lo, hi = buf.data_ptr(), buf.data_ptr() + buf.numel() * 4
+    assert all(lo <= p.grad.data_ptr() < hi for p in params), "a parameter gradient was copied out of the flat buffer"
+    ref = [p.grad.clone() for p in params]
+    cap = proc.CapturedStep(step)
+    for p in params:
+        p.grad.zero_()
+    out = cap()
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    for p, r in zip(params, ref):      # red.add ordering differs run to run: equal to rounding
+        assert mo.rel_l2(p.grad.cpu(), r.cpu()) < 1e-5
