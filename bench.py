@@ -143,6 +143,32 @@ def cpu_oracle_run(copies, reps, warmup, threads):
     return e / t, t, e
 
 
+def eager_gpu_run(ei, n, x0, e0, gx, reps=3, warmup=1):
+    """Part of the baseline leg: the oracle port's eager PyTorch ops on the GPU with TF32 enabled
+    (graphphysics/train.py:28) -- what the reference's code path costs on this B200.  Returns ms per fwd+bwd."""
+    from oracle import mgn_oracle as mo
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        p = {k: v.to(x0.device).requires_grad_(True) for k, v in mo.init_params(STEPS_MP, hidden=H, seed=0).items()}
+        ts = []
+        for it in range(warmup + reps):
+            for v in p.values():
+                v.grad = None
+            xi, ei_ = x0.clone().requires_grad_(True), e0.clone().requires_grad_(True)
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            x, _ = mo.processor(xi, ei, ei_, p, STEPS_MP)
+            x.backward(gx)
+            e.record()
+            torch.cuda.synchronize()
+            if it >= warmup:
+                ts.append(s.elapsed_time(e))
+        return float(np.median(ts))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
 # ------------------------------------------------------------------ reference arm (CPU)
 def run_reference(args):
     """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be
@@ -376,6 +402,14 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port",
                                     "sample": f"{args.cpu_copies} of {copies} meshes ({e_cpu} edges), 15 steps fwd+bwd, "
                                               f"fp32 oracle port, median of 2 after 1 warm-up, {t:.2f} s per pass"}
+            try:
+                ms_eg = eager_gpu_run(ei, N, x0, e0, gx)
+                line["cpu_baseline"]["eager_gpu"] = {
+                    "value": E / (ms_eg * 1e-3), "unit": "edges/s", "ms_per_step": ms_eg,
+                    "what": "the same oracle port (eager PyTorch ops, TF32 matmuls as graphphysics/train.py:28) on "
+                            "this GPU, full workload, median of 3"}
+            except Exception as exc:
+                line["cpu_baseline"]["eager_gpu"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
         print(json.dumps(line), flush=True)
         if os.environ.get("MGN_BENCH_BREAKDOWN"):       # developer aid: per-kernel device time of one extra step (stderr)
             names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "p_bwd"]
