@@ -84,7 +84,7 @@ struct EdgeBwdParams {
   const int32_t* senders;
   const int32_t* receivers;
   float* g_e;               // [E,128] out; may be the same buffer as g_eout
-  float* gP;                // [N,256] fp32, zero on entry
+  __half* dz16_out;         // fp16 tile images of dz1 (32 KB per 128-row tile), gathered by p_bwd
   const __half* W;          // packed edge tiles We, W2, W3, W4
   const float* b2;
   const float* b3;
@@ -359,61 +359,14 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       mbar_arrive_expect_tx(&bar_g, tile_bytes);
       bulk_g2s(lin32, p.g_eout + row0 * H, tile_bytes, &bar_g);
     }
-    // ---- dWe = dz1^T e16 into the working accumulator; under it, dz1 is scattered into gP:
-    //      by receiver (cols 0..127, segmented sum over the sorted receivers) and by sender (cols 128..255)
+    // ---- dWe = dz1^T e16 into the working accumulator; the dz1 tile goes to global memory as it is (one bulk
+    //      copy): p_bwd sums it per receiver and per sender, so nothing is scattered with atomics here
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_dwe);
-    }
-    {
-      // half-warp hw handles the 4 consecutive rows 8*warp + 4*hw + i; lane q owns columns 4q..4q+3 and 64+4q..64+4q+3,
-      // so that one red instruction of a half-warp covers 256 contiguous bytes (full sectors)
-      int curr = -1;
-      float sum[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) sum[i] = 0.f;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int r = m.warp * 8 + 4 * hw + i;
-        const int rc = __shfl_sync(0xffffffffu, cur.rcv, 4 * hw + i);
-        const int sn = __shfl_sync(0xffffffffu, cur.snd, 4 * hw + i);
-        const uint2 u0 = *reinterpret_cast<const uint2*>(sH1 + tile_off(128, r, 4 * q));
-        const uint2 u1 = *reinterpret_cast<const uint2*>(sH1 + tile_off(128, r, 64 + 4 * q));
-        float f[8];
-        {
-          const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&u0.x));
-          const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&u0.y));
-          const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&u1.x));
-          const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&u1.y));
-          f[0] = a0.x; f[1] = a0.y; f[2] = a1.x; f[3] = a1.y; f[4] = b0.x; f[5] = b0.y; f[6] = b1.x; f[7] = b1.y;
-        }
-        if (rc >= 0) {
-          float* dj = p.gP + (long long)sn * 256 + 128 + 4 * q;
-          if (!(p.dbg_skip & 1)) {
-            red_add_f4_hint(dj, make_float4(f[0], f[1], f[2], f[3]), pol_keep);
-            red_add_f4_hint(dj + 64, make_float4(f[4], f[5], f[6], f[7]), pol_keep);
-          }
-          if (rc != curr) {
-            if (curr >= 0 && !(p.dbg_skip & 2)) {
-              float* di = p.gP + (long long)curr * 256 + 4 * q;
-              red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
-              red_add_f4_hint(di + 64, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
-            }
-            curr = rc;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) sum[k] = f[k];
-          } else {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) sum[k] += f[k];
-          }
-        }
-      }
-      if (curr >= 0 && !(p.dbg_skip & 2)) {
-        float* di = p.gP + (long long)curr * 256 + 4 * q;
-        red_add_f4_hint(di, make_float4(sum[0], sum[1], sum[2], sum[3]), pol_keep);
-        red_add_f4_hint(di + 64, make_float4(sum[4], sum[5], sum[6], sum[7]), pol_keep);
-      }
+      bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
+      bulk_commit();
     }
     mbar_wait(&bar_dwe, it & 1);
     fence_after_sync();
@@ -432,6 +385,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       mbar_wait(&bar_wA, 0);
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
+      bulk_wait_read0();    // the dz1 image copy has read sH1: whoever sees this product complete may overwrite it
       mma_commit(&bar_mma);
       if (has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);
     }
@@ -721,10 +675,69 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
 }
 
 // ===================================================================================== P backward
-// gP [N,256] fp32 = [dP_i | dP_j]:  g_x += gP [W_i ; W_j] ; dW_i = dP_i^T x ; dW_j = dP_j^T x ; db1 = colsum dP_i
+// dP [N,256] fp16 = [dP_i | dP_j] is GATHERED (dp_gather_kernel) from the fp16 tile images of dz1 that edge_bwd
+// wrote -- no atomics, fixed summation order: dP_i[n] = sum of dz1 over the edges n receives (contiguous CSR
+// positions), dP_j[n] = sum over the edges n sends (positions listed by the sender-sorted index).  Then
+//   g_x += dP [W_i ; W_j] ; dW_i = dP_i^T x ; dW_j = dP_j^T x ; db1 = colsum dP_i          (p_bwd_kernel)
+struct DpGatherParams {
+  long long N;
+  const __half* dz16;       // tile images of dz1: tile t = 32 KB swizzled 128 x 128 fp16 (CSR positions 128t..)
+  const int32_t* rowptr;    // [N+1] receiver CSR
+  const int32_t* rowptr_s;  // [N+1] sender-sorted lists
+  const int32_t* out_pos;   // [E] CSR positions sorted by sender
+  __half* dP;               // [N,256]
+};
+
+// 16-byte chunk `l` (columns 8l..8l+7) of row `pos` of the dz1 images
+__device__ __forceinline__ uint4 ld_dz16_chunk(const __half* img, int pos, int l) {
+  const uint32_t r = (uint32_t)pos & 127u;
+  const size_t off = (size_t)(pos >> 7) * 32768 + (size_t)(l >> 3) * 16384 + r * 128 + (((uint32_t)l & 7u) ^ (r & 7u)) * 16;
+  return ldg_u4(reinterpret_cast<const uint8_t*>(img) + off);
+}
+
+// One half-warp per (node, side): a plain high-occupancy streaming kernel (no shared memory), fp32 sums, 4 rows in flight
+__global__ void __launch_bounds__(256) dp_gather_kernel(const DpGatherParams p) {
+  const int l = threadIdx.x & 15;
+  const long long ntask = 2 * p.N;
+  for (long long task = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4; task < ntask;
+       task += ((long long)gridDim.x * blockDim.x) >> 4) {
+    const long long n = task >> 1;
+    const int side = (int)(task & 1);
+    const int32_t* rp = side ? p.rowptr_s : p.rowptr;
+    const int beg = __ldg(rp + n), end = __ldg(rp + n + 1);
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll 1
+    for (int j = beg; j < end; j += 4) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (j + u < end) {
+          const int pos = side ? __ldg(p.out_pos + j + u) : j + u;
+          v[u] = ld_dz16_chunk(p.dz16, pos, l);
+        } else {
+          v[u] = make_uint4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8(v[u], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      }
+    }
+    uint4 pk;
+    pk.x = pack_h2(acc[0], acc[1]); pk.y = pack_h2(acc[2], acc[3]);
+    pk.z = pack_h2(acc[4], acc[5]); pk.w = pack_h2(acc[6], acc[7]);
+    *reinterpret_cast<uint4*>(p.dP + n * 256 + side * 128 + 8 * l) = pk;
+  }
+}
+
 struct PBwdParams {
   long long N;
-  const float* gP;
+  const __half* dP;         // [N,256] fp16
   const float* x;
   float* g_x;               // read-modify-write
   const __half* Wcat;       // [256 x 128] panel tile (64 KB)
@@ -766,11 +779,19 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
     auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
-    // gP rows are 256 floats: the two 128-column halves of a row are rows 2g, 2g+1 of a [2N,128] view
-    load8_f32_to_tile(sGP, 128, 0, p.gP, m, [&](int i) -> long long { const long long g = rf(i); return g < 0 ? -1 : 2 * g; },
-                      pol_once);
-    load8_f32_to_tile(sGP, 128, 128, p.gP, m,
-                      [&](int i) -> long long { const long long g = rf(i); return g < 0 ? -1 : 2 * g + 1; }, pol_once);
+    // ---- dP rows (512 bytes of fp16) -> operand tile: half a warp per 256-byte half row
+    {
+      const int hw = m.lane >> 4, q = m.lane & 15;
+      uint4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const long long g = rf(i);
+        v[i] = g >= 0 ? ld_u4_hint(p.dP + g * 256 + hw * 128 + 8 * q, pol_once) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint4*>(sGP + tile_off(128, m.warp * 8 + i, hw * 128 + 8 * q)) = v[i];
+    }
     load8_f32_to_tile(sX, 128, 0, p.x, m, rf, pol_keep);
     fence_async_smem();
     fence_before_sync();
@@ -901,21 +922,20 @@ static constexpr int NODE_WGRAD1_SMEM = 6 * SLOT + TAIL_BYTES;
 extern "C" int64_t mgn_grad_block_floats(void) { return GB_FLOATS; }
 
 // Backward of the edge update + aggregation (autograd of layers.py:687-698, 703-719).
-// gP [N,256] is zeroed here and receives the gradients of the per-node partial products.
+// dz16_out receives dz1 (the gradient at the first layer's pre-activation) as fp16 tile images for mgn_p_bwd.
 extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
-                            const float* g_eout,
-                            const float* g_aggr, const void* P, const int32_t* senders, const int32_t* receivers,
-                            float* g_e, float* gP, const void* packed, const float* b2, const float* b3,
-                            const float* b4, const float* scale, float* grad_block, void* stream_) {
+                            const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
+                            const int32_t* receivers, float* g_e, void* dz16_out, const void* packed,
+                            const float* b2, const float* b3, const float* b4, const float* scale,
+                            float* grad_block, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  MGN_CHECK_ARG(E >= 0 && N > 0 && gP, "edge_bwd: bad sizes");
-  MGN_CUDA(cudaMemsetAsync(gP, 0, sizeof(float) * N * 256, stream));
+  MGN_CHECK_ARG(E >= 0 && N > 0, "edge_bwd: bad sizes");
   if (E == 0) return MGN_OK;
-  MGN_CHECK_ARG((e_in || e16) && g_aggr && P && senders && receivers && g_e && packed && b2 && b3 && b4 && scale &&
-                    grad_block, "edge_bwd: null pointer");
+  MGN_CHECK_ARG((e_in || e16) && g_aggr && P && senders && receivers && g_e && dz16_out && packed && b2 && b3 && b4 &&
+                    scale && grad_block, "edge_bwd: null pointer");
   EdgeBwdParams p{};
   p.E = E; p.e_in = e_in; p.e16 = (const __half*)e16; p.rowmap = rowmap; p.g_eout = g_eout; p.g_aggr = g_aggr; p.P = (const __half*)P;
-  p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.gP = gP;
+  p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.dz16_out = (__half*)dz16_out;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale; p.grad = grad_block;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
@@ -955,12 +975,26 @@ extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, cons
   return MGN_OK;
 }
 
-// Backward of the per-node partial products (mgn_p_fwd): g_x += gP [W_i ; W_j], dW_i, dW_j, db1.
-extern "C" int mgn_p_bwd(int64_t N, const float* gP, const float* x, float* g_x, const void* packed,
+// Backward of the gathers x[col], x[row]: dP [N,256] fp16 = [sum of dz1 over received edges | over sent edges] from
+// edge_bwd's dz1 tile images, through the receiver CSR and the sender-sorted lists.  Fixed order, no atomics.
+extern "C" int mgn_dp_gather(int64_t N, const void* dz16, const int32_t* rowptr, const int32_t* rowptr_s,
+                             const int32_t* out_pos, void* dP, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(N > 0 && dz16 && rowptr && rowptr_s && out_pos && dP, "dp_gather: bad args");
+  DpGatherParams p{N, (const __half*)dz16, rowptr, rowptr_s, out_pos, (__half*)dP};
+  const int64_t blocks = ceil_div64(2 * N * 16, 256);
+  const int grid = (int)std::min<int64_t>(blocks, (int64_t)mgn_num_sms() * 8);
+  dp_gather_kernel<<<grid, 256, 0, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+// Backward of the per-node partial products (mgn_p_fwd): g_x += dP [W_i ; W_j], dW_i, dW_j, db1.
+extern "C" int mgn_p_bwd(int64_t N, const void* dP, const float* x, float* g_x, const void* packed,
                          float* grad_block, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  MGN_CHECK_ARG(N > 0 && gP && x && g_x && packed && grad_block, "p_bwd: bad args");
-  PBwdParams p{N, gP, x, g_x,
+  MGN_CHECK_ARG(N > 0 && dP && x && g_x && packed && grad_block, "p_bwd: bad args");
+  PBwdParams p{N, (const __half*)dP, x, g_x,
                reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_WCAT), grad_block};
   static bool attr = false;
   if (!attr) {

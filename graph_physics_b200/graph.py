@@ -208,6 +208,18 @@ class CSRGraph:
             object.__setattr__(self, "_perm_long", pl)
         return pl
 
+    @property
+    def by_sender(self):
+        """(rowptr_s [N+1] int32, out_pos [E] int32): for node n, out_pos[rowptr_s[n]:rowptr_s[n+1]] are the
+        CSR positions of the edges n SENDS (the gather lists of the deterministic backward of x[row])."""
+        bs = getattr(self, "_by_sender", None)
+        if bs is None:
+            flipped = torch.stack([self.receivers.long(), self.senders.long()])   # sort key = sender
+            c2 = build_csr(flipped, self.num_nodes)
+            bs = (c2.rowptr, c2.perm)
+            object.__setattr__(self, "_by_sender", bs)
+        return bs
+
 
 def build_csr(edge_index: torch.Tensor, num_nodes: int) -> CSRGraph:
     L.require_device(edge_index)

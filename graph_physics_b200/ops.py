@@ -115,8 +115,8 @@ def split_grad_block(flat: torch.Tensor):
 
 
 def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, packed, b2, b3, b4, scale,
-             grad_block, g_e=None, gP=None, e16=None, inplace=False):
-    """-> (g_e [E,128], gP [N,256] fp32).  g_eout may be None (zero upstream edge gradient).
+             grad_block, g_e=None, dz16=None, e16=None, inplace=False):
+    """-> (g_e [E,128], dz16: fp16 tile images of dz1 for p_bwd).  g_eout may be None (zero upstream edge gradient).
     `inplace` writes g_e over g_eout (each tile is read before it is written).
     e16: the forward kernel's fp16 tile images of e_in (then e_in may be None)."""
     E = senders.shape[0]
@@ -124,12 +124,12 @@ def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, pac
     if g_e is None:
         g_e = g_eout if (inplace and g_eout is not None) else torch.empty((E, H), dtype=torch.float32, device=dev)
     g_src = g_eout
-    if gP is None:
-        gP = torch.empty((num_nodes, 2 * H), dtype=torch.float32, device=dev)
+    if dz16 is None:
+        dz16 = e16_image(E, dev)
     L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16), L.p(rowmap), L.p(g_src),
-                                 L.p(g_aggr), L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(gP), L.p(packed),
+                                 L.p(g_aggr), L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(dz16), L.p(packed),
                                  L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
-    return g_e, gP
+    return g_e, dz16
 
 
 def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None):
@@ -147,9 +147,20 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
     return g_x, g_aggr, dz1
 
 
-def p_bwd(gP, x, g_x, packed, grad_block):
-    """g_x += gP [W_i ; W_j] (in place); dW_i, dW_j, db1 into grad_block."""
-    L.check(L.lib().mgn_p_bwd(L.i64(x.shape[0]), L.p(gP), L.p(x), L.p(g_x), L.p(packed), L.p(grad_block),
+def dp_gather(dz16, csr, dP=None):
+    """dP [N,256] fp16 = [sum of dz1 over received edges | over sent edges], gathered from edge_bwd's tile images in
+    a fixed order (no atomics).  csr: graph.CSRGraph."""
+    rowptr_s, out_pos = csr.by_sender
+    if dP is None:
+        dP = torch.empty((csr.num_nodes, 2 * H), dtype=torch.float16, device=dz16.device)
+    L.check(L.lib().mgn_dp_gather(L.i64(csr.num_nodes), L.p(dz16), L.p(csr.rowptr), L.p(rowptr_s), L.p(out_pos),
+                                  L.p(dP), L.stream()))
+    return dP
+
+
+def p_bwd(dP, x, g_x, packed, grad_block):
+    """g_x += dP [W_i ; W_j] (in place); dW_i, dW_j, db1 into grad_block."""
+    L.check(L.lib().mgn_p_bwd(L.i64(x.shape[0]), L.p(dP), L.p(x), L.p(g_x), L.p(packed), L.p(grad_block),
                               L.stream()))
     return g_x
 

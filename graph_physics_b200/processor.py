@@ -4,7 +4,7 @@ kernels of libmgn_b200.so.
 
 Per step k (GraphNetBlock.forward, graphphysics/models/layers.py:667-701):
   forward   P_k = p_fwd(x_k) ; e_{k+1}, aggr_k = edge_fwd(e_k, P_k) ; x_{k+1} = node_fwd(x_k, aggr_k)
-  backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, gP ; p_bwd -> g_x += ...
+  backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, dz1 images ; p_bwd -> g_x += ...
 Saved per step: x_k (the residual stream itself), e_k as the fp16 tile images the edge kernel
 built for its first product (the fp32 edge stream is NOT kept), aggr_k, P_k (fp16) and the node
 MLP's three hidden activations (fp16).  The edge MLP's hidden activations are recomputed.
@@ -174,7 +174,9 @@ class _ProcessorFn(torch.autograd.Function):
         gx_new = torch.empty_like(gx)
         g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
-        gP = torch.empty((N, 2 * H), dtype=torch.float32, device=dev)
+        dz16 = ops.e16_image(E, dev)       # dz1 of the current step: written by edge_bwd, gathered by p_bwd
+        dP = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
+        csr.by_sender                      # (built once per topology)
         if ge is None:      # no upstream edge gradient: the last block writes g_e, the others accumulate into it
             ge_buf, have_ge = torch.empty((E, H), dtype=torch.float32, device=dev), False
         else:
@@ -185,10 +187,11 @@ class _ProcessorFn(torch.autograd.Function):
                    g_aggr=g_aggr, dz1=dz1)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
             _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
-                   csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, gP=gP, e16=e16s[k],
+                   csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
                    inplace=True)
             have_ge = True
-            _timed("p_bwd", ops.p_bwd, gP, xs[k], gx_new, packed[k], grads[k])
+            _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
+            _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx
             grads[k].mul_(inv_s)
             if GRAD_SYNC is not None:

@@ -120,14 +120,21 @@ int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* agg
 /* edge_block + aggregation backward; recomputes the edge MLP from e16 (the forward's tile images)
  * or, if e16 is null, from the fp32 rows e_in (no hidden-activation saves either way).
  * g = g_eout + g_aggr[receiver]; g_e = g_eout + dz1 We (g_e may be the same buffer as g_eout; g_eout
- * may be null = no upstream edge gradient).  gP [N,256] fp32 (zeroed here)
- * receives dz1 summed by receiver (cols 0..127) and by sender (cols 128..255). */
+ * may be null = no upstream edge gradient).  dz16_out (ceil(E/128) * 32768 bytes) receives dz1, the
+ * gradient at the first layer's pre-activation, as fp16 tile images in CSR order: the backward of the
+ * gathers x[col], x[row] (layers.py:687-691) is finished by mgn_p_bwd without atomics. */
 int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
                  const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
-                 const int32_t* receivers, float* g_e, float* gP, const void* packed, const float* b2,
+                 const int32_t* receivers, float* g_e, void* dz16_out, const void* packed, const float* b2,
                  const float* b3, const float* b4, const float* scale, float* grad_block, void* stream);
-/* backward of mgn_p_fwd: g_x += gP [W_i ; W_j]; dW_i, dW_j, db1 into grad_block */
-int mgn_p_bwd(int64_t N, const float* gP, const float* x, float* g_x, const void* packed,
+/* backward of the two gathers: dP [N,256] fp16; dP[n, :128] = sum of dz1 over CSR positions
+ * rowptr[n]..rowptr[n+1] (edges n receives), dP[n, 128:] = sum over out_pos[rowptr_s[n]..rowptr_s[n+1]]
+ * (edges n sends; lists = mgn_build_csr of the flipped CSR-ordered pairs).  fp32 sums in a fixed
+ * order: bitwise reproducible, no atomics. */
+int mgn_dp_gather(int64_t N, const void* dz16, const int32_t* rowptr, const int32_t* rowptr_s,
+                  const int32_t* out_pos, void* dP, void* stream);
+/* backward of mgn_p_fwd: g_x += dP [W_i ; W_j]; dW_i, dW_j, db1 into grad_block */
+int mgn_p_bwd(int64_t N, const void* dP, const float* x, float* g_x, const void* packed,
               float* grad_block, void* stream);
 
 /* ------------------------------------------------------------------ developer hooks */

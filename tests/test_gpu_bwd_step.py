@@ -61,11 +61,11 @@ def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
     g_x, g_aggr, dz1 = ops.node_bwd(gx1.to(dev), saves, packed, nb[3], nsc, grad)
     ops.node_wgrad1(dz1, xd, aggr, grad)
     ge_before = None if ge is None else ge.clone()
-    g_e, gP = ops.edge_bwd(None if e16 is not None else e_in, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, n,
+    g_e, dz16 = ops.edge_bwd(None if e16 is not None else e_in, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, n,
                            packed, eb[1], eb[2], eb[3], esc, grad, e16=e16)
     if ge is not None:
         assert torch.equal(ge, ge_before)       # not in place unless asked
-    ops.p_bwd(gP, xd, g_x, packed, grad)
+    ops.p_bwd(ops.dp_gather(dz16, csr), xd, g_x, packed, grad)
     torch.cuda.synchronize()
     if not use_rowmap:
         back = torch.empty_like(g_e)

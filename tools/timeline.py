@@ -32,7 +32,7 @@ cap = 11 * 19 + 8 if which != "edge_bwd" else 9 * 19
 ge_in = torch.randn(E, 128, device=dev)
 g_aggr = torch.randn(N, 128, device=dev)
 ge_out = torch.empty_like(e)
-gP = torch.empty(N, 256, device=dev)
+dz16 = ops.e16_image(E, dev)
 gblock = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
 e16 = ops.e16_image(E, dev)
 ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr, e16_out=e16)
@@ -42,7 +42,7 @@ buf = torch.zeros(cap, dtype=torch.int64, device=dev)
 def run():
     if which == "edge_bwd":
         ops.edge_bwd(None, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
-                     gP=gP, e16=e16, inplace=True)
+                     dz16=dz16, e16=e16, inplace=True)
     elif which == "edge":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
     else:
