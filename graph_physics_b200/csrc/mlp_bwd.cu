@@ -365,8 +365,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
       mma_commit(&bar_dwe);
-      bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
-      bulk_commit();
+      if (!(p.dbg_skip & 64)) {
+        bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
+        bulk_commit();
+      }
     }
     mbar_wait(&bar_dwe, it & 1);
     fence_after_sync();
@@ -391,7 +393,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     const Idx done = cur;
     cur = nxt;
-    if (has_next) load_g(cur);
+    if (has_next && !(p.dbg_skip & 32)) load_g(cur);
     nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mma_wait();
     if (has_next) stage_pj(cur);          // sH1 is dead: the next tile's P_j rows, asynchronously

@@ -205,17 +205,21 @@ __device__ __forceinline__ void load8_f32_to_tile(uint8_t* tile, uint32_t tile_r
     *reinterpret_cast<uint2*>(tile + tile_off(tile_rows, m.warp * 8 + i, col0 + 4 * m.lane)) = pk;
   }
 }
-// tile row <- fp16(a[ga(i)] + b[gb(i)])
+// tile row <- fp16(a[ga(i)] + b[gb(i)]).  Consecutive rows that name the same b row (edges of one receiver, CSR
+// order) reuse the registers of the previous row instead of fetching it again (warp-uniform test).
 template <class RowFnA, class RowFnB>
 __device__ __forceinline__ void load8_sum2_to_tile(uint8_t* tile, const float* __restrict__ a,
                                                    const float* __restrict__ b, const Map& m, RowFnA ga, RowFnB gb,
                                                    uint64_t pol_a, uint64_t pol_b) {
   float4 va[8], vb[8];
+  long long prev = -2;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const long long ia = ga(i), ib = gb(i);
     va[i] = (ia >= 0) ? ld_f4_hint(a + ia * H + 4 * m.lane, pol_a) : make_float4(0.f, 0.f, 0.f, 0.f);
-    vb[i] = (ib >= 0) ? ld_f4_hint(b + ib * H + 4 * m.lane, pol_b) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i > 0 && ib == prev) vb[i] = vb[i - 1];
+    else vb[i] = (ib >= 0) ? ld_f4_hint(b + ib * H + 4 * m.lane, pol_b) : make_float4(0.f, 0.f, 0.f, 0.f);
+    prev = ib;
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
