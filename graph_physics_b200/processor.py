@@ -20,6 +20,7 @@ sm_100 device and the library is built.
 """
 from __future__ import annotations
 
+import weakref
 from typing import List, Optional, Sequence
 
 import torch
@@ -63,18 +64,20 @@ _csr_cache: dict = {}
 
 
 def csr_for(edge_index: torch.Tensor, num_nodes: int) -> G.CSRGraph:
-    """Receiver-sorted CSR of `edge_index`, cached on the tensor's identity and version (the
-    topology is constant along a trajectory; the reference caches K-hop edges the same way,
-    graphphysics/dataset/dataset.py:149-168)."""
-    key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, int(num_nodes),
-           edge_index.device.index)
+    """Receiver-sorted CSR of `edge_index`, cached per tensor OBJECT (weak reference + version counter): the topology
+    is constant along a trajectory and callers keep passing the same tensor (the reference caches K-hop edges the
+    same way, graphphysics/dataset/dataset.py:149-168).  A different tensor object is never a hit, even if the
+    allocator handed it the address of a freed one."""
+    key = id(edge_index)
     hit = _csr_cache.get(key)
     if hit is not None:
-        return hit
+        ref, version, n, csr = hit
+        if ref() is edge_index and version == edge_index._version and n == int(num_nodes):
+            return csr
     if len(_csr_cache) > 16:
         _csr_cache.clear()
     csr = G.build_csr(edge_index, num_nodes)
-    _csr_cache[key] = csr
+    _csr_cache[key] = (weakref.ref(edge_index), edge_index._version, int(num_nodes), csr)
     return csr
 
 
@@ -176,7 +179,10 @@ class _ProcessorFn(torch.autograd.Function):
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
         dz16 = ops.e16_image(E, dev)       # dz1 of the current step: written by edge_bwd, gathered by p_bwd
         dP = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
-        csr.by_sender                      # (built once per topology)
+        if E > 0:
+            csr.by_sender                  # (built once per topology)
+        else:
+            dP.zero_()                     # no edges: nothing flows back through the gathers
         if ge is None:      # no upstream edge gradient: the last block writes g_e, the others accumulate into it
             ge_buf, have_ge = torch.empty((E, H), dtype=torch.float32, device=dev), False
         else:
@@ -186,11 +192,12 @@ class _ProcessorFn(torch.autograd.Function):
             _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
                    g_aggr=g_aggr, dz1=dz1)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
-            _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
-                   csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
-                   inplace=True)
-            have_ge = True
-            _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
+            if E > 0:
+                _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
+                       csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
+                       inplace=True)
+                have_ge = True
+                _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
             _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx
             grads[k].mul_(inv_s)

@@ -168,3 +168,22 @@ def test_grads_alias_flat_buffer_and_captured_step_replays(golden_dir):
     assert torch.isfinite(out).all()
     for p, r in zip(params, ref):      # red.add ordering differs run to run: equal to rounding
         assert mo.rel_l2(p.grad.cpu(), r.cpu()) < 1e-5
+
+
+def test_csr_cache_is_per_tensor_object(golden_dir):
+    """A new edge_index tensor that lands on the address of a freed one must not reuse its CSR."""
+    from graph_physics_b200 import processor as proc
+    ei, n = _cyl(golden_dir)
+    a = ei.cuda()
+    c1 = proc.csr_for(a, n)
+    assert proc.csr_for(a, n) is c1                    # same object, same version: hit
+    ptr = a.data_ptr()
+    del a
+    perm = torch.randperm(ei.shape[1], generator=torch.Generator().manual_seed(0))
+    b = ei[:, perm].cuda()                             # usually the same address as the freed tensor
+    c2 = proc.csr_for(b, n)
+    assert c2 is not c1
+    assert torch.equal(c2.perm.long().cpu(), torch.sort(ei[1, perm], stable=True).indices)
+    b[0, 0] = b[0, 0]                                  # in-place write bumps the version: rebuilt
+    assert proc.csr_for(b, n) is not c2
+    del ptr
