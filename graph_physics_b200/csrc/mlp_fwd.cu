@@ -35,6 +35,9 @@ struct FwdParams {
   __half* save_h2;
   __half* save_h3;
   __half* e16_out;            // edge, optional: fp16 tile images of in0 (32 KB per 128-row tile) for edge_bwd
+  const __half* e16_in;       // edge, optional: tile images of in0 made by the previous step (then in0 is only read
+                              // for the residual and the operand tile arrives by bulk copy, one tile ahead)
+  __half* e16_next;           // edge, optional: tile images of the OUTPUT rows (the next step's e16_in)
   long long* dbg;             // developer timeline (null = off)
   int dbg_cap;
 };
@@ -55,10 +58,13 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   Tail2* tail = reinterpret_cast<Tail2*>(smem + W_BYTES + A_BYTES + (EDGE ? 2 * TILE_BYTES : 0));
   uint64_t& wbar = tail->bar[0];
   uint64_t& mbar = tail->bar[1];
+  uint64_t& bar_in = tail->bar[2];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
+  const bool img_in = EDGE && p.e16_in != nullptr;
 
   if (m.tid == 0) {
+    mbar_init(&bar_in, 1);
     mbar_init(&wbar, 1);
     mbar_init(&mbar, 1);
     mbar_init_fence();
@@ -95,9 +101,9 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   const uint64_t pol_keep = policy_evict_last();      // per-node arrays gathered by every edge
   // Index registers run one tile ahead (the loads for tile i+1 are issued during tile i), so no
   // thread waits on an index before it can issue its tile's row loads.
-  struct Idx { int rcv_o, snd_o, dst_c, rcv_c; };
+  struct Idx { int rcv_o, snd_o, dst_c, rcv_c, snd_c; };
   auto load_idx = [&](long long tile_) -> Idx {
-    Idx ix{0, 0, -1, -1};
+    Idx ix{0, 0, -1, -1, -1};
     if (tile_ >= num_tiles) return ix;
     const long long r0 = tile_ * TILE_ROWS;
     if (EDGE && r0 + m.row < p.M) {
@@ -107,15 +113,24 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     const long long g = r0 + m.warp * 8 + (m.lane & 7);
     if (g < p.M) {
       ix.dst_c = (EDGE && p.rowmap) ? __ldg(p.rowmap + g) : (int)g;
-      if (EDGE) ix.rcv_c = __ldg(p.receivers + g);
+      if (EDGE) {
+        ix.rcv_c = __ldg(p.receivers + g);
+        ix.snd_c = __ldg(p.senders + g);
+      }
     }
     return ix;
   };
   Idx nxt = load_idx(blockIdx.x);
+  auto issue_image = [&](long long tile_) {      // thread 0: operand tile of `tile_` by bulk copy
+    mbar_arrive_expect_tx(&bar_in, TILE_BYTES);
+    bulk_g2s(sA, reinterpret_cast<const uint8_t*>(p.e16_in) + (size_t)tile_ * TILE_BYTES, TILE_BYTES, &bar_in);
+  };
+  if (img_in && m.tid == 0 && (long long)blockIdx.x < num_tiles) issue_image(blockIdx.x);
+  uint32_t it = 0;
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
 
-  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     tl.stamp();   // 0 tile start
     const long long row0 = tile * TILE_ROWS;
     const long long grow = row0 + m.row;          // epilogue (row-owner) mapping
@@ -123,14 +138,28 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     const Idx cur = nxt;
     const int rcv_o = cur.rcv_o, snd_o = cur.snd_o, dst_c = cur.dst_c, rcv_c = cur.rcv_c;
 
-    // ---- load phase: fp32 rows -> fp16 operand tile
-    {
+    // P_j[sender] rows (a true gather): asynchronous copies into the idle staging area, half a warp per 256-byte
+    // row; they land while the operand tile is loaded and the layer-1 product runs.  P_i[receiver] rows are read by
+    // the epilogue threads directly (consecutive tile rows share their receiver).
+    if (EDGE) {
+      const int hw = m.lane >> 4, q = m.lane & 15;
+      const uint32_t st_u32 = smem_u32(stage);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int rc = __shfl_sync(0xffffffffu, cur.rcv_c, 2 * i + hw);
+        const int sn = __shfl_sync(0xffffffffu, cur.snd_c, 2 * i + hw);
+        cp_async16(st_u32 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q),
+                   p.P + (long long)(rc >= 0 ? sn : 0) * 256 + 128 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
+      }
+    }
+    // ---- load phase: fp32 rows -> fp16 operand tile (skipped when the previous step left the tile image)
+    if (!img_in) {
       auto rf = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, dst_c, i); };
       load8_f32_to_tile(sA, 128, 0, p.in0, m, rf, pol_stream);
       if (!EDGE) load8_f32_to_tile(sA, 128, 128, p.in1, m, rf, pol_stream);
     }
     nxt = load_idx(tile + gridDim.x);
-    tile_ready();
+    if (!img_in) tile_ready();
     if (!w_ready) {
       mbar_wait(&wbar, 0);
       w_ready = true;
@@ -139,8 +168,9 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
 
     // ---- layer 1
     if (m.tid == 0) {
+      if (img_in) mbar_wait(&bar_in, it & 1);
       fence_after_sync();
-      const bool image = EDGE && p.e16_out != nullptr;
+      const bool image = EDGE && p.e16_out != nullptr && !img_in;
       if (image) {      // the fp16 operand tile as it sits in shared memory is what edge_bwd bulk-loads
         bulk_s2g(reinterpret_cast<uint8_t*>(p.e16_out) + (size_t)tile * TILE_BYTES, sA, TILE_BYTES, pol_stream);
         bulk_commit();
@@ -150,28 +180,29 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       mma_commit(&mbar);
     }
     if (EDGE) {
-      uint4 pi[4], pj[4];
+      uint4 pi[4];
       if (rvalid) {
         const __half* Pi = p.P + (long long)rcv_o * 256 + m.c0;
-        const __half* Pj = p.P + (long long)snd_o * 256 + 128 + m.c0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { pi[j] = ld_u4_hint(Pi + 8 * j, pol_keep); pj[j] = ld_u4_hint(Pj + 8 * j, pol_keep); }
+        for (int j = 0; j < 4; ++j) pi[j] = ld_u4_hint(Pi + 8 * j, pol_keep);
       } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { pi[j] = make_uint4(0, 0, 0, 0); pj[j] = pi[j]; }
+        for (int j = 0; j < 4; ++j) pi[j] = make_uint4(0, 0, 0, 0);
       }
+      cp_async_wait_all();
+      __syncthreads();      // the staged P_j rows are visible to every thread
       mma_wait();
       tl.stamp();   // 2 layer-1 product done
-      float v[32];
+      float v[32], b[32];
       tmem_ld32(taddr, v);
+      load_row_chunk_f16(stage, 128, m.row, m.c0, b);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float a[8], b[8];
+        float a[8];
         unpack8(pi[j], a);
-        unpack8(pj[j], b);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
+        for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[8 * j + i], 0.f);
       }
       store_row_chunk_f16(sA, 128, m.row, m.c0, v);
       if (p.save_h1 != nullptr && rvalid) {
@@ -237,6 +268,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     mma_wait();
+    if (img_in && m.tid == 0 && tile + gridDim.x < num_tiles) issue_image(tile + gridDim.x);   // sA is dead
     tl.stamp();   // 8 layer-4 product done (residual rows requested before)
     {
       float v[32];
@@ -275,9 +307,19 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       for (int i = 0; i < 8; ++i) {
         const float4 y = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
         const int rc = EDGE ? __shfl_sync(0xffffffffu, rcv_c, i) : -1;
+        if (dst[i] < 0 && EDGE && p.e16_next != nullptr)      // rows past the end: zeros in the image
+          *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16_next) + (size_t)tile * TILE_BYTES +
+                                    tile_off(128, m.warp * 8 + i, 4 * m.lane)) = make_uint2(0u, 0u);
         if (dst[i] >= 0) {
-          st_f4_hint(p.out + (long long)dst[i] * H + 4 * m.lane,
-                     make_float4(old[i].x + y.x, old[i].y + y.y, old[i].z + y.z, old[i].w + y.w), pol_stream);
+          const float4 o = make_float4(old[i].x + y.x, old[i].y + y.y, old[i].z + y.z, old[i].w + y.w);
+          st_f4_hint(p.out + (long long)dst[i] * H + 4 * m.lane, o, pol_stream);
+          if (EDGE && p.e16_next != nullptr) {   // the same row in the next step's operand-tile image (8 bytes per lane)
+            uint2 pk;
+            pk.x = pack_h2(o.x, o.y);
+            pk.y = pack_h2(o.z, o.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16_next) + (size_t)tile * TILE_BYTES +
+                                      tile_off(128, m.warp * 8 + i, 4 * m.lane)) = pk;
+          }
           if (EDGE) {
             if (rc != cur) {
               if (cur >= 0) red_add_f4_hint(p.aggr + (long long)cur * H + 4 * m.lane, sum, pol_keep);
@@ -471,7 +513,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
                             const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                             const void* packed, const float* b2, const float* b3, const float* b4,
                             const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                            void* stream_) {
+                            const void* e16_in, void* e16_next, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
@@ -485,7 +527,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
-  p.e16_out = (__half*)e16_out;
+  p.e16_out = (__half*)e16_out; p.e16_in = (const __half*)e16_in; p.e16_next = (__half*)e16_next;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {

@@ -117,25 +117,36 @@ class _ProcessorFn(torch.autograd.Function):
             P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
             aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
             x_bufs = [torch.empty_like(x) for _ in range(min(K, 2))]
+        # fp16 operand-tile images of the edge stream: step k reads image k (step 0 builds it while loading e_0) and
+        # writes image k+1 next to e_{k+1}; training keeps them all (the edge backward recomputes from them)
+        img_bufs = [ops.e16_image(E, dev) for _ in range(min(K, 2))] if not need_grad else None
+        img = None
         for k in range(K):
             b = prm[18 * k:18 * (k + 1)]
             if need_grad:
                 P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
                 aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
-                e_out = e_bufs[k & 1]
                 x_out = torch.empty_like(x)
                 sv = tuple(torch.empty((N, H), dtype=torch.float16, device=dev) for _ in range(3))
-                e16 = ops.e16_image(E, dev)
             else:
-                e_out, x_out, sv, e16 = e_bufs[k & 1], x_bufs[k & 1], None, None
+                x_out, sv = x_bufs[k & 1], None
+            e_out = e_bufs[k & 1]
+            if k == 0:
+                img = ops.e16_image(E, dev) if need_grad else img_bufs[1 % len(img_bufs)]
+                img_self, img_in = img, None
+            else:
+                img_self, img_in = None, img
+            img_next = None
+            if k + 1 < K:
+                img_next = ops.e16_image(E, dev) if need_grad else img_bufs[k & 1]
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
             _timed("edge_fwd", ops.edge_fwd, e, None, P, csr.senders, csr.receivers, N, packed[k], b[3], b[5], b[7],
-                   b[8], e_out=e_out, aggr=aggr, e16_out=e16)
+                   b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in, e16_next=img_next)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
                    saves=sv)
             if need_grad:
-                aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(e16)
-            x, e = x_out, e_out
+                aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
+            x, e, img = x_out, e_out, img_next
         if csr.identity:
             e_ret = e
         else:
