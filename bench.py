@@ -412,7 +412,7 @@ def run_b200(args):
                 line["cpu_baseline"]["eager_gpu"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
         print(json.dumps(line), flush=True)
         if os.environ.get("MGN_BENCH_BREAKDOWN"):       # developer aid: per-kernel device time of one extra step (stderr)
-            names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "dp_gather", "p_bwd"]
+            names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "edge_wgrad1", "dp_gather", "p_bwd"]
             proc.EVENTS = {n: [] for n in names}
             s0, e0_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s0.record()

@@ -111,7 +111,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_wA = tail->bar[0];
   uint64_t& bar_wB = tail->bar[1];
   uint64_t& bar_mma = tail->bar[2];
-  uint64_t& bar_dwe = tail->bar[3];
   uint64_t& bar_e = tail->bar[4];
   uint64_t& bar_g = tail->bar[5];
   uint32_t& tmem_slot = tail->tmem_slot;
@@ -121,7 +120,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_wA, 1);
     mbar_init(&bar_wB, 1);
     mbar_init(&bar_mma, 1);
-    mbar_init(&bar_dwe, 1);
     mbar_init(&bar_e, 1);
     mbar_init(&bar_g, 1);
     mbar_init_fence();
@@ -138,9 +136,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   const uint64_t pol_stream = policy_evict_first();
   const uint64_t pol_keep = policy_evict_last();
   uint32_t phase = 0;
-  float dwe[32];                    // this thread's part of dWe = sum over tiles of dz1^T e16
-#pragma unroll
-  for (int j = 0; j < 32; ++j) dwe[j] = 0.f;
   float dsc = 0.f;
   float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
   if (m.tid == 0) {
@@ -242,7 +237,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       cp_async_wait_all();
       __syncthreads();      // the staged P_j rows (issued during the previous tile) are visible to every thread
       mma_wait();
-      if (m.tid == 0) load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
+      if (m.tid == 0) {
+        load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
+        if (has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);   // sE is dead: the next tile's e image
+      }
       float v[32], b[32];
       tmem_ld32(tm_W + qoff, v);
       load_row_chunk_f16(sH1, 128, m.row, m.c0, b);
@@ -359,44 +357,24 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       mbar_arrive_expect_tx(&bar_g, tile_bytes);
       bulk_g2s(lin32, p.g_eout + row0 * H, tile_bytes, &bar_g);
     }
-    // ---- dWe = dz1^T e16 into the working accumulator; the dz1 tile goes to global memory as it is (one bulk
-    //      copy): p_bwd sums it per receiver and per sender, so nothing is scattered with atomics here
-    if (m.tid == 0) {
-      fence_after_sync();
-      umma_tile(tm_W, uH1, 128, 1, uE, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_dwe);
-      if (!(p.dbg_skip & 64)) {
-        bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
-        bulk_commit();
-      }
+    // ---- the dz1 tile goes to global memory as it is (one bulk copy of the fp16 operand tile): dp_gather sums it per
+    //      receiver and per sender (nothing is scattered with atomics here) and edge_wgrad1 forms dWe = dz1^T e from it
+    if (m.tid == 0 && !(p.dbg_skip & 64)) {
+      bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
+      bulk_commit();
     }
-    mbar_wait(&bar_dwe, it & 1);
-    fence_after_sync();
-    {
-      float v[32];
-      tmem_ld32(tm_W + qoff, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < 32; ++j) dwe[j] += v[j];
-    }
-    fence_before_sync();
-    __syncthreads();      // working accumulator and sE are free
-    tl.stamp();   // 6 dWe done
-    // ---- D1: dz1 We; under it: the next tile's e image (bulk) and g (coalesced loads)
+    // ---- D1: dz1 We; under it: the next tile's g (coalesced loads)
     if (m.tid == 0) {
       mbar_wait(&bar_wA, 0);
       fence_after_sync();
       umma_tile(tm_W, uH1, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
-      bulk_wait_read0();    // the dz1 image copy has read sH1: whoever sees this product complete may overwrite it
       mma_commit(&bar_mma);
-      if (has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);
     }
     const Idx done = cur;
     cur = nxt;
     if (has_next && !(p.dbg_skip & 32)) load_g(cur);
     nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mma_wait();
-    if (has_next) stage_pj(cur);          // sH1 is dead: the next tile's P_j rows, asynchronously
     tl.stamp();   // 7 D1 done, next g loaded
     // ---- g_e = g_eout + dz1 We
     if (p.rowmap == nullptr) {
@@ -407,6 +385,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       tmem_ld_wait();
       if (p.g_eout != nullptr) add_row32_linear(lin32, m, v);
       else store_row32_linear(lin32, m, v);
+      if (m.tid == 0) bulk_wait_read0();    // the dz1 image copy has read sH1
       tile_ready();
       if (m.tid == 0 && !(p.dbg_skip & 8)) {
         bulk_s2g(p.g_e + row0 * H, lin32, tile_bytes, pol_stream);
@@ -430,8 +409,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         }
       }
       fence_before_sync();
+      if (m.tid == 0) bulk_wait_read0();    // the dz1 image copy has read sH1
       __syncthreads();      // every thread has read the accumulator before the next tile's first product
     }
+    if (has_next) stage_pj(cur);            // sH1 is dead: the next tile's P_j rows, asynchronously
     tl.stamp();   // 8 g_e issued
   }
   if (m.tid == 0) bulk_wait0();
@@ -440,12 +421,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   flush_acc_q(tm_dW4 + qoff, p.grad + GB_E_W4, 128, m);
   flush_acc_q(tm_dW3 + qoff, p.grad + GB_E_W3, 128, m);
   flush_acc_q(tm_dW2 + qoff, p.grad + GB_E_W2, 128, m);
-  {
-    float* dst = p.grad + GB_E_W1 + (long long)m.row * 384 + m.c0;
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-      red_add_f4(dst + 4 * j, make_float4(dwe[4 * j], dwe[4 * j + 1], dwe[4 * j + 2], dwe[4 * j + 3]));
-  }
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
@@ -915,11 +890,80 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
 }
 
+// ===================================================================================== edge layer-1 wgrad
+// dWe [128,128] += dz1^T e16 over all edge tiles, from the two fp16 tile-image streams (edge_bwd's dz1 images and the
+// forward's images of e): both are already in the shared-memory operand layout, so a tile is two 32 KB bulk copies and
+// eight MMAs.  Warp-specialised: thread 0 feeds a 3-stage ring, thread 32 issues the products (their completion
+// releases the stage), everybody flushes the TMEM-resident accumulator at the end.
+struct EdgeWgrad1Params {
+  long long E;
+  const __half* dz16;
+  const __half* e16;
+  float* grad;
+};
+
+__global__ void __launch_bounds__(NT, 1) edge_wgrad1_kernel(const EdgeWgrad1Params p) {
+  constexpr int STAGES = 3;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  check_smem_alignment(smem);
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + STAGES * 2 * SLOT);
+  uint64_t* full = &tail->bar[0];      // [3] both tiles of the stage have landed
+  uint64_t* empty = &tail->bar[3];     // [3] the products reading the stage have completed
+  uint64_t& bar_done = tail->bar[6];
+  uint32_t& tmem_slot = tail->tmem_slot;
+  const Map m = make_map();
+  if (m.tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(&bar_done, 1);
+    mbar_init_fence();
+  }
+  if (m.warp == 0) tmem_alloc<128>(&tmem_slot);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tm = tmem_slot;
+  const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
+  const uint32_t my_tiles = blockIdx.x < num_tiles ? (uint32_t)((num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  if (m.tid == 0) {                       // producer
+    for (uint32_t i = 0; i < my_tiles; ++i) {
+      const uint32_t s = i % STAGES, n = i / STAGES;
+      if (n > 0) mbar_wait(&empty[s], (n - 1) & 1);
+      const size_t off = (size_t)(blockIdx.x + (long long)i * gridDim.x) * SLOT;
+      mbar_arrive_expect_tx(&full[s], 2 * SLOT);
+      bulk_g2s(smem + (2 * s) * SLOT, reinterpret_cast<const uint8_t*>(p.dz16) + off, SLOT, &full[s]);
+      bulk_g2s(smem + (2 * s + 1) * SLOT, reinterpret_cast<const uint8_t*>(p.e16) + off, SLOT, &full[s]);
+    }
+  } else if (m.tid == 32) {               // MMA issuer
+    for (uint32_t i = 0; i < my_tiles; ++i) {
+      const uint32_t s = i % STAGES, n = i / STAGES;
+      mbar_wait(&full[s], n & 1);
+      fence_after_sync();
+      umma_tile(tm, smem_u32(smem + (2 * s) * SLOT), 128, 1, smem_u32(smem + (2 * s + 1) * SLOT), 128, 1, 0, 128, 8,
+                i > 0);
+      mma_commit(&empty[s]);
+    }
+    mma_commit(&bar_done);
+  }
+  __syncwarp();
+  if (my_tiles > 0) {
+    mbar_wait(&bar_done, 0);
+    fence_after_sync();
+    flush_acc_q(tm + m.lane_off + m.c0, p.grad + GB_E_W1, 384, m);
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (m.warp == 0) tmem_dealloc<128>(tmem_slot);
+}
+
 // ===================================================================================== C ABI
 static constexpr int EDGE_BWD_SMEM = 7 * SLOT + TAIL_BYTES;
 static constexpr int NODE_BWD_SMEM = 6 * SLOT + TAIL_BYTES;
 static constexpr int P_BWD_SMEM = 5 * SLOT + TAIL_BYTES;
 static constexpr int NODE_WGRAD1_SMEM = 6 * SLOT + TAIL_BYTES;
+static constexpr int EDGE_WGRAD1_SMEM = 6 * SLOT + TAIL_BYTES;
 
 extern "C" int64_t mgn_grad_block_floats(void) { return GB_FLOATS; }
 
@@ -1022,6 +1066,25 @@ extern "C" int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
   node_wgrad1_kernel<<<grid, NT, NODE_WGRAD1_SMEM, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+// Weight gradient of edge_block layer 1, edge-latent part: dWe += dz1^T e from the two tile-image streams
+// (edge_block.0.weight[:, 0:128]).
+extern "C" int mgn_edge_wgrad1(int64_t E, const void* dz16, const void* e16, float* grad_block, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(E >= 0, "edge_wgrad1: bad size");
+  if (E == 0) return MGN_OK;
+  MGN_CHECK_ARG(dz16 && e16 && grad_block, "edge_wgrad1: null pointer");
+  EdgeWgrad1Params p{E, (const __half*)dz16, (const __half*)e16, grad_block};
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(edge_wgrad1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_WGRAD1_SMEM));
+    attr = true;
+  }
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
+  edge_wgrad1_kernel<<<grid, NT, EDGE_WGRAD1_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

@@ -150,6 +150,11 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
     return g_x, g_aggr, dz1
 
 
+def edge_wgrad1(dz16, e16, num_edges, grad_block):
+    """dWe += dz1^T e (edge_block.0.weight[:, :128]) from the tile images of dz1 (edge_bwd) and of e (edge_fwd)."""
+    L.check(L.lib().mgn_edge_wgrad1(L.i64(num_edges), L.p(dz16), L.p(e16), L.p(grad_block), L.stream()))
+
+
 def dp_gather(dz16, csr, dP=None):
     """dP [N,256] fp16 = [sum of dz1 over received edges | over sent edges], gathered from edge_bwd's tile images in
     a fixed order (no atomics).  csr: graph.CSRGraph."""

@@ -4,7 +4,8 @@ kernels of libmgn_b200.so.
 
 Per step k (GraphNetBlock.forward, graphphysics/models/layers.py:667-701):
   forward   P_k = p_fwd(x_k) ; e_{k+1}, aggr_k = edge_fwd(e_k, P_k) ; x_{k+1} = node_fwd(x_k, aggr_k)
-  backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, dz1 images ; p_bwd -> g_x += ...
+  backward  node_bwd -> g_aggr, g_x (direct) ; node_wgrad1 ; edge_bwd -> g_e, dz1 images ; edge_wgrad1 ;
+            dp_gather -> dP ; p_bwd -> g_x += ...
 Saved per step: x_k (the residual stream itself), e_k as the fp16 tile images the edge kernel
 built for its first product (the fp32 edge stream is NOT kept), aggr_k, P_k (fp16) and the node
 MLP's three hidden activations (fp16).  The edge MLP's hidden activations are recomputed.
@@ -208,6 +209,7 @@ class _ProcessorFn(torch.autograd.Function):
                        csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
                        inplace=True)
                 have_ge = True
+                _timed("edge_wgrad1", ops.edge_wgrad1, dz16, e16s[k], E, grads[k])
                 _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
             _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx

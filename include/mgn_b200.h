@@ -130,6 +130,9 @@ int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const
                  const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
                  const int32_t* receivers, float* g_e, void* dz16_out, const void* packed, const float* b2,
                  const float* b3, const float* b4, const float* scale, float* grad_block, void* stream);
+/* edge_block layer-1 weight gradient, edge-latent columns (edge_block.0.weight[:, 0:128]):
+ * dWe += dz1^T e over all edges, streamed from the tile images of dz1 (mgn_edge_bwd) and of e (mgn_edge_fwd). */
+int mgn_edge_wgrad1(int64_t E, const void* dz16, const void* e16, float* grad_block, void* stream);
 /* backward of the two gathers: dP [N,256] fp16; dP[n, :128] = sum of dz1 over CSR positions
  * rowptr[n]..rowptr[n+1] (edges n receives), dP[n, 128:] = sum over out_pos[rowptr_s[n]..rowptr_s[n+1]]
  * (edges n sends; lists = mgn_build_csr of the flipped CSR-ordered pairs).  fp32 sums in a fixed

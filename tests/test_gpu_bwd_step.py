@@ -65,6 +65,10 @@ def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
                            packed, eb[1], eb[2], eb[3], esc, grad, e16=e16)
     if ge is not None:
         assert torch.equal(ge, ge_before)       # not in place unless asked
+    if e16 is None:      # the layer-1 weight gradient needs the images of e: build them with a second forward call
+        e16 = ops.e16_image(E, dev)
+        ops.edge_fwd(e_in, rowmap, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3], esc, e16_out=e16)
+    ops.edge_wgrad1(dz16, e16, E, grad)
     ops.p_bwd(ops.dp_gather(dz16, csr), xd, g_x, packed, grad)
     torch.cuda.synchronize()
     if not use_rowmap:

@@ -28,7 +28,7 @@ e2, x2 = torch.empty_like(e), torch.empty_like(x)
 P = ops.p_fwd(x, packed, b[0])
 aggr = torch.empty(N, 128, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
-cap = 11 * 19 + 8 if which != "edge_bwd" else 9 * 19
+cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19
 ge_in = torch.randn(E, 128, device=dev)
 g_aggr = torch.randn(N, 128, device=dev)
 ge_out = torch.empty_like(e)
@@ -61,8 +61,8 @@ t = t[t > 0]
 names = ["load", "L1 mma", "L1 epi", "L2 mma", "L2 epi", "L3 mma", "L3 epi", "L4 mma", "norm+stage", "output", "next"]
 per = 11
 if which == "edge_bwd":
-    names = ["top", "R1", "R2+R3", "R4+norm", "D4..D2", "dWe", "D1+g'", "g_e", "next"]
-    per = 9
+    names = ["top", "R1", "R2+R3", "R4+norm", "D4..D2", "D1+g'", "g_e", "next"]
+    per = 8
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
