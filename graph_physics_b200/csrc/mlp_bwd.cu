@@ -180,12 +180,31 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
                  p.P + (long long)(rc >= 0 ? sn : 0) * 256 + 128 + 8 * q, rc >= 0 ? 16u : 0u, pol_keep);
     }
   };
-  // g = g_eout + g_aggr[receiver] -> sG (fp16), coalesced
-  auto load_g = [&](const Idx& ix) {
-    auto dst_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.dst, i); };
-    auto rcv_of = [&](int i) -> long long { return (long long)__shfl_sync(0xffffffffu, ix.rcv, i); };
-    if (p.g_eout) load8_sum2_to_tile(sG, p.g_eout, p.g_aggr, m, dst_of, rcv_of, pol_stream, pol_keep);
-    else load8_f32_to_tile(sG, 128, 0, p.g_aggr, m, rcv_of, pol_keep);
+  // g = g_eout + g_aggr[receiver] -> sG (fp16), coalesced, in four pieces of two rows per warp.  The loads of a piece
+  // are issued at the start of one phase and its shared-memory stores happen at the start of the next one, so a whole
+  // product + epilogue hides their latency: pieces 0..3 of tile t+1 are issued at D3, D2, D1 and the g_e phase of tile t
+  // (sG is dead after D4) and the last one lands at R1 of tile t+1 (g is first read by R4).
+  struct GPiece { float4 a[2], b[2]; };
+  auto g_issue = [&](const Idx& ix, int piece) -> GPiece {
+    GPiece r;
+    const long long r0 = __shfl_sync(0xffffffffu, ix.rcv, 2 * piece), r1 = __shfl_sync(0xffffffffu, ix.rcv, 2 * piece + 1);
+    const long long d0 = __shfl_sync(0xffffffffu, ix.dst, 2 * piece), d1 = __shfl_sync(0xffffffffu, ix.dst, 2 * piece + 1);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    r.a[0] = (p.g_eout && d0 >= 0) ? ld_f4_hint(p.g_eout + d0 * H + 4 * m.lane, pol_stream) : z;
+    r.a[1] = (p.g_eout && d1 >= 0) ? ld_f4_hint(p.g_eout + d1 * H + 4 * m.lane, pol_stream) : z;
+    r.b[0] = r0 >= 0 ? ld_f4_hint(p.g_aggr + r0 * H + 4 * m.lane, pol_keep) : z;
+    if (r1 == r0) r.b[1] = r.b[0];      // both edges of one receiver: fetched once (warp-uniform)
+    else r.b[1] = r1 >= 0 ? ld_f4_hint(p.g_aggr + r1 * H + 4 * m.lane, pol_keep) : z;
+    return r;
+  };
+  auto g_store = [&](const GPiece& r, int piece) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      uint2 pk;
+      pk.x = pack_h2(r.a[i].x + r.b[i].x, r.a[i].y + r.b[i].y);
+      pk.y = pack_h2(r.a[i].z + r.b[i].z, r.a[i].w + r.b[i].w);
+      *reinterpret_cast<uint2*>(sG + tile_off(128, m.warp * 8 + 2 * piece + i, 4 * m.lane)) = pk;
+    }
   };
   // e tile: the forward kernel's fp16 tile image (one 32 KB bulk copy), else converted from the fp32 rows
   auto issue_e16 = [&](long long tile_) {      // thread 0
@@ -204,7 +223,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   Idx cur = load_idx(blockIdx.x);
   if (p.e16 != nullptr && m.tid == 0) issue_e16(blockIdx.x);
   stage_pj(cur);
-  load_g(cur);
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) g_store(g_issue(cur, q4), q4);
+  GPiece gq;                            // the piece in flight (next tile's g)
+  bool gq_pending = false;              // first tile: nothing left over from a previous tile
   Idx nxt = load_idx((long long)blockIdx.x + gridDim.x);
 
   uint32_t it = 0;
@@ -218,6 +240,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tl.stamp();   // 1
 
+    if (gq_pending) g_store(gq, 3);       // last piece of this tile's g
     // ---- R1: z1 = e We^T + P_i[recv] + P_j[send]
     if (m.tid == 0) {
       if (it == 0) mbar_wait(&bar_wA, 0);
@@ -332,6 +355,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
+    if (has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
@@ -344,6 +368,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+    }
+    if (has_next) {
+      g_store(gq, 0);
+      gq = g_issue(nxt, 1);
     }
     tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
@@ -372,9 +400,17 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     const Idx done = cur;
     cur = nxt;
-    if (has_next && !(p.dbg_skip & 32)) load_g(cur);
+    if (has_next) {
+      g_store(gq, 1);
+      gq = g_issue(cur, 2);
+    }
     nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mma_wait();
+    if (has_next) {
+      g_store(gq, 2);
+      gq = g_issue(cur, 3);
+    }
+    gq_pending = has_next;
     tl.stamp();   // 7 D1 done, next g loaded
     // ---- g_e = g_eout + dz1 We
     if (p.rowmap == nullptr) {
