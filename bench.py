@@ -41,6 +41,9 @@ METRIC = "mgn_processor_edges_per_s_fwd_bwd_h128_15steps"
 BYTES_EDGE_STEP, BYTES_NODE_STEP = 2568, 7168          # SURVEY.md 8(d), fwd+bwd per step
 FLOPS_EDGE_STEP, FLOPS_NODE_STEP = 589824, 491520
 EDGE_BWD_BYTES_EDGE, EDGE_BWD_BYTES_NODE = 1540, 2048  # the dominant kernel's share
+# dram__bytes_read.sum + dram__bytes_write.sum of one edge_bwd_kernel launch on this workload, from the committed
+# `ncu --set full` capture (profiles/r01_ncu_edge_bwd_v4.md); not re-measured by bench.py
+EDGE_BWD_DRAM_BYTES_NCU = 458_341_120 + 212_472_320
 
 
 def load_mesh():
@@ -386,7 +389,9 @@ def run_b200(args):
             "ms_per_step_eager": ms_eager / args.steps,
             "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "edge_bwd_kernel", "achieved": ach, "peak": hbm, "unit": "GB/s",
-                         "frac": ach / hbm, "traffic": None, "peak_source": which,
+                         "frac": ach / hbm, "traffic": EDGE_BWD_DRAM_BYTES_NCU if copies == 32 else None,
+                         "traffic_source": "ncu --set full, profiles/r01_ncu_edge_bwd_v4.md (bytes per launch)",
+                         "peak_source": which,
                          "ms_per_launch": edge_bwd_ms, "launches_timed": len(durs),
                          "timed_in": "eager pass of the same steps (one CUDA event pair per launch) run before the "
                                      "graph-replayed region of `value`",
