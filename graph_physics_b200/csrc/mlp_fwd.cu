@@ -20,6 +20,7 @@ struct FwdParams {
   const float* in0;           // edge: e [E,128]; node: x [N,128]
   const float* in1;           // node: aggr [N,128]
   const int32_t* rowmap;      // edge: CSR position -> caller row of e (null = identity)
+  int out_csr;                // edge: 1 = rowmap applies to the input rows only, the output is written in CSR order
   float* out;                 // e_out / x_out, same row convention as in0
   const __half* P;            // edge: [N,256] fp16 (P_i + b1 | P_j)
   const int32_t* senders;     // edge, CSR order
@@ -306,13 +307,14 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float4 y = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
+        const long long orow = (EDGE && p.out_csr) ? row0 + m.warp * 8 + i : (long long)dst[i];
         const int rc = EDGE ? __shfl_sync(0xffffffffu, rcv_c, i) : -1;
         if (dst[i] < 0 && EDGE && p.e16_next != nullptr)      // rows past the end: zeros in the image
           *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16_next) + (size_t)tile * TILE_BYTES +
                                     tile_off(128, m.warp * 8 + i, 4 * m.lane)) = make_uint2(0u, 0u);
         if (dst[i] >= 0) {
           const float4 o = make_float4(old[i].x + y.x, old[i].y + y.y, old[i].z + y.z, old[i].w + y.w);
-          st_f4_hint(p.out + (long long)dst[i] * H + 4 * m.lane, o, pol_stream);
+          st_f4_hint(p.out + orow * H + 4 * m.lane, o, pol_stream);
           if (EDGE && p.e16_next != nullptr) {   // the same row in the next step's operand-tile image (8 bytes per lane)
             uint2 pk;
             pk.x = pack_h2(o.x, o.y);
@@ -513,7 +515,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
                             const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                             const void* packed, const float* b2, const float* b3, const float* b4,
                             const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                            const void* e16_in, void* e16_next, void* stream_) {
+                            const void* e16_in, void* e16_next, int out_in_csr_order, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
@@ -522,7 +524,8 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
                 "edge_fwd: null pointer");
   MGN_CHECK_ARG(e_in != e_out, "edge_fwd: in-place not supported");
   FwdParams p{};
-  p.M = E; p.in0 = e_in; p.rowmap = rowmap; p.out = e_out; p.P = (const __half*)P;
+  p.M = E; p.in0 = e_in; p.rowmap = rowmap; p.out_csr = (rowmap != nullptr && out_in_csr_order) ? 1 : 0;
+  p.out = e_out; p.P = (const __half*)P;
   p.senders = senders; p.receivers = receivers; p.aggr = aggr;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;

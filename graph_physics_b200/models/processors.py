@@ -66,8 +66,9 @@ class EncodeProcessDecode(nn.Module):
         if len(self.processor_list) > 0:
             for block in self.processor_list:
                 block.check_supported()
-            x, edge_attr = _proc.run_processor(x, edge_index, edge_attr,
-                                               [block_param_list(b) for b in self.processor_list])
+            # the reference discards the final edge latents (processors.py:130-137): no exit permutation
+            x, _ = _proc.run_processor(x, edge_index, edge_attr, [block_param_list(b) for b in self.processor_list],
+                                       need_edges=False)
         if self.only_processor:
             return x
         return self.decode_module(x)

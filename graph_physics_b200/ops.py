@@ -55,12 +55,14 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
              e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None,
              e16_out: Optional[torch.Tensor] = None, e16_in: Optional[torch.Tensor] = None,
-             e16_next: Optional[torch.Tensor] = None):
+             e16_next: Optional[torch.Tensor] = None, out_in_csr_order: bool = False):
     """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
     used by the parity tests only -- the backward kernel recomputes them).
     e16_out: optional `e16_image(E)` buffer receiving the fp16 tile images of e_in that edge_bwd bulk-loads.
     e16_in: the tile images of e_in if a previous step already made them (its e16_next): the operand tiles then
-    arrive by bulk copy and e_in is read for the residual only.  e16_next: receives the images of e_out."""
+    arrive by bulk copy and e_in is read for the residual only.  e16_next: receives the images of e_out.
+    out_in_csr_order: with a rowmap, gather e_in through it but write e_out in CSR order (fuses the entry permutation
+    of the processor loop into its first step)."""
     E = e_in.shape[0]
     s1, s2, s3 = saves if saves is not None else (None, None, None)
     if e_out is None:
@@ -69,7 +71,7 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
     L.check(L.lib().mgn_edge_fwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
                                  L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
-                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next), L.stream()))
+                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next), L.i32(1 if out_in_csr_order else 0), L.stream()))
     return e_out, aggr
 
 

@@ -95,7 +95,7 @@ def _check_inputs(x, e, params, num_steps):
 
 class _ProcessorFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x0, e0, csr, num_steps, *params):
+    def forward(ctx, x0, e0, csr, num_steps, need_edges, *params):
         ctx.set_materialize_grads(False)
         K = int(num_steps)
         _check_inputs(x0, e0, params, K)
@@ -108,10 +108,10 @@ class _ProcessorFn(torch.autograd.Function):
             b = prm[18 * k:18 * (k + 1)]
             _timed("pack", ops.pack_block, [b[i] for i in _E_W], [b[i] for i in _N_W], out=packed[k])
         x = x0.detach().contiguous()
-        if csr.identity:
-            e = e0.detach().contiguous()
-        else:
-            e = e0.detach().index_select(0, csr.perm_long)
+        # edges run in receiver-sorted (CSR) order inside the loop; the first edge kernel gathers its input rows
+        # through the permutation (no separate pass over the edge stream)
+        e = e0.detach().contiguous()
+        rowmap0 = None if csr.identity else csr.perm
         xs, aggrs, Ps, saves, e16s = [x], [], [], [], []
         e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))]     # the fp32 edge stream ping-pongs
         if not need_grad:   # inference: ping-pong buffers, nothing kept
@@ -141,14 +141,18 @@ class _ProcessorFn(torch.autograd.Function):
             if k + 1 < K:
                 img_next = ops.e16_image(E, dev) if need_grad else img_bufs[k & 1]
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
-            _timed("edge_fwd", ops.edge_fwd, e, None, P, csr.senders, csr.receivers, N, packed[k], b[3], b[5], b[7],
-                   b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in, e16_next=img_next)
+            _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
+                   packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
+                   e16_next=img_next, out_in_csr_order=True)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
                    saves=sv)
             if need_grad:
                 aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
             x, e, img = x_out, e_out, img_next
-        if csr.identity:
+        if not need_edges:          # the caller discards the edge latents (EncodeProcessDecode): skip the exit permutation
+            e_ret = e.new_empty((0, H))
+            ctx.mark_non_differentiable(e_ret)
+        elif csr.identity:
             e_ret = e
         else:
             e_ret = torch.empty_like(e)
@@ -167,7 +171,7 @@ class _ProcessorFn(torch.autograd.Function):
         dev = xs[0].device
         N, E = xs[0].shape[0], ctx.E
         if g_x is None and g_e is None:
-            return (None,) * (4 + 18 * K)
+            return (None,) * (5 + 18 * K)
         # ---- power-of-two gradient scale (device-side, no host sync)
         amax = torch.zeros((), dtype=torch.float32, device=dev)
         if g_x is not None:
@@ -228,26 +232,27 @@ class _ProcessorFn(torch.autograd.Function):
             else:
                 g_e0 = torch.empty_like(ge)
                 g_e0.index_copy_(0, csr.perm_long, ge)
-        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None]
+        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None, None]
         for k in range(K):
             views = ops.split_grad_block(grads[k])
             for i, name in enumerate(PARAM_NAMES):
-                out.append(views[name] if ctx.needs_input_grad[4 + 18 * k + i] else None)
+                out.append(views[name] if ctx.needs_input_grad[5 + 18 * k + i] else None)
         return tuple(out)
 
 
 def run_processor(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
-                  block_params: Sequence[Sequence[torch.Tensor]], csr: Optional[G.CSRGraph] = None):
+                  block_params: Sequence[Sequence[torch.Tensor]], csr: Optional[G.CSRGraph] = None,
+                  need_edges: bool = True):
     """x [N,128], edge_index [2,E] int64, edge_attr [E,128] (caller's edge order),
     block_params: per GraphNetBlock the 18 tensors in ops.GRAD_LAYOUT order.
-    Returns (x_K, edge_attr_K) with edge_attr_K in the caller's edge order."""
+    Returns (x_K, edge_attr_K) with edge_attr_K in the caller's edge order (an empty tensor if not need_edges)."""
     L.require_device(x)
     if csr is None:
         csr = csr_for(edge_index, x.shape[0])
     if csr.num_edges != edge_attr.shape[0] or csr.num_nodes != x.shape[0]:
         raise ValueError("edge_index / edge_attr / x sizes disagree")
     flat = [t for blk in block_params for t in blk]
-    return _ProcessorFn.apply(x, edge_attr, csr, len(block_params), *flat)
+    return _ProcessorFn.apply(x, edge_attr, csr, len(block_params), bool(need_edges), *flat)
 
 
 class CapturedStep:

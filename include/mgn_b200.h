@@ -94,12 +94,14 @@ int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edg
  * CSR tile order) tie consecutive steps and the backward together: e16_in (optional) = images of e_in left
  * by the previous step (operand tiles then arrive by bulk copy; e_in is read for the residual only);
  * e16_out (optional, used when e16_in is null) receives the images of e_in; e16_next (optional) receives
- * the images of e_out.  mgn_edge_bwd recomputes from the images of e_in. */
+ * the images of e_out.  mgn_edge_bwd recomputes from the images of e_in.  out_in_csr_order != 0 with a rowmap:
+ * e_in is gathered through the rowmap but e_out is written in CSR order (the entry permutation of a processor
+ * loop fused into its first step). */
 int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
                  const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                  const void* packed, const float* b2, const float* b3, const float* b4,
                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                 const void* e16_in, void* e16_next, void* stream);
+                 const void* e16_in, void* e16_next, int out_in_csr_order, void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
  * fp16, optional) are the hidden activations mgn_node_bwd needs. */
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
