@@ -1,0 +1,310 @@
+"""The processor loop on ONE mesh cut over several GPUs (BASELINE.json config 5).
+
+Every rank runs the same fused kernels as `processor.py` on its partition (`partition.Partition`): its owned nodes,
+the halo copies of remote senders, and every edge whose receiver it owns.  Per message-passing step:
+
+  forward   halo rows of x_k <- owners (all-to-all-v) ; P = p_fwd(x_k[owned | halo]) ; e_{k+1}, aggr = edge_fwd ;
+            x_{k+1}[owned] = node_fwd
+  backward  node_bwd, node_wgrad1 on the owned rows ; edge_bwd, edge_wgrad1, dp_gather on the local edges ;
+            p_bwd on owned + halo rows ; halo rows of g_x -> owners, summed there (all-to-all-v)
+
+and once per sweep: the gradient pre-scale is agreed with a MAX all-reduce (one float), the 15 flat weight-gradient
+blocks are SUMMED over ranks (every rank holds a partial sum over its edges / nodes).
+
+`PartitionEngine` is the step-wise state machine (no communication inside): `PartitionedProcessorFn` drives it with
+torch.distributed collectives as one autograd node; `run_partitions_local` drives several engines in one process
+(single-GPU validation of the partition logic against `processor.run_processor`).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from . import _lib as L
+from . import graph as G
+from . import ops
+from .partition import HaloExchange, LocalHaloExchange, Partition
+from .processor import PARAM_NAMES, _E_W, _N_W, _check_inputs, _timed
+
+H = ops.H
+
+
+class PartitionEngine:
+    """One rank's share of the loop.  The caller fills the halo rows of `x_ext(k)` before `fwd_step(k)` and returns
+    the halo rows of `g_ext()` to their owners after `bwd_step(k)`."""
+
+    def __init__(self, part: Partition, block_params: Sequence[Sequence[torch.Tensor]], need_grad: bool = True,
+                 csr: Optional[G.CSRGraph] = None):
+        self.part, self.K, self.need_grad = part, len(block_params), need_grad
+        if part.num_owned == 0:
+            raise ValueError("a partition must own at least one node")
+        self.csr = csr if csr is not None else G.build_csr(part.edge_index, part.num_ext)
+        self.prm = [[p.detach().contiguous() for p in blk] for blk in block_params]
+        self.packed = None
+
+    # ------------------------------------------------------------------ forward
+    def fwd_begin(self, x_owned: torch.Tensor, e_local: torch.Tensor) -> None:
+        part, K = self.part, self.K
+        _check_inputs(x_owned, e_local, [t for b in self.prm for t in b], K)
+        if x_owned.shape[0] != part.num_owned or e_local.shape[0] != self.csr.num_edges:
+            raise ValueError("x_owned / e_local do not match the partition")
+        dev = x_owned.device
+        self.dev, self.E = dev, e_local.shape[0]
+        self.packed = torch.empty((K, ops.packed_block_bytes()), dtype=torch.uint8, device=dev)
+        for k in range(K):
+            b = self.prm[k]
+            _timed("pack", ops.pack_block, [b[i] for i in _E_W], [b[i] for i in _N_W], out=self.packed[k])
+        x0 = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
+        x0[:part.num_owned] = x_owned.detach()
+        self.xs: List[Optional[torch.Tensor]] = [x0]
+        self.e = e_local.detach().contiguous()
+        self.e_bufs = [torch.empty_like(self.e) for _ in range(min(K, 2))]
+        self.aggrs, self.Ps, self.saves, self.e16s = [], [], [], []
+        self.img = None
+        if not self.need_grad:
+            self.P = torch.empty((part.num_ext, 2 * H), dtype=torch.float16, device=dev)
+            self.aggr = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
+            self.img_bufs = [ops.e16_image(self.E, dev) for _ in range(min(K, 2))]
+
+    def x_ext(self, k: int) -> torch.Tensor:
+        return self.xs[k] if self.need_grad else self.xs[-1]
+
+    def fwd_step(self, k: int) -> None:
+        part, K, dev, E = self.part, self.K, self.dev, self.E
+        n_own, n_ext = part.num_owned, part.num_ext
+        b, csr, ng = self.prm[k], self.csr, self.need_grad
+        x = self.x_ext(k)
+        x_out = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
+        if ng:
+            P = torch.empty((n_ext, 2 * H), dtype=torch.float16, device=dev)
+            aggr = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
+            sv = tuple(torch.empty((n_own, H), dtype=torch.float16, device=dev) for _ in range(3))
+        else:
+            P, aggr, sv = self.P, self.aggr, None
+        _timed("p_fwd", ops.p_fwd, x, self.packed[k], b[1], out=P)
+        if E > 0:
+            e_out = self.e_bufs[k & 1]
+            if k == 0:
+                self.img = ops.e16_image(E, dev) if ng else self.img_bufs[1 % len(self.img_bufs)]
+                img_self, img_in = self.img, None
+            else:
+                img_self, img_in = None, self.img
+            img_next = None
+            if k + 1 < K:
+                img_next = ops.e16_image(E, dev) if ng else self.img_bufs[k & 1]
+            rowmap = csr.perm if (k == 0 and not csr.identity) else None
+            _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
+                   b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
+                   e16_next=img_next, out_in_csr_order=True)
+            if ng:
+                self.e16s.append(self.img)
+            self.e, self.img = e_out, img_next
+        else:
+            aggr.zero_()
+            if ng:
+                self.e16s.append(None)
+        _timed("node_fwd", ops.node_fwd, x[:n_own], aggr[:n_own], self.packed[k], b[10], b[12], b[14], b[16], b[17],
+               x_out=x_out[:n_own], saves=sv)
+        if ng:
+            self.aggrs.append(aggr); self.Ps.append(P); self.saves.append(sv); self.xs.append(x_out)
+        else:
+            self.xs = [x_out]
+
+    def outputs(self, need_edges: bool = True):
+        """(x_K of the owned nodes, e_K of the local edges in the caller's local edge order)."""
+        x = self.xs[-1][:self.part.num_owned]
+        if not need_edges:
+            return x, self.e.new_empty((0, H))
+        if self.csr.identity or self.E == 0:
+            return x, self.e
+        e_ret = torch.empty_like(self.e)
+        e_ret.index_copy_(0, self.csr.perm_long, self.e)
+        return x, e_ret
+
+    # ------------------------------------------------------------------ backward
+    def grad_amax(self, g_x: Optional[torch.Tensor], g_e: Optional[torch.Tensor]) -> torch.Tensor:
+        amax = torch.zeros((), dtype=torch.float32, device=self.dev)
+        if g_x is not None:
+            amax = torch.maximum(amax, g_x.detach().abs().max())
+        if g_e is not None and g_e.numel():
+            amax = torch.maximum(amax, g_e.detach().abs().max())
+        return amax
+
+    @staticmethod
+    def scale_from_amax(amax: torch.Tensor) -> torch.Tensor:
+        """The power of two the sweep is multiplied by (same rule as processor.py); `amax` must be the maximum over
+        ALL ranks, because halo gradients of different ranks are added together."""
+        return torch.exp2(torch.floor(torch.log2(64.0 / amax.clamp_min(1e-30)))).clamp(2.0 ** -100, 2.0 ** 100)
+
+    def bwd_begin(self, g_x: Optional[torch.Tensor], g_e: Optional[torch.Tensor], s: torch.Tensor) -> None:
+        part, K, dev, E, csr = self.part, self.K, self.dev, self.E, self.csr
+        n_own, n_ext = part.num_owned, part.num_ext
+        self.s, self.inv_s = s, 1.0 / s
+        self.gx = torch.zeros((n_ext, H), dtype=torch.float32, device=dev)
+        if g_x is not None:
+            self.gx[:n_own] = g_x.detach() * s
+        self.gx_new = torch.empty_like(self.gx)
+        if g_e is not None and E > 0:
+            ge = g_e.detach() if csr.identity else g_e.detach().index_select(0, csr.perm_long)
+            self.ge_buf, self.have_ge = (ge * s).contiguous(), True
+        else:
+            self.ge_buf, self.have_ge = torch.empty((E, H), dtype=torch.float32, device=dev), False
+        self.grads = torch.zeros((K, ops.GRAD_BLOCK_FLOATS), dtype=torch.float32, device=dev)
+        self.g_aggr = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
+        self.dz1 = torch.empty((n_own, H), dtype=torch.float16, device=dev)
+        self.dz16 = ops.e16_image(E, dev)
+        self.dP = torch.empty((n_ext, 2 * H), dtype=torch.float16, device=dev)
+        if E > 0:
+            csr.by_sender
+        else:
+            self.dP.zero_()
+
+    def g_ext(self) -> torch.Tensor:
+        return self.gx
+
+    def bwd_step(self, k: int) -> None:
+        part, E, csr = self.part, self.E, self.csr
+        n_own, n_ext = part.num_owned, part.num_ext
+        b, pk, gk = self.prm[k], self.packed[k], self.grads[k]
+        gx, gx_new = self.gx, self.gx_new
+        _timed("node_bwd", ops.node_bwd, gx[:n_own], self.saves[k], pk, b[16], b[17], gk, g_x=gx_new[:n_own],
+               g_aggr=self.g_aggr[:n_own], dz1=self.dz1)
+        if part.num_halo:
+            gx_new[n_own:].zero_()            # halo rows only collect what this rank's edges send back
+        _timed("node_wgrad1", ops.node_wgrad1, self.dz1, self.xs[k][:n_own], self.aggrs[k][:n_own], gk)
+        if E > 0:
+            _timed("edge_bwd", ops.edge_bwd, None, None, self.ge_buf if self.have_ge else None, self.g_aggr,
+                   self.Ps[k], csr.senders, csr.receivers, n_ext, pk, b[3], b[5], b[7], b[8], gk, g_e=self.ge_buf,
+                   dz16=self.dz16, e16=self.e16s[k], inplace=True)
+            self.have_ge = True
+            _timed("edge_wgrad1", ops.edge_wgrad1, self.dz16, self.e16s[k], E, gk)
+            _timed("dp_gather", ops.dp_gather, self.dz16, csr, self.dP)
+        _timed("p_bwd", ops.p_bwd, self.dP, self.xs[k], gx_new, pk, gk)
+        self.gx, self.gx_new = gx_new, gx
+        gk.mul_(self.inv_s)
+        self.saves[k] = None; self.aggrs[k] = None; self.Ps[k] = None; self.e16s[k] = None
+        self.xs[k + 1] = None
+
+    def input_grads(self, need_gx: bool = True, need_ge: bool = True):
+        """(g_x0 of the owned nodes, g_e0 of the local edges in the caller's local order); call after the halo return
+        of step 0."""
+        g_x0 = self.gx[:self.part.num_owned] * self.inv_s if need_gx else None
+        g_e0 = None
+        if need_ge:
+            ge = (self.ge_buf * self.inv_s) if self.have_ge else torch.zeros_like(self.ge_buf)
+            if self.csr.identity or self.E == 0:
+                g_e0 = ge
+            else:
+                g_e0 = torch.empty_like(ge)
+                g_e0.index_copy_(0, self.csr.perm_long, ge)
+        return g_x0, g_e0
+
+
+# ---------------------------------------------------------------------- torch.distributed driver
+class PartitionedProcessorFn(torch.autograd.Function):
+    """(x_owned, e_local) -> (x_K owned, e_K local) on this rank's partition; collectives inside forward and backward."""
+
+    @staticmethod
+    def forward(ctx, x_owned, e_local, part, csr, group, num_steps, need_edges, *params):
+        ctx.set_materialize_grads(False)
+        K = int(num_steps)
+        blocks = [params[18 * k:18 * (k + 1)] for k in range(K)]
+        need_grad = any(ctx.needs_input_grad)
+        eng = PartitionEngine(part, blocks, need_grad=need_grad, csr=csr)
+        halo = HaloExchange(part, group)
+        eng.fwd_begin(x_owned, e_local)
+        for k in range(K):
+            halo.forward(eng.x_ext(k))
+            eng.fwd_step(k)
+        x, e = eng.outputs(need_edges)
+        if not need_edges:
+            ctx.mark_non_differentiable(e)
+        if need_grad:
+            ctx.eng, ctx.halo, ctx.group, ctx.K = eng, halo, group, K
+        return x, e
+
+    @staticmethod
+    def backward(ctx, g_x, g_e):
+        eng, halo, K = ctx.eng, ctx.halo, ctx.K
+        # every rank must take part in the collectives, also one whose outputs received no gradient
+        amax = eng.grad_amax(g_x, g_e)
+        multi = eng.part.world > 1
+        if multi:
+            dist.all_reduce(amax, op=dist.ReduceOp.MAX, group=ctx.group)
+        eng.bwd_begin(g_x, g_e, eng.scale_from_amax(amax))
+        for k in range(K - 1, -1, -1):
+            eng.bwd_step(k)
+            halo.backward(eng.g_ext())
+        if multi:
+            dist.all_reduce(eng.grads, op=dist.ReduceOp.SUM, group=ctx.group)
+        g_x0, g_e0 = eng.input_grads(ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None, None, None, None]
+        for k in range(K):
+            views = ops.split_grad_block(eng.grads[k])
+            for i, name in enumerate(PARAM_NAMES):
+                out.append(views[name] if ctx.needs_input_grad[7 + 18 * k + i] else None)
+        ctx.eng = None
+        return tuple(out)
+
+
+def run_partitioned(x_owned: torch.Tensor, e_local: torch.Tensor, part: Partition,
+                    block_params: Sequence[Sequence[torch.Tensor]], group=None, csr: Optional[G.CSRGraph] = None,
+                    need_edges: bool = True):
+    """This rank's share of `processor.run_processor` on a mesh cut by `partition.build_partition`.
+    x_owned [num_owned,128]: latents of the owned nodes; e_local [E_loc,128]: latents of the local edges, rows in
+    the order of `part.edge_ids`.  Weight gradients come back already summed over the ranks of `group`."""
+    L.require_device(x_owned)
+    flat = [t for blk in block_params for t in blk]
+    return PartitionedProcessorFn.apply(x_owned, e_local, part, csr, group, len(block_params), bool(need_edges),
+                                        *flat)
+
+
+# ---------------------------------------------------------------------- single-process driver
+def run_partitions_local(parts: Sequence[Partition], x: torch.Tensor, e: torch.Tensor,
+                         block_params: Sequence[Sequence[torch.Tensor]], g_x: Optional[torch.Tensor] = None,
+                         g_e: Optional[torch.Tensor] = None):
+    """All partitions of one mesh on ONE device, stepped in lock-step with copies in place of the collectives.
+    x [N,128], e [E,128], g_x / g_e: upstream gradients (global numbering).  Returns a dict with x_out, e_out and, if
+    a gradient was given, g_x, g_e and grads ([K, GRAD_BLOCK_FLOATS], summed over partitions)."""
+    K = len(block_params)
+    need_grad = g_x is not None or g_e is not None
+    engs = [PartitionEngine(p, block_params, need_grad=need_grad) for p in parts]
+    halo = LocalHaloExchange(parts)
+    for p, eng in zip(parts, engs):
+        lo = p.node_begin
+        eng.fwd_begin(x[lo:lo + p.num_owned].contiguous(), e.index_select(0, p.edge_ids))
+    for k in range(K):
+        halo.forward_all([eng.x_ext(k) for eng in engs])
+        for eng in engs:
+            eng.fwd_step(k)
+    x_out, e_out = torch.empty_like(x), torch.empty_like(e)
+    for p, eng in zip(parts, engs):
+        xo, eo = eng.outputs(True)
+        x_out[p.node_begin:p.node_begin + p.num_owned] = xo
+        e_out.index_copy_(0, p.edge_ids, eo)
+    res = {"x_out": x_out, "e_out": e_out}
+    if not need_grad:
+        return res
+    loc = []
+    for p, eng in zip(parts, engs):
+        lo = p.node_begin
+        gxl = g_x[lo:lo + p.num_owned] if g_x is not None else None
+        gel = g_e.index_select(0, p.edge_ids) if g_e is not None else None
+        loc.append((gxl, gel))
+    amax = torch.stack([eng.grad_amax(*l) for eng, l in zip(engs, loc)]).max()
+    s = PartitionEngine.scale_from_amax(amax)
+    for eng, (gxl, gel) in zip(engs, loc):
+        eng.bwd_begin(gxl, gel, s)
+    for k in range(K - 1, -1, -1):
+        for eng in engs:
+            eng.bwd_step(k)
+        halo.backward_all([eng.g_ext() for eng in engs])
+    gx0, ge0 = torch.empty_like(x), torch.empty_like(e)
+    for p, eng in zip(parts, engs):
+        a, b = eng.input_grads()
+        gx0[p.node_begin:p.node_begin + p.num_owned] = a
+        ge0.index_copy_(0, p.edge_ids, b)
+    res.update(g_x=gx0, g_e=ge0, grads=torch.stack([eng.grads for eng in engs]).sum(0))
+    return res
