@@ -11,6 +11,8 @@ compute_k_hop_edge_index (torch_graph.py:16-53)      | compute_k_hop_edge_index
 filter_edges / build_masked_graph / reconstruct_graph (meshmask.py:9-118) | same names
 add_edge_features = Cartesian+Distance (preprocessing.py:16-23) | edge_features
 add_world_pos_features (preprocessing.py:143-174)    | world_pos_features
+add_world_edges (preprocessing.py:92-140)            | world_pairs, add_world_edges
+_add_random_edges (dataset/dataset.py:104-137)       | add_random_edges
 PyG Batch collation of identical meshes (train.py:164-165) | tile_batch
 (new) receiver-sorted CSR replacing the scatter-sum  | build_csr -> CSRGraph
 """
@@ -128,6 +130,97 @@ def edge_features(pos: torch.Tensor, edge_index: torch.Tensor) -> torch.Tensor:
 def world_pos_features(edge_attr: torch.Tensor, world_pos: torch.Tensor, edge_index: torch.Tensor) -> torch.Tensor:
     """append [wpos[s]-wpos[r], ||.||] (same arithmetic as edge_features on world_pos)."""
     return torch.cat([edge_attr, edge_features(world_pos, edge_index)], dim=-1)
+
+
+def world_pairs(world_pos: torch.Tensor, node_type: torch.Tensor, radius: float = 0.03, obstacle: int = 1,
+                normal: int = 0, sample: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """All (OBSTACLE node, NORMAL node) pairs at world distance <= radius: [2,M] int64, row 0 = obstacle.  The
+    pairs cKDTree.query_pairs + the two node-type masks keep in add_world_edges (preprocessing.py:103-131), found
+    with a uniform cell list on the device.  `sample` [N] restricts pairs to nodes of the same sample (the
+    reference runs per sample, before collation).  NodeType.NORMAL = 0, OBSTACLE = 1 (utils/nodetype.py:4-15)."""
+    import ctypes
+    L.require_device(world_pos)
+    pos = world_pos.to(torch.float32).contiguous()
+    N, D = pos.shape
+    dev = pos.device
+    if D not in (2, 3):
+        raise ValueError("world positions must be 2-D or 3-D")
+    if not radius > 0:
+        raise ValueError("radius must be positive")
+    if N == 0:
+        return torch.empty((2, 0), dtype=torch.int64, device=dev)
+    t = node_type.reshape(-1)
+    cls = ((t == obstacle).to(torch.uint8) + 2 * (t == normal).to(torch.uint8)).contiguous()
+    smp = sample.to(torch.int32).contiguous() if sample is not None else None
+    lo = pos.min(0).values.double().cpu()
+    hi = pos.max(0).values.double().cpu()
+    cell = 1.001 * float(radius)
+    dims = [int((float(hi[a]) - float(lo[a])) // cell) + 1 if a < D else 1 for a in range(3)]
+    nsmp = int(smp.max()) + 1 if smp is not None else 1
+    if nsmp * dims[0] * dims[1] * dims[2] >= 2 ** 62:
+        raise ValueError("world-edge cell grid too large for the radius")
+    origin = (ctypes.c_double * 3)(*[float(lo[a]) if a < D else 0.0 for a in range(3)])
+    cdims = (ctypes.c_int64 * 3)(*dims)
+    keys = torch.empty(N, dtype=torch.int64, device=dev)
+    L.check(L.lib().mgn_world_cell_keys(L.p(pos), L.i32(D), L.i64(N), L.p(smp), origin, ctypes.c_double(radius),
+                                        cdims, L.p(keys), L.stream()))
+    keys_sorted, order = torch.sort(keys)
+    order = order.to(torch.int32)
+    counts = torch.empty(N, dtype=torch.int64, device=dev)
+    args = (L.p(pos), L.i32(D), L.i64(N), L.p(cls), L.p(smp), L.p(keys_sorted), L.p(order), origin,
+            ctypes.c_double(radius), cdims)
+    L.check(L.lib().mgn_world_pairs(*args, L.p(counts), L.p(None), L.p(None), L.i64(0), L.stream()))
+    ends = torch.cumsum(counts, 0)
+    M = int(ends[-1])
+    pairs = torch.empty((2, M), dtype=torch.int64, device=dev)
+    if M:
+        offs = (ends - counts).contiguous()
+        L.check(L.lib().mgn_world_pairs(*args, L.p(None), L.p(offs), L.p(pairs), L.i64(M), L.stream()))
+    return pairs
+
+
+def add_world_edges(edge_index: torch.Tensor, world_pos: torch.Tensor, node_type: torch.Tensor, num_nodes: int,
+                    radius: float = 0.03, obstacle: int = 1, normal: int = 0,
+                    sample: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """add_world_edges (preprocessing.py:92-140) on tensors: world pairs in front of the mesh edges, to_undirected."""
+    pairs = world_pairs(world_pos, node_type, radius, obstacle, normal, sample)
+    return to_undirected(torch.cat([pairs, _i64c(edge_index)], dim=1), num_nodes)
+
+
+def add_random_edges(edge_index: torch.Tensor, p: float, num_nodes: int,
+                     generator: Optional[torch.Generator] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """_add_random_edges (dataset/dataset.py:104-137) -> PyG add_random_edge(edge_index, p, force_undirected=True):
+    round(E p) // 2 new undirected pairs (no self loops, none already present, no duplicates), both directions
+    appended AFTER the existing edges.  Returns (edge_index', added [2, 2*pairs]).  Random: comparable with the
+    reference by count, symmetry and disjointness only."""
+    L.require_device(edge_index)
+    ei = _i64c(edge_index)
+    dev = ei.device
+    E, N = ei.shape[1], int(num_nodes)
+    want = int(round(E * p)) // 2
+    if want == 0 or N < 2:
+        return ei, torch.empty((2, 0), dtype=torch.int64, device=dev)
+    lo, hi = torch.minimum(ei[0], ei[1]), torch.maximum(ei[0], ei[1])
+    have = torch.unique(lo * N + hi)
+    free = N * (N - 1) // 2 - int(((have // N) != (have % N)).sum())
+    if want > free:
+        raise ValueError("not enough absent node pairs for the requested random edges")
+    new = torch.empty(0, dtype=torch.int64, device=dev)
+    while new.numel() < want:
+        m = 2 * (want - int(new.numel())) + 64
+        a = torch.randint(0, N, (m,), device=dev, generator=generator)
+        b = torch.randint(0, N, (m,), device=dev, generator=generator)
+        k = torch.minimum(a, b) * N + torch.maximum(a, b)
+        k = k[a != b]
+        pos = torch.searchsorted(have, k).clamp_(max=have.numel() - 1)
+        k = k[have[pos] != k] if have.numel() else k
+        new = torch.unique(torch.cat([new, k]))
+        if new.numel() > want:      # unique() sorted them: drop a random subset, not the largest keys
+            keep = torch.randperm(new.numel(), device=dev, generator=generator)[:want]
+            new = new[keep]
+    pairs = torch.stack([new // N, new % N])
+    added = to_undirected(pairs, N)
+    return torch.cat([ei, added], dim=1), added
 
 
 def filter_edges(edge_index: torch.Tensor, node_index: torch.Tensor, edge_attr: Optional[torch.Tensor] = None):

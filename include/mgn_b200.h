@@ -70,6 +70,24 @@ int mgn_filter_edges(const int64_t* edge_index, int64_t E, const int64_t* node_i
 int mgn_edge_features(const float* pos, int dim, const int64_t* edge_index, int64_t E, float* out,
                       void* stream);
 
+/* add_world_edges, graphphysics/dataset/preprocessing.py:92-140: the radius search that replaces
+ * scipy.spatial.cKDTree.query_pairs + the OBSTACLE/NORMAL masks.  Uniform cell list (cell edge 1.001 radius):
+ *   1. mgn_world_cell_keys -> keys [N] int64 = ((sample*DX + cx)*DY + cy)*DZ + cz; the caller sorts them
+ *      (keys_sorted ascending, order [N] int32 = node at each sorted position);
+ *   2. mgn_world_pairs with offs == NULL -> counts [N] int64 (pairs found per first-set node);
+ *   3. mgn_world_pairs with offs = exclusive sum of counts -> pairs [2,M] int64 (row 0 = first-set node).
+ * pos [N,dim] f32 (dim 2 or 3); cls [N] u8: 1 = first set (OBSTACLE), 2 = second set (NORMAL), other = ignored;
+ * sample [N] int32 or NULL: pairs only join nodes of the same sample; origin[3], dims[3] are HOST arrays
+ * (per-axis minimum; floor((max-origin)/(1.001 radius)) + 1).  Test: squared distance of the float64-converted
+ * coordinates <= radius^2 (scipy's).  The caller then runs mgn_edge_keys/mgn_sort_unique_keys (to_undirected) on
+ * pairs ++ mesh edges exactly as the reference does. */
+int mgn_world_cell_keys(const float* pos, int dim, int64_t N, const int32_t* sample, const double* origin,
+                        double radius, const int64_t* dims, int64_t* keys, void* stream);
+int mgn_world_pairs(const float* pos, int dim, int64_t N, const uint8_t* cls, const int32_t* sample,
+                    const int64_t* keys_sorted, const int32_t* order, const double* origin, double radius,
+                    const int64_t* dims, int64_t* counts, const int64_t* offs, int64_t* pairs, int64_t M,
+                    void* stream);
+
 /* ------------------------------------------------------------------ message-passing step
  * One GraphNetBlock (graphphysics/models/layers.py:622-746) with hidden_size 128, nb_of_layers 4,
  * layer_norm (RMSNorm, layers.py:49-74).  Latents are fp32 [rows,128] row-major.  Products run on
