@@ -365,6 +365,17 @@ def run_b200(args):
     clk = clocks.stop() if rank == 0 else None
     e2e_steps = max(2, min(args.steps, 5))
     ms_e2e, _, _ = timed(e2e_fn, e2e_steps, 2)
+    # forward only (inference / rollout step, SURVEY.md 8(d) "also report"): no_grad, ping-pong buffers, graph replay
+    def fwd_only():
+        with torch.no_grad():
+            return model(Graph(x=x0, edge_index=ei, edge_attr=e0))
+    fwd_fn = fwd_only
+    if graphed:
+        try:
+            fwd_fn = proc.CapturedStep(fwd_only)
+        except Exception:
+            fwd_fn = fwd_only
+    ms_fwd, _, _ = timed(fwd_fn, args.steps, 3)
 
     if rank == 0:
         hbm, tf, which = peaks()
@@ -387,6 +398,8 @@ def run_b200(args):
             "gpu_launches": launches,
             "launch_mode": "cuda_graph_replay" if graphed else "eager",
             "ms_per_step_eager": ms_eager / args.steps,
+            "forward_only": {"value": world * E / (ms_fwd / args.steps * 1e-3), "unit": "edges/s",
+                             "ms_per_step": ms_fwd / args.steps, "what": "15 blocks forward under no_grad"},
             "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "edge_bwd_kernel", "achieved": ach, "peak": hbm, "unit": "GB/s",
                          "frac": ach / hbm, "traffic": EDGE_BWD_DRAM_BYTES_NCU if copies == 32 else None,

@@ -100,3 +100,113 @@ extern "C" int mgn_selftest_umma(const void* a, const void* b, float* d, int a_c
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
+
+// ---------------------------------------------------------------------------------
+// Probe 2 (round-2 groundwork): variants the fused kernels do not use yet.
+//   m = 64            : UMMA M = 64 (which TMEM lanes receive the 64 accumulator rows)
+//   a_tmem = 1 / 2    : A operand read from TENSOR MEMORY (tcgen05.mma [d], [a], b-desc): the A tile is written with
+//                       tcgen05.st, 16 K-elements = 8 32-bit columns per k-step; 1 = element 2c in the low half of
+//                       column c, 2 = in the high half
+// d receives all 128 TMEM lanes x n columns, whatever the shape, so the host can see where rows land.
+struct Selftest2Args {
+  const __half* a;   // [128][128] row-major, K-major operand
+  const __half* b;   // [128][128] row-major, K-major operand
+  float* d;          // [128][n]
+  int n, ksteps, m, a_tmem;
+};
+
+__device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__global__ void __launch_bounds__(128, 1) umma_selftest2_kernel(Selftest2Args p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tileA = smem;
+  uint8_t* tileB = smem + 32768;
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 128 * 128; i += 128) {
+    int r = i >> 7, c = i & 127;
+    *reinterpret_cast<__half*>(tileA + tile_off(128, r, c)) = p.a[i];
+    *reinterpret_cast<__half*>(tileB + tile_off(128, r, c)) = p.b[i];
+  }
+  if (warp == 0) tmem_alloc<256>(&tmem_slot);
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    mbar_init_fence();
+  }
+  fence_async_smem();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t a_col0 = 128;            // A operand columns [128, 192)
+  // clear the accumulator lanes so that untouched lanes read as zero
+  {
+    uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int c = 0; c < 128; c += 8) tmem_st8(lane_base + c, z);
+    tmem_st_wait();
+  }
+  if (p.a_tmem) {   // thread t owns TMEM lane t = row t of A
+    for (int ks = 0; ks < 8; ++ks) {
+      uint32_t r[8];
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t lo = __half_as_ushort(p.a[tid * 128 + ks * 16 + 2 * c]);
+        const uint32_t hi = __half_as_ushort(p.a[tid * 128 + ks * 16 + 2 * c + 1]);
+        r[c] = p.a_tmem == 1 ? (lo | (hi << 16)) : (hi | (lo << 16));
+      }
+      tmem_st8(lane_base + a_col0 + ks * 8, r);
+    }
+    tmem_st_wait();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  if (tid == 0) {
+    const uint32_t idesc = make_idesc(p.m, p.n, 0, 0);
+    for (int ks = 0; ks < p.ksteps; ++ks) {
+      const uint64_t bd = desc_kmajor(smem_u32(tileB), 128, ks);
+      if (p.a_tmem) mma_f16_ts(tmem, tmem + a_col0 + ks * 8, bd, idesc, ks > 0 ? 1u : 0u);
+      else mma_f16(tmem, desc_kmajor(smem_u32(tileA), 128, ks), bd, idesc, ks > 0 ? 1u : 0u);
+    }
+    mma_commit(&bar);
+  }
+  mbar_wait(&bar, 0);
+  fence_after_sync();
+  for (int c0 = 0; c0 < p.n; c0 += 16) {
+    float v[16];
+    tmem_ld16(lane_base + c0, v);
+    tmem_ld_wait();
+    for (int j = 0; j < 16; ++j) p.d[(size_t)tid * p.n + c0 + j] = v[j];
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<256>(tmem);
+}
+
+extern "C" int mgn_selftest_umma2(const void* a, const void* b, float* d, int n, int ksteps, int m, int a_tmem,
+                                  void* stream) {
+  MGN_CHECK_ARG(a && b && d, "selftest2: null pointer");
+  MGN_CHECK_ARG(n >= 16 && n <= 128 && n % 16 == 0 && ksteps >= 1 && ksteps <= 8, "selftest2: n / ksteps");
+  MGN_CHECK_ARG((m == 64 || m == 128) && a_tmem >= 0 && a_tmem <= 2, "selftest2: m / a_tmem");
+  Selftest2Args p{(const __half*)a, (const __half*)b, d, n, ksteps, m, a_tmem};
+  const int smem = 65536 + 1024;
+  MGN_CUDA(cudaFuncSetAttribute(umma_selftest2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  umma_selftest2_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}

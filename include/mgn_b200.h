@@ -173,6 +173,9 @@ int mgn_debug_set_timeline(long long* buf, int cap);
 int mgn_selftest_umma(const void* a, const void* b, float* d, int a_cols, int b_cols, int a_mn, int b_mn,
                       int n, int ksteps, int b_col0, int use_ones, int repeat, int lbo_a, int sbo_a,
                       int lbo_b, int sbo_b, void* stream);
+/* probe of shapes the fused kernels do not use yet: UMMA M = 64 (m), A operand from tensor memory (a_tmem 1/2 =
+ * packing of two fp16 per 32-bit column); d [128 TMEM lanes][n] (tools/umma_probe2.py) */
+int mgn_selftest_umma2(const void* a, const void* b, float* d, int n, int ksteps, int m, int a_tmem, void* stream);
 
 #ifdef __cplusplus
 }

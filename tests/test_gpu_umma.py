@@ -56,3 +56,37 @@ def run_case(cfg, lbo_a=-1, sbo_a=-1, lbo_b=-1, sbo_b=-1, seed=0):
 def test_umma_case(name):
     err = run_case(CASES[name])
     assert err < 2e-3, f"{name}: rel max err {err}"
+
+
+def _run2(n, ksteps, m, a_tmem, seed=0):
+    from graph_physics_b200 import _lib as L
+    L.require_device()
+    g = torch.Generator().manual_seed(seed)
+    a = (torch.randn(128, 128, generator=g) * 0.5).half()
+    b = (torch.randn(128, 128, generator=g) * 0.5).half()
+    d = torch.full((128, n), float("nan"), device="cuda")
+    ad, bd = a.cuda(), b.cuda()
+    L.check(L.lib().mgn_selftest_umma2(L.p(ad), L.p(bd), L.p(d), n, ksteps, m, a_tmem, L.stream()))
+    torch.cuda.synchronize()
+    K = 16 * ksteps
+    return d.cpu().double(), a.double()[:, :K] @ b.double()[:n, :K].t()
+
+
+def test_a_operand_from_tensor_memory():
+    """tcgen05.mma with the A operand in TMEM (written by tcgen05.st): row r = TMEM lane r, one k-step = 8 32-bit
+    columns, K element 2c in the LOW half of column c.  Not used by the fused kernels yet."""
+    for n, ks in ((128, 8), (64, 4)):
+        d, want = _run2(n, ks, 128, 1)
+        assert float((d - want).abs().max() / want.abs().max()) < 2e-3
+    d, want = _run2(128, 8, 128, 2)                     # the other packing is wrong, so the probe is discriminating
+    assert float((d - want).abs().max() / want.abs().max()) > 0.1
+
+
+def test_m64_accumulator_lanes():
+    """UMMA M = 64 (cta_group::1): accumulator row r lands in TMEM lane 32 * (r // 16) + r % 16; the other lanes
+    are not written."""
+    d, want = _run2(128, 8, 64, 0)
+    lanes = [32 * (r // 16) + r % 16 for r in range(64)]
+    assert float((d[lanes] - want[:64]).abs().max() / want.abs().max()) < 2e-3
+    rest = [i for i in range(128) if i not in lanes]
+    assert float(d[rest].abs().max()) == 0.0
