@@ -1,0 +1,124 @@
+"""The encoder MLPs of EncodeProcessDecode (`nodes_encoder`, `edges_encoder`: build_mlp(in, 128, 128) = 4 Linear +
+ReLU + RMSNorm, graphphysics/models/processors.py:72-84, layers.py:77-113) on the fused node kernels.
+
+SURVEY.md 8(f) N1.  The node kernel computes  out = x + RMSNorm(MLP([x | a]))  with a 256-wide first layer.  An
+encoder is the same chain without the residual and with a narrow input, so it runs as
+    x = 0,  a = features zero-padded to 128 columns,  W1' = [0 | W1 zero-padded]
+through `mgn_node_fwd`, and its backward through `mgn_node_bwd` + `mgn_node_wgrad1` (dW1 is the [:, 128:128+in] slice
+of the 256-wide first-layer gradient).  No new kernel: three launches forward+backward instead of ~25 eager ones, hidden
+activations kept in fp16.  The zero half costs redundant tensor work and the read of a zero matrix.
+
+Numerics are those of the processor: fp16 tensor-core operands (the input features are rounded to fp16: they are
+normalised, O(1) quantities), fp32 accumulation, fp32 RMSNorm; the gradient is pre-scaled by a power of two.
+"""
+from __future__ import annotations
+
+from typing import Sequence
+
+import torch
+
+from . import _lib as L
+from . import ops
+
+H = ops.H
+# tests only: when True, the fp16 hidden activations of the last training-mode forward stay reachable here, so a test
+# can differentiate the oracle through the same ReLU active set as the kernels
+DEBUG_KEEP_SAVES = False
+LAST_SAVES = None
+
+
+def _pad_cols(t: torch.Tensor, cols: int) -> torch.Tensor:
+    out = torch.zeros((t.shape[0], cols), dtype=torch.float32, device=t.device)
+    out[:, :t.shape[1]] = t
+    return out
+
+
+class _EncoderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, feat, w1, b1, w2, b2, w3, b3, w4, b4, scale):
+        L.require_device(feat)
+        if feat.dim() != 2 or feat.shape[1] > H:
+            raise ValueError(f"fused encoder: input width must be <= {H}, got {tuple(feat.shape)}")
+        if tuple(w1.shape) != (H, feat.shape[1]) or any(tuple(w.shape) != (H, H) for w in (w2, w3, w4)):
+            raise ValueError("fused encoder supports build_mlp(in, 128, 128, nb_of_layers=4, layer_norm=True) only")
+        M, fin = feat.shape
+        dev = feat.device
+        a = _pad_cols(feat.detach().float(), H)                         # the "aggr" half of the node kernel's input
+        xz = torch.zeros((M, H), dtype=torch.float32, device=dev)
+        w1p = torch.zeros((H, 2 * H), dtype=torch.float32, device=dev)
+        w1p[:, H:H + fin] = w1.detach()
+        zero_e = [torch.zeros((H, 3 * H), device=dev)] + [torch.zeros((H, H), device=dev) for _ in range(3)]
+        packed = ops.pack_block(zero_e, [w1p, w2.detach(), w3.detach(), w4.detach()])
+        need_grad = any(ctx.needs_input_grad)
+        sv = tuple(torch.empty((M, H), dtype=torch.float16, device=dev) for _ in range(3)) if need_grad else None
+        out = torch.empty((M, H), dtype=torch.float32, device=dev)
+        if M > 0:
+            ops.node_fwd(xz, a, packed, b1.detach().contiguous(), b2.detach().contiguous(), b3.detach().contiguous(),
+                         b4.detach().contiguous(), scale.detach().contiguous(), x_out=out, saves=sv)
+        if need_grad:
+            if DEBUG_KEEP_SAVES:
+                global LAST_SAVES
+                LAST_SAVES = sv
+            ctx.a, ctx.xz, ctx.sv, ctx.packed, ctx.fin = a, xz, sv, packed, fin
+            ctx.b4, ctx.scale = b4.detach().contiguous(), scale.detach().contiguous()
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        a, xz, sv, packed, fin = ctx.a, ctx.xz, ctx.sv, ctx.packed, ctx.fin
+        M = a.shape[0]
+        dev = a.device
+        grads = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
+        g_feat = None
+        if M > 0:
+            amax = g.detach().abs().max()
+            s = torch.exp2(torch.floor(torch.log2(64.0 / amax.clamp_min(1e-30)))).clamp(2.0 ** -100, 2.0 ** 100)
+            gs = (g.detach() * s).contiguous()
+            _, g_a, dz1 = ops.node_bwd(gs, sv, packed, ctx.b4, ctx.scale, grads)
+            ops.node_wgrad1(dz1, xz, a, grads)
+            grads.mul_(1.0 / s)
+            if ctx.needs_input_grad[0]:
+                g_feat = g_a[:, :fin] * (1.0 / s)
+        elif ctx.needs_input_grad[0]:
+            g_feat = torch.zeros((0, fin), dtype=torch.float32, device=dev)
+        v = ops.split_grad_block(grads)
+        need = ctx.needs_input_grad
+        names = ["node_block.0.weight", "node_block.0.bias", "node_block.2.weight", "node_block.2.bias",
+                 "node_block.4.weight", "node_block.4.bias", "node_block.6.weight", "node_block.6.bias",
+                 "node_block.7.scale"]
+        out = [g_feat]
+        for i, nme in enumerate(names):
+            if not need[1 + i]:
+                out.append(None)
+            elif i == 0:
+                out.append(v[nme][:, H:H + fin].contiguous())
+            else:
+                out.append(v[nme])
+        return tuple(out)
+
+
+def supported(mlp: torch.nn.Module, in_features: int) -> bool:
+    """True if `mlp` is build_mlp(in <= 128, 128, 128, nb_of_layers=4, layer_norm=True)."""
+    mods = list(mlp)
+    if len(mods) != 8 or in_features > H:
+        return False
+    lin = [mods[i] for i in (0, 2, 4, 6)]
+    if not all(isinstance(m, torch.nn.Linear) for m in lin) or not hasattr(mods[7], "scale"):
+        return False
+    if getattr(mods[7], "bias", False) or getattr(mods[7], "p", -1.0) >= 0.0:
+        return False
+    return (tuple(lin[0].weight.shape) == (H, in_features)
+            and all(tuple(m.weight.shape) == (H, H) for m in lin[1:]) and all(m.bias is not None for m in lin))
+
+
+def encoder_params(mlp: torch.nn.Module) -> Sequence[torch.Tensor]:
+    return [mlp[0].weight, mlp[0].bias, mlp[2].weight, mlp[2].bias, mlp[4].weight, mlp[4].bias, mlp[6].weight,
+            mlp[6].bias, mlp[7].scale]
+
+
+def run_encoder(mlp: torch.nn.Module, feat: torch.Tensor) -> torch.Tensor:
+    """`mlp(feat)` for an encoder-shaped build_mlp module on the fused kernels (raises if the shape is not supported
+    or the tensors are not on an sm_100 device: no eager fallback here -- the caller chooses)."""
+    if not supported(mlp, feat.shape[1]):
+        raise ValueError("fused encoder: unsupported MLP shape")
+    return _EncoderFn.apply(feat, *encoder_params(mlp))

@@ -8,7 +8,9 @@ so `get_model` (training/parse_parameters.py:91-101), `Simulator` (models/simula
 `forward(graph)` reads `graph.x`, `graph.edge_attr`, `graph.edge_index` only (duck typed: a
 torch_geometric `Data` / `Batch` or any object with those attributes).  The 15-block hot loop
 (`processors.py:130-131`) runs as one fused autograd node on the sm_100a kernels
-(graph_physics_b200.processor); encoder and decoder MLPs are plain torch modules.
+(graph_physics_b200.processor); the two encoder MLPs run on the fused node kernels
+(graph_physics_b200.encoder) when their shape allows (input width <= 128) and
+`fused_encoders` is left on; the decoder (no RMSNorm, 2-3 outputs, N rows only) is a plain torch module.
 """
 from __future__ import annotations
 
@@ -17,6 +19,7 @@ from types import SimpleNamespace
 import torch
 import torch.nn as nn
 
+from .. import encoder as _enc
 from .. import processor as _proc
 from .layers import GraphNetBlock, block_param_list, build_mlp
 
@@ -32,6 +35,8 @@ class Graph(SimpleNamespace):
 
 
 class EncodeProcessDecode(nn.Module):
+    fused_encoders = True      # set False (class or instance) to run the encoders as eager torch modules
+
     def __init__(self, message_passing_num: int, node_input_size: int, edge_input_size: int, output_size: int,
                  hidden_size: int = 128, only_processor: bool = False, num_mixture_components: int = 0,
                  temperature: float = None, use_diagonal: bool = True):
@@ -56,13 +61,18 @@ class EncodeProcessDecode(nn.Module):
         self.processor_list = nn.ModuleList(
             [GraphNetBlock(hidden_size=hidden_size) for _ in range(message_passing_num)])
 
+    def _encode(self, mlp, feat):
+        if self.fused_encoders and feat.is_cuda and feat.dim() == 2 and _enc.supported(mlp, feat.shape[1]):
+            return _enc.run_encoder(mlp, feat)
+        return mlp(feat)
+
     def forward(self, graph) -> torch.Tensor:
         edge_index = graph.edge_index
         if self.only_processor:
             x, edge_attr = graph.x, graph.edge_attr
         else:
-            x = self.nodes_encoder(graph.x)
-            edge_attr = self.edges_encoder(graph.edge_attr)
+            x = self._encode(self.nodes_encoder, graph.x)
+            edge_attr = self._encode(self.edges_encoder, graph.edge_attr)
         if len(self.processor_list) > 0:
             for block in self.processor_list:
                 block.check_supported()
