@@ -414,7 +414,7 @@ def run_b200(args):
                               "algorithmic_GB_per_step": step_bytes / 1e9, "algorithmic_TFLOP_per_step": step_flops / 1e12,
                               "edge_bwd_share_of_step": edge_bwd_ms * STEPS_MP / ms_step},
         }
-        if args.cpu_seconds > 0:
+        if args.cpu_seconds > 0 and world == 1:      # the CPU leg runs at N=1 only (rank 0 would hold N-1 ranks at a barrier)
             threads = os.cpu_count() or 1
             eps, t, e_cpu = cpu_oracle_run(args.cpu_copies, 2, 1, threads)
             line["cpu_baseline"] = {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port",
