@@ -70,12 +70,17 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     mbar_init(&mbar, 1);
     mbar_init_fence();
   }
-  if (m.warp == 0) tmem_alloc<128>(&tmem_slot);
+  // edge kernel: the hidden activations never touch shared memory -- each epilogue writes its fp16 row chunk into 64
+  // TMEM columns next to the accumulator and the next product reads its A operand from there
+  constexpr uint32_t TMEM_COLS = EDGE ? 256 : 128;
+  if (m.warp == 0) tmem_alloc<TMEM_COLS>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem_acc = tmem_slot;
   const uint32_t taddr = tmem_acc + m.lane_off + m.c0;
+  const uint32_t tmem_a = tmem_acc + 128;
+  const uint32_t taddr_a = tmem_a + m.lane_off + (m.c0 >> 1);
 
   if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, W_BYTES);
@@ -94,6 +99,11 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   };
   auto tile_ready = [&]() {
     fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+  };
+  auto acts_ready = [&]() {       // the TMEM-resident activations of every warp are written
+    tmem_st_wait();
     fence_before_sync();
     __syncthreads();
   };
@@ -205,20 +215,20 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[8 * j + i], 0.f);
       }
-      store_row_chunk_f16(sA, 128, m.row, m.c0, v);
-      if (p.save_h1 != nullptr && rvalid) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4*>(p.save_h1 + grow * H + m.c0 + 8 * j) =
-              *reinterpret_cast<const uint4*>(sA + tile_off(128, m.row, m.c0 + 8 * j));
-      }
+      store_row_chunk_tmem(taddr_a, v, rvalid ? p.save_h1 : nullptr, grow, m.c0);
     } else {
       float4 bb[8];
       load_vec32(p.b1, m.c0, bb);
       mma_wait();
       epi_bias_relu_q(taddr, bb, sA, m, rvalid ? p.save_h1 : nullptr, grow);
     }
-    tile_ready();
+    if (EDGE) {
+      // sA is dead from here on: the next tile's operand image can come in now, three products ahead of its use
+      if (img_in && m.tid == 0 && tile + gridDim.x < num_tiles) issue_image(tile + gridDim.x);
+      acts_ready();
+    } else {
+      tile_ready();
+    }
     tl.stamp();   // 3 layer-1 epilogue done (edge) 
     // L2 prefetch of the next tile's rows (one 128-byte line per thread and stream); its indices
     // were requested a whole layer ago
@@ -241,7 +251,8 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     for (int layer = 1; layer < 3; ++layer) {
       if (m.tid == 0) {
         fence_after_sync();
-        umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        if (EDGE) umma_tile_ts(tmem_acc, tmem_a, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        else umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
         mma_commit(&mbar);
       }
       float4 bb[8];
@@ -249,15 +260,21 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       mma_wait();
       tl.stamp();   // 4, 6 product done
       __half* save = layer == 1 ? p.save_h2 : p.save_h3;
-      epi_bias_relu_q(taddr, bb, sA, m, rvalid ? save : nullptr, grow);
-      tile_ready();
+      if (EDGE) {
+        epi_bias_relu_tmem_q(taddr, taddr_a, bb, m, rvalid ? save : nullptr, grow);
+        acts_ready();
+      } else {
+        epi_bias_relu_q(taddr, bb, sA, m, rvalid ? save : nullptr, grow);
+        tile_ready();
+      }
       tl.stamp();   // 5, 7 epilogue done
     }
 
     // ---- layer 4 + RMSNorm + residual (+ segmented sum over receivers)
     if (m.tid == 0) {
       fence_after_sync();
-      umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+      if (EDGE) umma_tile_ts(tmem_acc, tmem_a, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+      else umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
       mma_commit(&mbar);
     }
     float4 old[8];
@@ -269,7 +286,6 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     mma_wait();
-    if (img_in && m.tid == 0 && tile + gridDim.x < num_tiles) issue_image(tile + gridDim.x);   // sA is dead
     tl.stamp();   // 8 layer-4 product done (residual rows requested before)
     {
       float v[32];
@@ -342,7 +358,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
 
   fence_before_sync();
   __syncthreads();
-  if (m.warp == 0) tmem_dealloc<128>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<TMEM_COLS>(tmem_slot);
 }
 
 // ---------------------------------------------------------------------------------

@@ -79,6 +79,36 @@ __device__ __forceinline__ void epi_bias_relu_q(uint32_t taddr, const float4 (&b
   }
 }
 
+// 32 fp32 of one row -> 16 packed fp16 pairs -> this thread's 16 columns of a TMEM-resident A operand (tc05.cuh
+// mma_f16_ts: K element 2c in the low half of column c); optional fp16 copy of the row chunk to save[grow, c0..c0+32)
+__device__ __forceinline__ void store_row_chunk_tmem(uint32_t taddr_a, const float (&v)[32], __half* save,
+                                                     long long grow, int c0) {
+  uint32_t r[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = pack_h2(v[2 * j], v[2 * j + 1]);
+  tmem_st16(taddr_a, r);
+  if (save != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<uint4*>(save + grow * H + c0 + 8 * j) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+  }
+}
+// hidden layer kept in tensor memory: A-operand columns <- fp16(relu(acc + bias))
+__device__ __forceinline__ void epi_bias_relu_tmem_q(uint32_t taddr, uint32_t taddr_a, const float4 (&bb)[8],
+                                                     const Map& m, __half* save, long long grow) {
+  float v[32];
+  tmem_ld32(taddr, v);
+  tmem_ld_wait();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
+    v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
+    v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
+    v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
+  }
+  store_row_chunk_tmem(taddr_a, v, save, grow, m.c0);
+}
+
 // ReLU backward in place: tile holds h = relu(z); overwrite with fp16(acc * [h > 0])
 __device__ __forceinline__ void epi_relu_mask_q(uint32_t taddr, uint8_t* tile, const Map& m) {
   float v[32], h[32];

@@ -171,6 +171,28 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// registers -> TMEM: the calling warp writes 16 consecutive 32-bit columns of its own 32 lanes
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// A operand from tensor memory (pinned by tests/test_gpu_umma.py::test_a_operand_from_tensor_memory): row r of A is
+// TMEM lane r; one k-step (16 fp16) is 8 consecutive 32-bit columns; K element 2c sits in the LOW half of column c.
+__device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // sub-block barrier over `nthreads` threads (ids 1..15; 0 is __syncthreads)
 __device__ __forceinline__ void named_bar(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -192,6 +214,17 @@ __device__ __forceinline__ void umma_tile(uint32_t tmem_d, uint32_t a_saddr, uin
     uint64_t ad = a_mn ? desc_mnmajor(a_saddr, a_rows, ks) : desc_kmajor(a_saddr, a_rows, ks);
     uint64_t bd = b_mn ? desc_mnmajor(b_saddr, b_rows, ks, b_col0) : desc_kmajor(b_saddr, b_rows, ks);
     mma_f16(tmem_d, ad, bd, idesc, (ks > 0) ? 1u : accumulate_first);
+  }
+}
+
+// Same product with the A operand (128 rows x 16*ksteps fp16) in tensor memory at column `tmem_a`.
+__device__ __forceinline__ void umma_tile_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_saddr, uint32_t b_rows,
+                                             uint32_t b_mn, uint32_t b_col0, uint32_t N, uint32_t ksteps,
+                                             uint32_t accumulate_first) {
+  const uint32_t idesc = make_idesc(128, N, 0, b_mn);
+  for (uint32_t ks = 0; ks < ksteps; ++ks) {
+    uint64_t bd = b_mn ? desc_mnmajor(b_saddr, b_rows, ks, b_col0) : desc_kmajor(b_saddr, b_rows, ks);
+    mma_f16_ts(tmem_d, tmem_a + ks * 8, bd, idesc, (ks > 0) ? 1u : accumulate_first);
   }
 }
 
