@@ -120,6 +120,13 @@ int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap,
                  const void* packed, const float* b2, const float* b3, const float* b4,
                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
                  const void* e16_in, void* e16_next, int out_in_csr_order, void* stream);
+/* The same edge update for steps 1..K-1 of the processor loop (operand tile images of e_in available, rows in CSR
+ * order): two tiles in flight per CTA, hidden activations in tensor memory (csrc/edge_fwd_pp.cu).  Results equal
+ * mgn_edge_fwd(rowmap = NULL, e16_in) up to the summation order of the per-warp aggregation partials. */
+int mgn_edge_fwd_pp(int64_t E, int64_t N, const float* e_in, const void* e16_in, float* e_out, void* e16_next,
+                    const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                    const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
+                    void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
  * fp16, optional) are the hidden activations mgn_node_bwd needs. */
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,

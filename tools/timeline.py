@@ -29,6 +29,8 @@ P = ops.p_fwd(x, packed, b[0])
 aggr = torch.empty(N, 128, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
 cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19
+if which == "edge_pp":
+    cap = 6 * 21
 ge_in = torch.randn(E, 128, device=dev)
 g_aggr = torch.randn(N, 128, device=dev)
 ge_out = torch.empty_like(e)
@@ -43,6 +45,9 @@ def run():
     if which == "edge_bwd":
         ops.edge_bwd(None, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
                      dz16=dz16, e16=e16, inplace=True)
+    elif which == "edge_pp":
+        ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr,
+                     e16_in=e16, e16_next=dz16)
     elif which == "edge":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
     else:
@@ -63,6 +68,11 @@ per = 11
 if which == "edge_bwd":
     names = ["top", "R1", "R2+R3", "R4+norm", "D4..D2", "D1+g'", "g_e", "next"]
     per = 8
+if which == "edge_pp":
+    names = ["O3(k-1)", "O1(k)", "O4(k-1)", "O2(k)", "O5(k-1)", "O0(k+1)"]
+    per = 6
+if which == "edge_pp":
+    pass
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
