@@ -18,6 +18,7 @@ OUT = os.path.join(HERE, "libmgn_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+FLAGS += os.environ.get("MGN_NVCC_EXTRA", "").split()   # developer experiments, e.g. -DMGN_FINE_TL
 
 
 def _sources():

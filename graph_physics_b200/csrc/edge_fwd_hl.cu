@@ -1,0 +1,374 @@
+// edge_fwd_hl.cu -- the edge forward kernel of steps 1..K-1 with the residual stream kept as TWO fp16 tile images:
+// hi = fp16(e) (the layer-1 operand tile, which the edge backward also recomputes from) and lo = fp16(e - hi).
+//
+// Same arithmetic as mlp_fwd_kernel<true> in mlp_fwd.cu (GraphNetBlock.forward, graphphysics/models/layers.py:687-698:
+// edge_block on [e | x[col] | x[row]], RMSNorm, residual, sum at the receivers), except that the residual add reads
+// e = hi + lo (exact in fp32, >= 21 significant bits of the fp32 stream) instead of the fp32 rows.  What this buys:
+//   * the edge stream moves ONLY by bulk copies -- hi / lo tiles in, hi / lo tiles out, 4 x 32 KB per 128 edges instead
+//     of 2 x 64 KB fp32 rows + 2 x 32 KB images -- so no thread waits on a load of the stream or drains its stores;
+//   * everything after the last product runs in the accumulator's own (row, 32-column) mapping: no fp32 staging tile,
+//     no second pass over the rows; the segmented sum by receiver is a shuffle scan over the 32 rows of a warp
+//     (receivers are sorted, so a segment is a run of lanes) followed by one red.add per (run, column quad);
+//   * the layer-1 product of the next tile is issued before that scan, so the tensor pipe works under it.
+// Shared memory: four weight tiles (resident), hi tile (free after layer 1: the next tile's image is requested three
+// products ahead), lo tile (updated in place), one output tile for the new hi (between tiles it stages the gathered
+// P_j rows of the next tile).  Tensor memory: accumulator (128
+// columns), the hidden activations as the next product's A operand (64), the parked hi chunk of every thread (64).
+#include <algorithm>
+
+#include "mlp_v2.cuh"
+#include "mlp_fwd_abi.cuh"
+
+using namespace mgn;
+
+struct EdgeHLParams {
+  long long E;
+  const __half* hi_in;      // tile images of fp16(e_in)
+  const __half* lo_in;      // tile images of fp16(e_in - hi)
+  __half* hi_out;           // tile images of e_out, or null
+  __half* lo_out;           // or null
+  float* e_out;             // [E,128] fp32, CSR order, or null (only the last step needs the rows)
+  const __half* P;          // [N,256] fp16
+  const int32_t* senders;
+  const int32_t* receivers;
+  float* aggr;              // [N,128] fp32, zero on entry
+  const __half* W;          // We, W2, W3, W4 tiles
+  const float* b2;
+  const float* b3;
+  const float* b4;
+  const float* scale;
+  long long* dbg;
+  int dbg_cap;
+};
+
+__global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  check_smem_alignment(smem);
+  uint8_t* sW = smem;                          // 4 x 32 KB
+  uint8_t* sHi = smem + 4 * TILE_BYTES;
+  uint8_t* sLo = smem + 5 * TILE_BYTES;
+  uint8_t* sOut = smem + 6 * TILE_BYTES;
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 7 * TILE_BYTES);
+  uint64_t& wbar = tail->bar[0];
+  uint64_t& mbar = tail->bar[1];
+  uint64_t& bar_hi = tail->bar[2];
+  uint64_t& bar_lo = tail->bar[3];
+  uint32_t& tmem_slot = tail->tmem_slot;
+  const Map m = make_map();
+
+  if (m.tid == 0) {
+    mbar_init(&wbar, 1);
+    mbar_init(&mbar, 1);
+    mbar_init(&bar_hi, 1);
+    mbar_init(&bar_lo, 1);
+    mbar_init_fence();
+  }
+  if (m.warp == 0) tmem_alloc<256>(&tmem_slot);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_acc = tmem_slot;
+  const uint32_t taddr = tmem_acc + m.lane_off + m.c0;
+  const uint32_t tmem_a = tmem_acc + 128;
+  const uint32_t taddr_a = tmem_a + m.lane_off + (m.c0 >> 1);
+  const uint32_t taddr_park = tmem_acc + 192 + m.lane_off + (m.c0 >> 1);
+  const uint32_t sW_u32 = smem_u32(sW), sHi_u32 = smem_u32(sHi);
+
+  const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
+  const long long first = blockIdx.x, stride = gridDim.x;
+  const int K = first < num_tiles ? (int)((num_tiles - first + stride - 1) / stride) : 0;
+  auto tile_of = [&](int k) -> long long { return first + (long long)k * stride; };
+  const uint64_t pol_stream = policy_evict_first();
+  const uint64_t pol_keep = policy_evict_last();
+
+  if (m.tid == 0) {
+    mbar_arrive_expect_tx(&wbar, 4 * TILE_BYTES);
+    for (uint32_t o = 0; o < 4 * TILE_BYTES; o += TILE_BYTES)
+      bulk_g2s(sW + o, reinterpret_cast<const uint8_t*>(p.W) + o, TILE_BYTES, &wbar);
+  }
+  auto issue_hi = [&](int k) {                 // thread 0
+    mbar_arrive_expect_tx(&bar_hi, TILE_BYTES);
+    bulk_g2s(sHi, reinterpret_cast<const uint8_t*>(p.hi_in) + (size_t)tile_of(k) * TILE_BYTES, TILE_BYTES, &bar_hi);
+  };
+  auto issue_lo = [&](int k) {                 // thread 0
+    mbar_arrive_expect_tx(&bar_lo, TILE_BYTES);
+    bulk_g2s(sLo, reinterpret_cast<const uint8_t*>(p.lo_in) + (size_t)tile_of(k) * TILE_BYTES, TILE_BYTES, &bar_lo);
+  };
+  uint32_t phase = 0;
+  auto mma_wait = [&]() {
+    mbar_wait(&mbar, phase);
+    phase ^= 1;
+    fence_after_sync();
+  };
+  auto acts_ready = [&]() {       // the TMEM-resident activations (and parked rows) of every warp are written
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+  };
+  // indices, requested one tile ahead: this thread's row (epilogue mapping) -> receiver; coalesced mapping (lane j < 8
+  // of warp w stands for tile row 8w + j) -> sender
+  struct Idx { int rcv, snd_c; bool ok; };
+  auto load_idx = [&](int k) -> Idx {
+    Idx ix{0, -1, false};
+    if (k >= K) return ix;
+    const long long r0 = tile_of(k) * TILE_ROWS;
+    if (r0 + m.row < p.E) {
+      ix.rcv = __ldg(p.receivers + r0 + m.row);
+      ix.ok = true;
+    }
+    const long long g = r0 + m.warp * 8 + (m.lane & 7);
+    if (g < p.E) ix.snd_c = __ldg(p.senders + g);
+    return ix;
+  };
+  // P_i[receiver]: read directly by the row's thread (rows of one receiver are consecutive, so a warp's request
+  // touches a handful of lines).  P_j[sender] is a true gather: asynchronous copies into the idle output tile, half
+  // a warp per 256-byte row, picked up from there by the row's thread before the tile is needed for the new image.
+  uint4 pi[4], pj[4];
+  auto load_pi = [&](const Idx& ix) {
+    const __half* Pi = p.P + (long long)ix.rcv * 256 + m.c0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) pi[j] = ix.ok ? ld_u4_hint(Pi + 8 * j, pol_keep) : make_uint4(0, 0, 0, 0);
+  };
+  const uint32_t sOut_u32 = smem_u32(sOut);
+  auto stage_pj = [&](const Idx& ix) {
+    const int hw = m.lane >> 4, q = m.lane & 15;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int sn = __shfl_sync(0xffffffffu, ix.snd_c, 2 * i + hw);
+      cp_async16(sOut_u32 + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q),
+                 p.P + (long long)(sn >= 0 ? sn : 0) * 256 + 128 + 8 * q, sn >= 0 ? 16u : 0u, pol_keep);
+    }
+  };
+  auto fetch_pj = [&]() {                      // after cp_async_wait_all() and a barrier
+#pragma unroll
+    for (int j = 0; j < 4; ++j) pj[j] = *reinterpret_cast<const uint4*>(sOut + tile_off(128, m.row, m.c0 + 8 * j));
+  };
+  auto issue_l1 = [&](int k) {                 // thread 0: product 1 of the k-th tile of this CTA
+    mbar_wait(&bar_hi, (uint32_t)k & 1u);
+    fence_after_sync();
+    umma_tile(tmem_acc, sHi_u32, 128, 0, sW_u32, 128, 0, 0, 128, 8, 0);
+    mma_commit(&mbar);
+  };
+  Timeline tl;
+  tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
+
+  // ---- prologue: first tile's image, indices, P rows and product 1
+  Idx cur = load_idx(0);
+  Idx nxt = load_idx(1);
+  if (K > 0) {
+    if (m.tid == 0) {
+      issue_hi(0);
+      mbar_wait(&wbar, 0);
+      issue_l1(0);
+    }
+    load_pi(cur);
+    stage_pj(cur);
+    cp_async_wait_all();
+    __syncthreads();
+    fetch_pj();
+  }
+
+  for (int k = 0; k < K; ++k) {
+    tl.stamp();   // 0 tile start (product 1 in flight)
+    const long long tile = tile_of(k);
+    const long long grow = tile * TILE_ROWS + m.row;
+    const bool rvalid = cur.ok;
+    const bool has_next = k + 1 < K;
+
+    // ---- layer 1: + P_i[receiver] + P_j[sender], ReLU -> A operand in tensor memory; park this thread's hi chunk
+    mma_wait();
+    tl.stamp();   // 1 product 1 done
+    {
+      float v[32];
+      tmem_ld32(taddr, v);
+      uint32_t hr[16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint4 u = *reinterpret_cast<const uint4*>(sHi + tile_off(128, m.row, m.c0 + 8 * j));
+        hr[4 * j] = u.x; hr[4 * j + 1] = u.y; hr[4 * j + 2] = u.z; hr[4 * j + 3] = u.w;
+      }
+      tmem_st16(taddr_park, hr);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float a[8], b[8];
+        unpack8(pi[j], a);
+        unpack8(pj[j], b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
+      }
+      store_row_chunk_tmem(taddr_a, v, nullptr, 0, m.c0);
+    }
+    acts_ready();
+    if (m.tid == 0) {
+      fence_after_sync();
+      umma_tile_ts(tmem_acc, tmem_a, sW_u32 + TILE_BYTES, 128, 0, 0, 128, 8, 0);
+      mma_commit(&mbar);
+      if (has_next) issue_hi(k + 1);           // the hi tile is parked: next tile's operand image, three products ahead
+      if (k > 0) bulk_wait_read0();            // the previous tile's stores have read sLo / sOut
+      issue_lo(k);
+    }
+    tl.stamp();   // 2 layer-1 epilogue done
+
+    // ---- layers 2, 3
+#pragma unroll 1
+    for (int layer = 1; layer < 3; ++layer) {
+      float4 bb[8];
+      load_vec32(layer == 1 ? p.b2 : p.b3, m.c0, bb);
+      mma_wait();
+      epi_bias_relu_tmem_q(taddr, taddr_a, bb, m, nullptr, 0);
+      acts_ready();
+      if (m.tid == 0) {
+        fence_after_sync();
+        umma_tile_ts(tmem_acc, tmem_a, sW_u32 + (uint32_t)(layer + 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        mma_commit(&mbar);
+      }
+      // the output tile is idle (thread 0 saw the previous tile's stores leave it before this barrier): the next
+      // tile's P_j rows land there under products 3 and 4
+      if (layer == 1 && has_next) stage_pj(nxt);
+    }
+    tl.stamp();   // 3 layers 2, 3 done, product 4 issued
+
+    // ---- layer 4 + RMSNorm; residual in image + remainder form; new images
+    float y[32];
+    {
+      float4 bb[8];
+      load_vec32(p.b4, m.c0, bb);
+      mma_wait();
+      tmem_ld32(taddr, y);
+      float4 sc[8];
+      load_vec32(p.scale, m.c0, sc);
+      tmem_ld_wait();
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        y[4 * j] += bb[j].x; y[4 * j + 1] += bb[j].y; y[4 * j + 2] += bb[j].z; y[4 * j + 3] += bb[j].w;
+        ss += y[4 * j] * y[4 * j] + y[4 * j + 1] * y[4 * j + 1] + y[4 * j + 2] * y[4 * j + 2] + y[4 * j + 3] * y[4 * j + 3];
+      }
+      fence_before_sync();        // the accumulator is read: the barriers below order this before the next product 1
+      cp_async_wait_all();        // (the barriers inside row_sum4 make every thread's staged P_j rows visible)
+      ss = row_sum4(ss, tail->red, m);
+      fetch_pj();                 // next tile's P_j chunk of this thread's row; the same bytes then take the new image
+      const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        y[4 * j + 0] = sc[j].x * (y[4 * j + 0] * inv);
+        y[4 * j + 1] = sc[j].y * (y[4 * j + 1] * inv);
+        y[4 * j + 2] = sc[j].z * (y[4 * j + 2] * inv);
+        y[4 * j + 3] = sc[j].w * (y[4 * j + 3] * inv);
+      }
+    }
+    tl.stamp();   // 4 product 4 + norm done
+    {
+      uint32_t hr[16];
+      tmem_ld16(taddr_park, reinterpret_cast<float*>(hr));
+      mbar_wait(&bar_lo, (uint32_t)k & 1u);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint8_t* plo = sLo + tile_off(128, m.row, m.c0 + 8 * j);
+        const uint4 lu = *reinterpret_cast<const uint4*>(plo);
+        const uint32_t lw[4] = {lu.x, lu.y, lu.z, lu.w};
+        uint32_t hn[4], ln[4];
+        float s[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hr[4 * j + i]));
+          const float2 l = __half22float2(*reinterpret_cast<const __half2*>(&lw[i]));
+          s[2 * i] = (h.x + l.x) + y[8 * j + 2 * i];
+          s[2 * i + 1] = (h.y + l.y) + y[8 * j + 2 * i + 1];
+          hn[i] = pack_h2(s[2 * i], s[2 * i + 1]);
+          const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hn[i]));
+          ln[i] = pack_h2(s[2 * i] - hf.x, s[2 * i + 1] - hf.y);
+          if (!rvalid) { hn[i] = 0u; ln[i] = 0u; }     // rows past the end: zeros in both images
+        }
+        *reinterpret_cast<uint4*>(sOut + tile_off(128, m.row, m.c0 + 8 * j)) = make_uint4(hn[0], hn[1], hn[2], hn[3]);
+        *reinterpret_cast<uint4*>(plo) = make_uint4(ln[0], ln[1], ln[2], ln[3]);
+        if (p.e_out != nullptr && rvalid) st_f8_hint(p.e_out + grow * H + m.c0 + 8 * j, s, pol_stream);
+      }
+    }
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+    tl.stamp();   // 5 new images staged
+    if (m.tid == 0) {
+      if (p.hi_out != nullptr) {
+        bulk_s2g(reinterpret_cast<uint8_t*>(p.hi_out) + (size_t)tile * TILE_BYTES, sOut, TILE_BYTES, pol_stream);
+        bulk_s2g(reinterpret_cast<uint8_t*>(p.lo_out) + (size_t)tile * TILE_BYTES, sLo, TILE_BYTES, pol_stream);
+      }
+      bulk_commit();
+      if (has_next) issue_l1(k + 1);           // every thread has read the accumulator: next tile's product 1
+    }
+    tl.stamp();   // 6 stores + next product 1 issued
+    // ---- next tile's indices / P rows, then the segmented sum of y over the receivers (sorted: runs of lanes)
+    const int key = rvalid ? cur.rcv : -1 - m.lane;     // rows past the end never join a run
+    cur = nxt;
+    if (has_next) load_pi(cur);
+    nxt = load_idx(k + 2);
+    tl.stamp();   // 7 next P rows requested
+    {
+#pragma unroll 1
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, key, d);
+        const bool same = m.lane >= d && up == key;
+        if (!__any_sync(0xffffffffu, same)) break;       // no run reaches back d lanes (nor further)
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float t = __shfl_up_sync(0xffffffffu, y[c], d);
+          y[c] += same ? t : 0.f;
+        }
+      }
+      tl.stamp();   // 8 scan done
+      const int dn = __shfl_down_sync(0xffffffffu, key, 1);
+      if (rvalid && (m.lane == 31 || dn != key)) {       // last lane of a run holds its sum
+        float* dst = p.aggr + (long long)key * H + m.c0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          red_add_f4_hint(dst + 4 * j, make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]), pol_keep);
+      }
+    }
+    tl.stamp();   // 9 aggregation issued
+  }
+  if (K == 0 && m.tid == 0) mbar_wait(&wbar, 0);    // never exit with the weight copy in flight
+  if (m.tid == 0) bulk_wait0();
+
+  fence_before_sync();
+  __syncthreads();
+  if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
+}
+
+static constexpr int EDGE_HL_SMEM = 7 * 32768 + TAIL_BYTES;
+
+// Steps 1..K-1 of the processor loop with the edge stream as image + remainder (see the header of this file).
+// hi_out / lo_out (both or neither) receive the images of e_out; e_out (fp32 rows, CSR order) is optional.
+// Replaces the same reference lines as mgn_edge_fwd (graphphysics/models/layers.py:687-698).
+extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
+                               float* e_out, const void* P, const int32_t* senders, const int32_t* receivers,
+                               float* aggr, const void* packed, const float* b2, const float* b3, const float* b4,
+                               const float* scale, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd_hl: bad sizes");
+  MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
+  if (E == 0) return MGN_OK;
+  MGN_CHECK_ARG(hi_in && lo_in && P && senders && receivers && packed && b2 && b3 && b4 && scale,
+                "edge_fwd_hl: null pointer");
+  MGN_CHECK_ARG((hi_out == nullptr) == (lo_out == nullptr), "edge_fwd_hl: hi_out and lo_out go together");
+  MGN_CHECK_ARG(hi_out != hi_in && lo_out != lo_in, "edge_fwd_hl: in-place not supported");
+  EdgeHLParams p{};
+  p.E = E; p.hi_in = (const __half*)hi_in; p.lo_in = (const __half*)lo_in;
+  p.hi_out = (__half*)hi_out; p.lo_out = (__half*)lo_out; p.e_out = e_out;
+  p.P = (const __half*)P; p.senders = senders; p.receivers = receivers; p.aggr = aggr;
+  p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
+  p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    attr = true;
+  }
+  const int64_t tiles = ceil_div64(E, TILE_ROWS);
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
+  edge_fwd_hl_kernel<<<grid, NT, EDGE_HL_SMEM, stream>>>(p);
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}

@@ -39,6 +39,8 @@ struct FwdParams {
   const __half* e16_in;       // edge, optional: tile images of in0 made by the previous step (then in0 is only read
                               // for the residual and the operand tile arrives by bulk copy, one tile ahead)
   __half* e16_next;           // edge, optional: tile images of the OUTPUT rows (the next step's e16_in)
+  __half* e16lo_next;         // edge, optional: tile images of the fp16 remainder  out - fp16(out)  (edge_fwd_hl.cu reads
+                              // the residual stream as image + remainder); `out` may then be null
   long long* dbg;             // developer timeline (null = off)
   int dbg_cap;
 };
@@ -330,13 +332,21 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
                                     tile_off(128, m.warp * 8 + i, 4 * m.lane)) = make_uint2(0u, 0u);
         if (dst[i] >= 0) {
           const float4 o = make_float4(old[i].x + y.x, old[i].y + y.y, old[i].z + y.z, old[i].w + y.w);
-          st_f4_hint(p.out + orow * H + 4 * m.lane, o, pol_stream);
+          if (p.out != nullptr) st_f4_hint(p.out + orow * H + 4 * m.lane, o, pol_stream);
           if (EDGE && p.e16_next != nullptr) {   // the same row in the next step's operand-tile image (8 bytes per lane)
             uint2 pk;
             pk.x = pack_h2(o.x, o.y);
             pk.y = pack_h2(o.z, o.w);
-            *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16_next) + (size_t)tile * TILE_BYTES +
-                                      tile_off(128, m.warp * 8 + i, 4 * m.lane)) = pk;
+            const size_t ioff = (size_t)tile * TILE_BYTES + tile_off(128, m.warp * 8 + i, 4 * m.lane);
+            *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16_next) + ioff) = pk;
+            if (p.e16lo_next != nullptr) {       // what the image rounds away, again in fp16
+              const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&pk.x));
+              const float2 h1 = __half22float2(*reinterpret_cast<const __half2*>(&pk.y));
+              uint2 lo;
+              lo.x = pack_h2(o.x - h0.x, o.y - h0.y);
+              lo.y = pack_h2(o.z - h1.x, o.w - h1.y);
+              *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(p.e16lo_next) + ioff) = lo;
+            }
           }
           if (EDGE) {
             if (rc != cur) {
@@ -527,17 +537,21 @@ static constexpr int P_FWD_SMEM = 3 * 32768 + TAIL_BYTES;
 
 // GraphNetBlock edge update + aggregation (layers.py:687-698).  e_in/e_out [E,128] fp32 in
 // the caller's edge order when rowmap (= CSR perm) is given, else already in CSR order.
-extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
-                            const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
-                            const void* packed, const float* b2, const float* b3, const float* b4,
-                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                            const void* e16_in, void* e16_next, int out_in_csr_order, void* stream_) {
+// mgn_edge_fwd2 = mgn_edge_fwd plus e16lo_next (tile images of e_out - fp16(e_out), the second half of the image +
+// remainder form of the residual stream that mgn_edge_fwd_hl consumes); with both images requested e_out may be NULL.
+extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
+                             const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                             const void* packed, const float* b2, const float* b3, const float* b4,
+                             const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
+                             const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order,
+                             void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
   if (E == 0) return MGN_OK;
-  MGN_CHECK_ARG(e_in && e_out && P && senders && receivers && packed && b2 && b3 && b4 && scale,
-                "edge_fwd: null pointer");
+  MGN_CHECK_ARG(e_in && P && senders && receivers && packed && b2 && b3 && b4 && scale, "edge_fwd: null pointer");
+  MGN_CHECK_ARG(e_out || (e16_next && e16lo_next), "edge_fwd: e_out may be null only if both output images are given");
+  MGN_CHECK_ARG(!e16lo_next || e16_next, "edge_fwd: e16lo_next needs e16_next");
   MGN_CHECK_ARG(e_in != e_out, "edge_fwd: in-place not supported");
   FwdParams p{};
   p.M = E; p.in0 = e_in; p.rowmap = rowmap; p.out_csr = (rowmap != nullptr && out_in_csr_order) ? 1 : 0;
@@ -547,6 +561,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
   p.e16_out = (__half*)e16_out; p.e16_in = (const __half*)e16_in; p.e16_next = (__half*)e16_next;
+  p.e16lo_next = (__half*)e16lo_next;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
@@ -558,6 +573,16 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
   mlp_fwd_kernel<true><<<grid, NT, EDGE_FWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
+}
+
+extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
+                            const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                            const void* packed, const float* b2, const float* b3, const float* b4,
+                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
+                            const void* e16_in, void* e16_next, int out_in_csr_order, void* stream_) {
+  MGN_CHECK_ARG(E == 0 || e_out, "edge_fwd: null pointer");
+  return mgn_edge_fwd2(E, N, e_in, rowmap, e_out, P, senders, receivers, aggr, packed, b2, b3, b4, scale, save_h1,
+                       save_h2, save_h3, e16_out, e16_in, e16_next, nullptr, out_in_csr_order, stream_);
 }
 
 // GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).

@@ -61,17 +61,24 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
              e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None,
              e16_out: Optional[torch.Tensor] = None, e16_in: Optional[torch.Tensor] = None,
-             e16_next: Optional[torch.Tensor] = None, out_in_csr_order: bool = False):
+             e16_next: Optional[torch.Tensor] = None, out_in_csr_order: bool = False,
+             e16lo_next: Optional[torch.Tensor] = None, write_rows: bool = True):
     """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
     used by the parity tests only -- the backward kernel recomputes them).
     e16_out: optional `e16_image(E)` buffer receiving the fp16 tile images of e_in that edge_bwd bulk-loads.
     e16_in: the tile images of e_in if a previous step already made them (its e16_next): the operand tiles then
     arrive by bulk copy and e_in is read for the residual only.  e16_next: receives the images of e_out.
     out_in_csr_order: with a rowmap, gather e_in through it but write e_out in CSR order (fuses the entry permutation
-    of the processor loop into its first step)."""
+    of the processor loop into its first step).
+    e16lo_next: receives the images of e_out - fp16(e_out) (the remainder stream edge_fwd_hl reads); with
+    write_rows=False the fp32 rows of e_out are then not written (returns None for them)."""
     E = e_in.shape[0]
     s1, s2, s3 = saves if saves is not None else (None, None, None)
-    if e_out is None:
+    if not write_rows:
+        if e16_next is None or e16lo_next is None:
+            raise ValueError("write_rows=False needs e16_next and e16lo_next")
+        e_out = None
+    elif e_out is None:
         e_out = torch.empty_like(e_in)
     if aggr is None:
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
@@ -81,10 +88,32 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
                                         L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3),
                                         L.p(b4), L.p(scale), L.stream()))
         return e_out, aggr
-    L.check(L.lib().mgn_edge_fwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
-                                 L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
-                                 L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next), L.i32(1 if out_in_csr_order else 0), L.stream()))
+    L.check(L.lib().mgn_edge_fwd2(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
+                                  L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
+                                  L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next),
+                                  L.p(e16lo_next), L.i32(1 if out_in_csr_order else 0), L.stream()))
     return e_out, aggr
+
+
+# The processor loop keeps the edge stream of steps 1..K-1 as two fp16 tile-image streams (csrc/edge_fwd_hl.cu);
+# MGN_EDGE_FWD_HL=0 falls back to the fp32-row kernel for every step.
+EDGE_FWD_HL = bool(int(__import__("os").environ.get("MGN_EDGE_FWD_HL", "1")))
+
+
+def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, senders: torch.Tensor,
+                receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
+                hi_out: Optional[torch.Tensor] = None, lo_out: Optional[torch.Tensor] = None,
+                e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None):
+    """Edge update of one step (layers.py:687-698) on the image + remainder form of the edge stream:
+    e_in = hi_in + lo_in (`e16_image` buffers, CSR tile order).  hi_out / lo_out receive the same form of e_out,
+    e_out (optional, [E,128] fp32, CSR order) its fp32 rows.  -> aggr"""
+    E = senders.shape[0]
+    if aggr is None:
+        aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=hi_in.device)
+    L.check(L.lib().mgn_edge_fwd_hl(L.i64(E), L.i64(num_nodes), L.p(hi_in), L.p(lo_in), L.p(hi_out), L.p(lo_out),
+                                    L.p(e_out), L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed),
+                                    L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.stream()))
+    return aggr
 
 
 def e16_image(num_edges: int, device) -> torch.Tensor:

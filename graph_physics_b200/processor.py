@@ -113,7 +113,12 @@ class _ProcessorFn(torch.autograd.Function):
         e = e0.detach().contiguous()
         rowmap0 = None if csr.identity else csr.perm
         xs, aggrs, Ps, saves, e16s = [x], [], [], [], []
-        e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))]     # the fp32 edge stream ping-pongs
+        hl = ops.EDGE_FWD_HL and E > 0
+        # the fp32 edge stream ping-pongs; in image + remainder form (hl) only step 0 reads fp32 rows (the caller's)
+        # and only the last step writes them, and only if the caller wants the edge latents back
+        e_bufs = [torch.empty_like(e) for _ in range(min(K, 2))] if not hl else None
+        e_last = torch.empty_like(e) if (hl and (need_edges or K == 1)) else None
+        lo_bufs = [ops.e16_image(E, dev) for _ in range(min(K - 1, 2))] if hl else None
         if not need_grad:   # inference: ping-pong buffers, nothing kept
             P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
             aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
@@ -131,24 +136,36 @@ class _ProcessorFn(torch.autograd.Function):
                 sv = tuple(torch.empty((N, H), dtype=torch.float16, device=dev) for _ in range(3))
             else:
                 x_out, sv = x_bufs[k & 1], None
-            e_out = e_bufs[k & 1]
+            last = k + 1 == K
+            if hl:
+                e_out = e_last if last else None
+            else:
+                e_out = e_bufs[k & 1]
             if k == 0:
                 img = ops.e16_image(E, dev) if need_grad else img_bufs[1 % len(img_bufs)]
                 img_self, img_in = img, None
             else:
                 img_self, img_in = None, img
             img_next = None
-            if k + 1 < K:
+            if not last:
                 img_next = ops.e16_image(E, dev) if need_grad else img_bufs[k & 1]
+            lo_next = lo_bufs[k & 1] if (hl and not last) else None
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
-            _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
-                   packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
-                   e16_next=img_next, out_in_csr_order=True)
+            if hl and k > 0:
+                _timed("edge_fwd", ops.edge_fwd_hl, img_in, lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers, N,
+                       packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out, aggr=aggr)
+            else:
+                _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
+                       packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
+                       e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
+                       write_rows=not (hl and e_out is None))
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
                    saves=sv)
             if need_grad:
                 aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
-            x, e, img = x_out, e_out, img_next
+            x, img = x_out, img_next
+            if e_out is not None:
+                e = e_out
         if not need_edges:          # the caller discards the edge latents (EncodeProcessDecode): skip the exit permutation
             e_ret = e.new_empty((0, H))
             ctx.mark_non_differentiable(e_ret)

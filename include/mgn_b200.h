@@ -127,6 +127,23 @@ int mgn_edge_fwd_pp(int64_t E, int64_t N, const float* e_in, const void* e16_in,
                     const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
                     void* stream);
+/* mgn_edge_fwd plus e16lo_next: tile images of  e_out - fp16(e_out)  (fp16), i.e. together with e16_next the
+ * image + remainder form of the residual stream that mgn_edge_fwd_hl consumes.  With both images requested e_out
+ * may be NULL (the fp32 rows are then not written at all). */
+int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
+                  const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                  const void* packed, const float* b2, const float* b3, const float* b4,
+                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
+                  const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order, void* stream);
+/* The same edge update (layers.py:687-698) for steps 1..K-1 with the residual stream held as two fp16 tile-image
+ * streams, hi = fp16(e) (= the operand images mgn_edge_bwd recomputes from) and lo = fp16(e - hi): e = hi + lo
+ * carries >= 21 significant bits of the fp32 stream, the residual add is done in fp32, and the stream moves only by
+ * 32 KB bulk copies (csrc/edge_fwd_hl.cu).  hi_out / lo_out (both or neither) receive the images of e_out; e_out
+ * (fp32 rows, CSR order) is optional -- only a caller that wants the edge latents back needs it. */
+int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
+                    float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
+                    const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
+                    void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
  * fp16, optional) are the hidden activations mgn_node_bwd needs. */
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,

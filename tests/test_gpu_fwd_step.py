@@ -134,3 +134,116 @@ def test_two_tile_edge_kernel_equals_one_tile_kernel(golden_dir):
     assert torch.equal(e0, e1)
     assert torch.equal(i0, i1)
     assert float((a0 - a1).abs().max()) <= 1e-5 * float(a0.abs().max())
+
+
+def _hl_setup(golden_dir, copies, seed):
+    import numpy as np
+    from graph_physics_b200 import graph as G, ops
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    n1 = z["points"].shape[0]
+    ei = G.tile_batch(torch.as_tensor(z["edge_index"].astype(np.int64)).cuda(), n1, copies)
+    N, E = n1 * copies, ei.shape[1]
+    csr = G.build_csr(ei, N)
+    torch.manual_seed(seed)
+    dev = "cuda"
+    ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    b = [torch.randn(128, device=dev) * 0.05 for _ in range(4)]
+    sc = 1.0 + 0.1 * torch.randn(128, device=dev)
+    packed = ops.pack_block(ew, nw)
+    x = torch.randn(N, 128, device=dev)
+    e = torch.randn(E, 128, device=dev)
+    P = ops.p_fwd(x, packed, b[0])
+    return ops, csr, N, E, packed, b, sc, P, e
+
+
+def _image_rows(img, E):
+    """Undo the 128-byte-swizzled 128 x 128 tile layout of an e16_image buffer -> [E,128] fp32 (tc05.cuh tile_off)."""
+    t = img.view(-1, 2, 128, 8, 8).float()                       # tile, panel, row, chunk slot, 8 halfs
+    rows = torch.arange(128, device=img.device)
+    chunk = torch.arange(8, device=img.device)
+    slot = (chunk[None, :] ^ (rows[:, None] & 7))                # chunk c of row r sits in slot c ^ (r & 7)
+    idx = slot[None, None, :, :, None].expand(t.shape[0], 2, 128, 8, 8)
+    un = torch.gather(t, 3, idx)                                 # [tile, panel, row, chunk, 8]
+    return un.permute(0, 2, 1, 3, 4).reshape(-1, 128)[:E]
+
+
+@pytest.mark.parametrize("copies", [1, 7])
+def test_image_remainder_edge_kernel_matches_row_kernel(golden_dir, copies):
+    """csrc/edge_fwd_hl.cu (edge stream as fp16 image + fp16 remainder, bulk copies only, row-owner output and shuffle
+    segmented sum) against mlp_fwd_kernel<true> (fp32 rows) on the same step: the products see identical operands, so
+    the MLP output is identical; the residual add sees e to >= 21 bits, so rows agree to ~1e-6 and the images of the
+    output describe the same rows; the aggregation differs only in summation order."""
+    ops, csr, N, E, packed, b, sc, P, e = _hl_setup(golden_dir, copies, 4)
+    dev = "cuda"
+    hi, lo = ops.e16_image(E, dev), ops.e16_image(E, dev)
+    # step A (row kernel) produces e1 as rows and as image + remainder
+    e1, _ = ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e16_next=hi,
+                         e16lo_next=lo)
+    assert float((_image_rows(hi, E) + _image_rows(lo, E) - e1).abs().max()) <= 2.0 ** -20 * float(e1.abs().max())
+    # the same, rows not written at all
+    hi_b, lo_b = ops.e16_image(E, dev), ops.e16_image(E, dev)
+    none_rows, _ = ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc,
+                                e16_next=hi_b, e16lo_next=lo_b, write_rows=False)
+    assert none_rows is None and torch.equal(hi_b, hi) and torch.equal(lo_b[: E // 128], lo[: E // 128])
+    # step B on e1: row kernel (image-fed) vs image + remainder kernel
+    hi2_ref = ops.e16_image(E, dev)
+    e2_ref, aggr_ref = ops.edge_fwd(e1, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc,
+                                    e16_in=hi, e16_next=hi2_ref)
+    hi2, lo2 = ops.e16_image(E, dev), ops.e16_image(E, dev)
+    e2 = torch.empty_like(e1)
+    aggr = ops.edge_fwd_hl(hi, lo, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=hi2,
+                           lo_out=lo2, e_out=e2)
+    torch.cuda.synchronize()
+    scale_e = float(e2_ref.abs().max())
+    assert float((e2 - e2_ref).abs().max()) <= 4e-6 * scale_e
+    assert float((aggr - aggr_ref).abs().max()) <= 2e-5 * float(aggr_ref.abs().max())
+    r_hi, r_lo = _image_rows(hi2, E), _image_rows(lo2, E)
+    assert float((r_hi + r_lo - e2).abs().max()) <= 2.0 ** -20 * scale_e
+    assert float((r_hi - e2).abs().max()) <= 2.0 ** -10 * scale_e          # hi alone is fp16(e2)
+    # rows past the end of the last tile are zeros in both images
+    if E % 128:
+        tail_hi = _image_rows(hi2.clone(), (E + 127) // 128 * 128)[E:]
+        tail_lo = _image_rows(lo2.clone(), (E + 127) // 128 * 128)[E:]
+        assert float(tail_hi.abs().max()) == 0.0 and float(tail_lo.abs().max()) == 0.0
+    # images only (what steps 1..K-2 of the processor loop ask for), and aggregation only (the last step)
+    hi3, lo3 = ops.e16_image(E, dev), ops.e16_image(E, dev)
+    aggr3 = ops.edge_fwd_hl(hi, lo, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=hi3,
+                            lo_out=lo3)
+    aggr4 = ops.edge_fwd_hl(hi, lo, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc)
+    torch.cuda.synchronize()
+    assert torch.equal(hi3, hi2) and torch.equal(lo3, lo2)
+    assert float((aggr3 - aggr).abs().max()) <= 2e-5 * float(aggr.abs().max())
+    assert float((aggr4 - aggr).abs().max()) <= 2e-5 * float(aggr.abs().max())
+
+
+def test_processor_image_remainder_path_matches_row_path(golden_dir):
+    """The whole 6-step loop, forward and backward, with MGN_EDGE_FWD_HL on and off."""
+    from graph_physics_b200 import graph as G, ops, processor
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    n1 = z["points"].shape[0]
+    ei = G.tile_batch(torch.as_tensor(z["edge_index"].astype(np.int64)).cuda(), n1, 3)
+    N, E = n1 * 3, ei.shape[1]
+    K = 6
+    p = mo.init_params(K, hidden=128, seed=3)
+    blocks = [[p[f"processor_list.{k}.{n}"].cuda().requires_grad_(True) for n in processor.PARAM_NAMES]
+              for k in range(K)]
+    x0, e0, gx = processor_inputs(N, E, 128, seed=1)
+    res = []
+    for hl in (False, True):
+        old = ops.EDGE_FWD_HL
+        ops.EDGE_FWD_HL = hl
+        try:
+            xd = x0.cuda().requires_grad_(True)
+            ed = e0.cuda().requires_grad_(True)
+            xk, ek = processor.run_processor(xd, ei, ed, blocks)
+            loss = (xk * gx.cuda()).sum() + (ek * ek).sum() * 1e-4
+            grads = torch.autograd.grad(loss, [xd, ed] + [t for blk in blocks for t in blk])
+            torch.cuda.synchronize()
+            res.append((xk.detach(), ek.detach(), grads))
+        finally:
+            ops.EDGE_FWD_HL = old
+    (x_a, e_a, g_a), (x_b, e_b, g_b) = res
+    assert mo.rel_l2(x_b, x_a) < 1e-3 and mo.rel_l2(e_b, e_a) < 1e-3    # six steps of last-ulp differences
+    for ga, gb in zip(g_a, g_b):
+        assert mo.rel_l2(gb, ga) < 3e-2      # ReLU-mask flips of the last-ulp differences (DESIGN.md section 5)

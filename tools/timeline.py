@@ -28,9 +28,14 @@ e2, x2 = torch.empty_like(e), torch.empty_like(x)
 P = ops.p_fwd(x, packed, b[0])
 aggr = torch.empty(N, 128, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
+fine = int(sys.argv[2]) if len(sys.argv) > 2 else 0      # stamps per tile of a -DMGN_FINE_TL build
 cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19
 if which == "edge_pp":
     cap = 6 * 21
+if which == "edge_hl":
+    cap = 10 * 19
+if fine:
+    cap = fine * 19
 ge_in = torch.randn(E, 128, device=dev)
 g_aggr = torch.randn(N, 128, device=dev)
 ge_out = torch.empty_like(e)
@@ -38,6 +43,7 @@ dz16 = ops.e16_image(E, dev)
 gblock = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
 e16 = ops.e16_image(E, dev)
 ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr, e16_out=e16)
+lo16, lo16b = ops.e16_image(E, dev).zero_(), ops.e16_image(E, dev)
 buf = torch.zeros(cap, dtype=torch.int64, device=dev)
 
 
@@ -48,6 +54,12 @@ def run():
     elif which == "edge_pp":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr,
                      e16_in=e16, e16_next=dz16)
+    elif which.startswith("edge_img"):
+        ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr,
+                     e16_in=e16, e16_next=dz16)
+    elif which == "edge_hl":
+        ops.edge_fwd_hl(e16, lo16, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=dz16,
+                        lo_out=lo16b, aggr=aggr)
     elif which == "edge":
         ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e_out=e2, aggr=aggr)
     else:
@@ -61,6 +73,13 @@ L.check(L.lib().mgn_debug_set_timeline(ctypes.c_void_p(buf.data_ptr()), ctypes.c
 run()
 torch.cuda.synchronize()
 L.check(L.lib().mgn_debug_set_timeline(ctypes.c_void_p(0), ctypes.c_int(0)))
+evs = []
+for _ in range(6):
+    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(); run(); b_.record()
+    evs.append((a, b_))
+torch.cuda.synchronize()
+print("event us per launch:", sorted(round(a.elapsed_time(b_) * 1e3, 1) for a, b_ in evs))
 t = buf.cpu().numpy()
 t = t[t > 0]
 names = ["load", "L1 mma", "L1 epi", "L2 mma", "L2 epi", "L3 mma", "L3 epi", "L4 mma", "norm+stage", "output", "next"]
@@ -71,8 +90,15 @@ if which == "edge_bwd":
 if which == "edge_pp":
     names = ["O3(k-1)", "O1(k)", "O4(k-1)", "O2(k)", "O5(k-1)", "O0(k+1)"]
     per = 6
-if which == "edge_pp":
-    pass
+if which == "edge_hl":
+    names = ["L1 mma", "L1 epi", "L2+L3", "L4+norm", "images", "st+mma1", "ldP", "scan", "red", "next"]
+    per = 10
+if fine:
+    per = fine
+    names = [f"s{i}" for i in range(fine)]
+if which.endswith("_raw"):
+    print("entry->loop", t[1] - t[0], "tiles", np.diff(t[1:-1]).tolist(), "loop total", t[-2] - t[1], "kernel cycles", t[-2] - t[0])
+    sys.exit(0)
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
