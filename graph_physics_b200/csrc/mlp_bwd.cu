@@ -154,9 +154,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   };
   // Indices, requested one tile ahead.  Coalesced mapping (lane i < 8 <-> tile row 8*warp + i): dst, rcv, snd.
   // Epilogue mapping (this thread's tile row m.row): own = row of g_e (used with a rowmap only).
-  struct Idx { int dst, rcv, snd, own; };
+  struct Idx { int dst, rcv, snd, own, rcv_o; };
   auto load_idx = [&](long long tile_) -> Idx {
-    Idx ix{-1, -1, -1, -1};
+    Idx ix{-1, -1, -1, -1, -1};
     const long long g = tile_ * TILE_ROWS + m.warp * 8 + (m.lane & 7);
     const long long go = tile_ * TILE_ROWS + m.row;
     if (tile_ < num_tiles && g < p.E) {
@@ -165,6 +165,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       ix.snd = __ldg(p.senders + g);
     }
     if (p.rowmap && tile_ < num_tiles && go < p.E) ix.own = __ldg(p.rowmap + go);
+    if (tile_ < num_tiles && go < p.E) ix.rcv_o = __ldg(p.receivers + go);   // epilogue row's receiver (P_i gather)
     return ix;
   };
   const int hw = m.lane >> 4, q = m.lane & 15;
@@ -252,9 +253,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     {
       // under the product: P_j rows -> sH1 (staging, overwritten in place by h1), P_i rows -> registers
       uint4 pi[4];
-      const long long go = tile * TILE_ROWS + m.row;
-      const bool ok = go < p.E;
-      const __half* si = p.P + (long long)(ok ? __ldg(p.receivers + go) : 0) * 256 + m.c0;
+      const bool ok = cur.rcv_o >= 0;
+      const __half* si = p.P + (long long)(ok ? cur.rcv_o : 0) * 256 + m.c0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) pi[j] = ok ? ld_u4_hint(si + 8 * j, pol_keep) : make_uint4(0, 0, 0, 0);
       cp_async_wait_all();
@@ -280,14 +280,22 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (m.tid == 0) bulk_wait_read0();    // the previous tile's g_e store has read lin32 (= sH2 + sH3)
     tile_ready();
     tl.stamp();   // 2 R1 done
-    // L2 prefetch of the next tile's streamed rows
+    // L2 prefetch of the next tile's streamed rows: the upstream tile is contiguous without a rowmap (one bulk
+    // prefetch by one thread); g_aggr rows once per distinct receiver (consecutive rows share it)
     {
       const int nd = __shfl_sync(0xffffffffu, nxt.dst, m.lane & 7);
       const int nr = __shfl_sync(0xffffffffu, nxt.rcv, m.lane & 7);
+      const int np = __shfl_sync(0xffffffffu, nxt.rcv, (m.lane & 7) ? (m.lane & 7) - 1 : 0);
       const int part = m.lane >> 3;           // 4 lanes per row: one 128-byte line each
       if (nd >= 0) {
-        if (p.g_eout) prefetch_l2(reinterpret_cast<const char*>(p.g_eout + (long long)nd * H) + 128 * part);
-        prefetch_l2(reinterpret_cast<const char*>(p.g_aggr + (long long)nr * H) + 128 * part);
+        if (p.g_eout && p.rowmap) prefetch_l2(reinterpret_cast<const char*>(p.g_eout + (long long)nd * H) + 128 * part);
+        if ((m.lane & 7) == 0 || nr != np)
+          prefetch_l2(reinterpret_cast<const char*>(p.g_aggr + (long long)nr * H) + 128 * part);
+      }
+      if (m.tid == 0 && p.g_eout && !p.rowmap && has_next) {
+        const long long nrow0 = (tile + gridDim.x) * TILE_ROWS;
+        const long long nrows = (p.E - nrow0) < TILE_ROWS ? (p.E - nrow0) : TILE_ROWS;
+        bulk_prefetch_l2(p.g_eout + nrow0 * H, (uint32_t)(nrows * 512));
       }
     }
     // ---- R2
@@ -475,7 +483,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
 struct NodeBwdParams {
   long long N;
   const float* g_xout;      // [N,128]
-  const __half* h1;         // fp16 hidden saves of node_fwd
+  const __half* h1;         // fp16 hidden saves of node_fwd: tile images (32 KB per 128 rows), bulk-loaded
   const __half* h2;
   const __half* h3;
   float* g_x;               // [N,128] out: g_xout + dz1' W1'[:, :128]
@@ -499,12 +507,14 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   Tail2* tail = reinterpret_cast<Tail2*>(smem + 6 * SLOT);
   uint64_t* bar_w = &tail->bar[0];
   uint64_t& bar_mma = tail->bar[2];
+  uint64_t& bar_h = tail->bar[3];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
   if (m.tid == 0) {
     mbar_init(&bar_w[0], 1);
     mbar_init(&bar_w[1], 1);
     mbar_init(&bar_mma, 1);
+    mbar_init(&bar_h, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -551,10 +561,14 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     const long long row0 = tile * TILE_ROWS;
     const uint32_t q0 = 5 * it;
     auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
-    load8_f16_to_tile(sH1, p.h1, m, rf);
-    load8_f16_to_tile(sH2, p.h2, m, rf);
-    load8_f16_to_tile(sH3, p.h3, m, rf);
+    if (m.tid == 0) {          // the three saved activation tiles arrive as they were stored: one bulk copy each
+      mbar_arrive_expect_tx(&bar_h, 3 * SLOT);
+      bulk_g2s(sH3, reinterpret_cast<const uint8_t*>(p.h3) + (size_t)tile * SLOT, SLOT, &bar_h);
+      bulk_g2s(sH2, reinterpret_cast<const uint8_t*>(p.h2) + (size_t)tile * SLOT, SLOT, &bar_h);
+      bulk_g2s(sH1, reinterpret_cast<const uint8_t*>(p.h1) + (size_t)tile * SLOT, SLOT, &bar_h);
+    }
     load8_f32_to_tile(sG, 128, 0, p.g_xout, m, rf, pol_keep);
+    mbar_wait(&bar_h, it & 1);
     tile_ready();
     // ---- R4: z4 = h3 W4'^T, RMSNorm backward
     {

@@ -220,6 +220,7 @@ __device__ __forceinline__ void bulk_red_add_f32(float* gdst, const void* smem_s
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ------------------------------------------------------------------ developer timeline (tools/timeline.py)
@@ -240,6 +241,10 @@ struct Timeline {
 
 // ------------------------------------------------------------------ prefetch / misc
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// one instruction, one thread: a contiguous range (16-byte aligned, multiple of 16 bytes) into L2
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 // one 512-byte fp32 row = 4 lines
 __device__ __forceinline__ void prefetch_row_f32(const float* row) {
   const char* c = reinterpret_cast<const char*>(row);

@@ -32,9 +32,9 @@ struct FwdParams {
   const float* b3;
   const float* b4;
   const float* scale;
-  __half* save_h1;            // optional fp16 saves of the hidden activations (row = tile row index)
-  __half* save_h2;
-  __half* save_h3;
+  __half* save_h1;            // optional fp16 saves of the hidden activations.  edge: [M,128] rows (row = CSR position);
+  __half* save_h2;            // node: tile images (32 KB swizzled 128 x 128 tile per 128 rows, bulk-stored as the tile
+  __half* save_h3;            // sits in shared memory -- exactly what node_bwd's operand slots want)
   __half* e16_out;            // edge, optional: fp16 tile images of in0 (32 KB per 128-row tile) for edge_bwd
   const __half* e16_in;       // edge, optional: tile images of in0 made by the previous step (then in0 is only read
                               // for the residual and the operand tile arrives by bulk copy, one tile ahead)
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       float4 bb[8];
       load_vec32(p.b1, m.c0, bb);
       mma_wait();
-      epi_bias_relu_q(taddr, bb, sA, m, rvalid ? p.save_h1 : nullptr, grow);
+      epi_bias_relu_q(taddr, bb, sA, m, nullptr, 0);
     }
     if (EDGE) {
       // sA is dead from here on: the next tile's operand image can come in now, three products ahead of its use
@@ -249,12 +249,24 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     }
 
     // ---- layers 2, 3
+    // node kernel: the hidden activations alternate between the two halves of sA (h1 -> first, h2 -> second, h3 ->
+    // first) so that each tile can leave for global memory as one bulk copy (the saves node_bwd bulk-loads) while the
+    // next product reads it; thread 0 checks that the copy issued a layer earlier has read its half before it issues
+    // the product whose epilogue overwrites that half (every thread then waits for that product anyway)
 #pragma unroll 1
     for (int layer = 1; layer < 3; ++layer) {
+      uint8_t* act_in = (EDGE || layer == 1) ? sA : sA + TILE_BYTES;
+      uint8_t* act_out = (EDGE || layer == 2) ? sA : sA + TILE_BYTES;
       if (m.tid == 0) {
         fence_after_sync();
+        if (!EDGE && p.save_h1 != nullptr) {
+          bulk_s2g(reinterpret_cast<uint8_t*>(layer == 1 ? p.save_h1 : p.save_h2) + (size_t)tile * TILE_BYTES, act_in,
+                   TILE_BYTES, pol_keep);
+          bulk_commit();
+          if (layer == 2) bulk_wait_read1();
+        }
         if (EDGE) umma_tile_ts(tmem_acc, tmem_a, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
-        else umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
+        else umma_tile(tmem_acc, smem_u32(act_in), 128, 0, sW_u32 + W1_BYTES + (layer - 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
         mma_commit(&mbar);
       }
       float4 bb[8];
@@ -266,7 +278,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
         epi_bias_relu_tmem_q(taddr, taddr_a, bb, m, rvalid ? save : nullptr, grow);
         acts_ready();
       } else {
-        epi_bias_relu_q(taddr, bb, sA, m, rvalid ? save : nullptr, grow);
+        epi_bias_relu_q(taddr, bb, act_out, m, nullptr, 0);
         tile_ready();
       }
       tl.stamp();   // 5, 7 epilogue done
@@ -275,6 +287,10 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     // ---- layer 4 + RMSNorm + residual (+ segmented sum over receivers)
     if (m.tid == 0) {
       fence_after_sync();
+      if (!EDGE && p.save_h1 != nullptr) {      // h3 sits in the first half of sA
+        bulk_s2g(reinterpret_cast<uint8_t*>(p.save_h3) + (size_t)tile * TILE_BYTES, sA, TILE_BYTES, pol_keep);
+        bulk_commit();
+      }
       if (EDGE) umma_tile_ts(tmem_acc, tmem_a, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
       else umma_tile(tmem_acc, sA_u32, 128, 0, sW_u32 + W1_BYTES + 2 * TILE_BYTES, 128, 0, 0, 128, 8, 0);
       mma_commit(&mbar);
@@ -288,6 +304,9 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     mma_wait();
+    // node kernel: the output staging below reuses both halves of sA -- the copies of h2 and h3 must have read them
+    // (the barriers inside row_sum4 publish this to the other threads)
+    if (!EDGE && m.tid == 0 && p.save_h1 != nullptr) bulk_wait_read0();
     tl.stamp();   // 8 layer-4 product done (residual rows requested before)
     {
       float v[32];
@@ -365,6 +384,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     tl.stamp();   // 10 output done
   }
   if (!w_ready) mbar_wait(&wbar, 0);   // never exit with the weight copy in flight
+  if (!EDGE && m.tid == 0) bulk_wait0();
 
   fence_before_sync();
   __syncthreads();
@@ -592,6 +612,8 @@ extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float*
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && x && aggr && x_out && packed && b1 && b2 && b3 && b4 && scale, "node_fwd: bad args");
   MGN_CHECK_ARG(x != x_out, "node_fwd: in-place not supported");
+  MGN_CHECK_ARG((save_h1 == nullptr) == (save_h2 == nullptr) && (save_h1 == nullptr) == (save_h3 == nullptr),
+                "node_fwd: the three saves go together");
   FwdParams p{};
   p.M = N; p.in0 = x; p.in1 = aggr; p.out = x_out;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);

@@ -80,7 +80,7 @@ class PartitionEngine:
         if ng:
             P = torch.empty((n_ext, 2 * H), dtype=torch.float16, device=dev)
             aggr = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
-            sv = tuple(torch.empty((n_own, H), dtype=torch.float16, device=dev) for _ in range(3))
+            sv = ops.node_saves(n_own, dev)
         else:
             P, aggr, sv = self.P, self.aggr, None
         _timed("p_fwd", ops.p_fwd, x, self.packed[k], b[1], out=P)

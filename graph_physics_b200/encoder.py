@@ -50,7 +50,7 @@ class _EncoderFn(torch.autograd.Function):
         zero_e = [torch.zeros((H, 3 * H), device=dev)] + [torch.zeros((H, H), device=dev) for _ in range(3)]
         packed = ops.pack_block(zero_e, [w1p, w2.detach(), w3.detach(), w4.detach()])
         need_grad = any(ctx.needs_input_grad)
-        sv = tuple(torch.empty((M, H), dtype=torch.float16, device=dev) for _ in range(3)) if need_grad else None
+        sv = ops.node_saves(M, dev) if need_grad else None
         out = torch.empty((M, H), dtype=torch.float32, device=dev)
         if M > 0:
             ops.node_fwd(xz, a, packed, b1.detach().contiguous(), b2.detach().contiguous(), b3.detach().contiguous(),

@@ -122,9 +122,29 @@ def e16_image(num_edges: int, device) -> torch.Tensor:
     return torch.empty((tiles, 128 * H), dtype=torch.float16, device=device)
 
 
+def node_saves(num_rows: int, device):
+    """The three buffers node_fwd fills with the node MLP's hidden activations for node_bwd: fp16 tile images (the
+    128 x 128 swizzled operand tiles as they sit in shared memory, bulk-stored / bulk-loaded)."""
+    return tuple(e16_image(num_rows, device) for _ in range(3))
+
+
+def image_rows(img: torch.Tensor, num_rows: int) -> torch.Tensor:
+    """[num_rows,128] fp32 view of a tile-image buffer (`e16_image` / `node_saves`): undoes the 128-byte swizzle of
+    csrc/tc05.cuh tile_off.  For tests and debugging; the kernels never need the rows."""
+    t = img.view(-1, 2, 128, 8, 8).float()                       # tile, 64-column panel, row, 16-byte slot, 8 halfs
+    rows = torch.arange(128, device=img.device)
+    chunk = torch.arange(8, device=img.device)
+    slot = chunk[None, :] ^ (rows[:, None] & 7)                  # chunk c of row r sits in slot c ^ (r & 7)
+    un = torch.gather(t, 3, slot[None, None, :, :, None].expand(t.shape[0], 2, 128, 8, 8))
+    return un.permute(0, 2, 1, 3, 4).reshape(-1, 128)[:num_rows]
+
+
 def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
              x_out: Optional[torch.Tensor] = None, saves=None) -> torch.Tensor:
+    """saves: `node_saves(N)` buffers (tile images), or None."""
     N = x.shape[0]
+    if saves is not None and any(sv.numel() < ((N + 127) // 128) * 128 * H for sv in saves):
+        raise ValueError("node_fwd: saves must be node_saves(N) tile-image buffers")
     if x_out is None:
         x_out = torch.empty_like(x)
     s1, s2, s3 = saves if saves is not None else (None, None, None)

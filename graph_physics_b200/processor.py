@@ -133,7 +133,7 @@ class _ProcessorFn(torch.autograd.Function):
                 P = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
                 aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
                 x_out = torch.empty_like(x)
-                sv = tuple(torch.empty((N, H), dtype=torch.float16, device=dev) for _ in range(3))
+                sv = ops.node_saves(N, dev)
             else:
                 x_out, sv = x_bufs[k & 1], None
             last = k + 1 == K

@@ -144,8 +144,9 @@ int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, 
                     float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
                     void* stream);
-/* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* ([N,128]
- * fp16, optional) are the hidden activations mgn_node_bwd needs. */
+/* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* (optional, all three or
+ * none) receive the hidden activations mgn_node_bwd needs as fp16 TILE IMAGES: ceil(N/128) * 32768 bytes each, one
+ * 128-byte-swizzled 128 x 128 operand tile per 128 rows, bulk-stored as it sits in shared memory. */
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                  const float* b1, const float* b2, const float* b3, const float* b4,
                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream);
@@ -156,7 +157,7 @@ int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, con
  * in the block's state-dict order (edge_block.0.weight, .0.bias, ..., .7.scale, node_block...);
  * the caller zeroes it.  Upstream gradients may be pre-scaled by any power of two. */
 int64_t mgn_grad_block_floats(void);
-/* node_block backward from the fp16 hidden saves: g_x = g_xout + dz1 W1'[:, :128],
+/* node_block backward from the fp16 hidden saves (the tile images mgn_node_fwd wrote): g_x = g_xout + dz1 W1'[:, :128],
  * g_aggr = dz1 W1'[:, 128:], dz1 [N,128] fp16; dW2'..dW4', all biases, dscale. */
 int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                  float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,

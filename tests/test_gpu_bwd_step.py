@@ -55,7 +55,7 @@ def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
     e16 = None if use_rowmap else ops.e16_image(E, dev)
     e_out, aggr = ops.edge_fwd(e_in, rowmap, P, csr.senders, csr.receivers, n, packed, eb[1], eb[2], eb[3], esc,
                                saves=esaves, e16_out=e16)
-    saves = tuple(torch.empty((n, 128), dtype=torch.float16, device=dev) for _ in range(3))
+    saves = ops.node_saves(n, dev)
     x_out = ops.node_fwd(xd, aggr, packed, nb[0], nb[1], nb[2], nb[3], nsc, saves=saves)
     grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
     g_x, g_aggr, dz1 = ops.node_bwd(gx1.to(dev), saves, packed, nb[3], nsc, grad)
@@ -80,7 +80,7 @@ def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
         m = torch.empty_like(hs, dtype=torch.float64)
         m[perm] = (hs > 0).double()
         emasks.append(m.cpu())
-    nmasks = [(hs > 0).double().cpu() for hs in saves]
+    nmasks = [(ops.image_rows(hs, n) > 0).double().cpu() for hs in saves]
     return (g_x.cpu(), g_e.cpu(), {k: v.cpu() for k, v in ops.split_grad_block(grad).items()}, emasks, nmasks)
 
 

@@ -78,6 +78,7 @@ def test_fused_encoder_gradients_through_the_same_active_set():
     from graph_physics_b200 import encoder as ENC
     from graph_physics_b200.models.layers import build_mlp
     from oracle import mgn_oracle as mo
+    from graph_physics_b200 import ops
     torch.manual_seed(3)
     rows, fin = 1923, 11
     mlp = build_mlp(fin, 128, 128).cuda()
@@ -87,7 +88,7 @@ def test_fused_encoder_gradients_through_the_same_active_set():
     ENC.DEBUG_KEEP_SAVES = True
     try:
         out = ENC.run_encoder(mlp, f1)
-        masks = [(h > 0).double().cpu() for h in ENC.LAST_SAVES]
+        masks = [(ops.image_rows(h, rows) > 0).double().cpu() for h in ENC.LAST_SAVES]     # saves are tile images
     finally:
         ENC.DEBUG_KEEP_SAVES, ENC.LAST_SAVES = False, None
     out.backward(g)

@@ -158,14 +158,8 @@ def _hl_setup(golden_dir, copies, seed):
 
 
 def _image_rows(img, E):
-    """Undo the 128-byte-swizzled 128 x 128 tile layout of an e16_image buffer -> [E,128] fp32 (tc05.cuh tile_off)."""
-    t = img.view(-1, 2, 128, 8, 8).float()                       # tile, panel, row, chunk slot, 8 halfs
-    rows = torch.arange(128, device=img.device)
-    chunk = torch.arange(8, device=img.device)
-    slot = (chunk[None, :] ^ (rows[:, None] & 7))                # chunk c of row r sits in slot c ^ (r & 7)
-    idx = slot[None, None, :, :, None].expand(t.shape[0], 2, 128, 8, 8)
-    un = torch.gather(t, 3, idx)                                 # [tile, panel, row, chunk, 8]
-    return un.permute(0, 2, 1, 3, 4).reshape(-1, 128)[:E]
+    from graph_physics_b200 import ops
+    return ops.image_rows(img, E)
 
 
 @pytest.mark.parametrize("copies", [1, 7])
