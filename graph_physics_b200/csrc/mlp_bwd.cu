@@ -460,11 +460,13 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     tl.stamp();   // 8 g_e issued
   }
   if (m.tid == 0) bulk_wait0();
+  tl.stamp();   // loop done
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
-  flush_acc_q(tm_dW4 + qoff, p.grad + GB_E_W4, 128, m);
-  flush_acc_q(tm_dW3 + qoff, p.grad + GB_E_W3, 128, m);
-  flush_acc_q(tm_dW2 + qoff, p.grad + GB_E_W2, 128, m);
+  __syncthreads();          // thread 0 has seen the last g_e store leave lin32
+  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_E_W4, 128, lin32, m, pol_keep);
+  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_E_W3, 128, lin32, m, pol_keep);
+  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_E_W2, 128, lin32, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
@@ -473,6 +475,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   atomicAdd(p.grad + GB_E_B2 + 2 * cp, db2a);
   atomicAdd(p.grad + GB_E_B2 + 2 * cp + 1, db2b);
   atomicAdd(p.grad + GB_E_SC + m.c0 + m.lane, dsc);
+  tl.stamp();   // flush issued
 
   fence_before_sync();
   __syncthreads();
@@ -683,9 +686,9 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     __syncthreads();
   }
   fence_after_sync();
-  flush_acc_q(tm_dW4 + qoff, p.grad + GB_N_W4, 128, m);
-  flush_acc_q(tm_dW3 + qoff, p.grad + GB_N_W3, 128, m);
-  flush_acc_q(tm_dW2 + qoff, p.grad + GB_N_W2, 128, m);
+  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_N_W4, 128, stage, m, pol_keep);
+  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_N_W3, 128, stage, m, pol_keep);
+  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_N_W2, 128, stage, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_N_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_N_B4 + 2 * cp + 1, db4b);
@@ -863,8 +866,8 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
   }
   fence_after_sync();
   // dW_i -> edge_block.0.weight[:, 128:256], dW_j -> [:, 256:384]
-  flush_acc_q(tm_dWi + qoff, p.grad + GB_E_W1 + 128, 384, m);
-  flush_acc_q(tm_dWj + qoff, p.grad + GB_E_W1 + 256, 384, m);
+  flush_acc_bulk(tm_dWi + qoff, p.grad + GB_E_W1 + 128, 384, sGP, m, pol_keep);
+  flush_acc_bulk(tm_dWj + qoff, p.grad + GB_E_W1 + 256, 384, sGP, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B1 + 2 * cp, db1a);
   atomicAdd(p.grad + GB_E_B1 + 2 * cp + 1, db1b);
@@ -933,8 +936,9 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   if (it >= 1) mbar_wait(&bar_set[(it - 1) & 1], ((it - 1) >> 1) & 1);
   if (it >= 2) mbar_wait(&bar_set[it & 1], ((it - 2) >> 1) & 1);
   fence_after_sync();
-  flush_acc_q(tm + qoff, p.grad + GB_N_W1, 256, m);
-  flush_acc_q(tm + 128 + qoff, p.grad + GB_N_W1 + 128, 256, m);
+  __syncthreads();          // every thread is past its last operand store: the operand buffers are dead
+  flush_acc_bulk(tm + qoff, p.grad + GB_N_W1, 256, smem, m, policy_evict_last());
+  flush_acc_bulk(tm + 128 + qoff, p.grad + GB_N_W1 + 128, 256, smem, m, policy_evict_last());
   fence_before_sync();
   __syncthreads();
   if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
@@ -1001,7 +1005,7 @@ __global__ void __launch_bounds__(NT, 1) edge_wgrad1_kernel(const EdgeWgrad1Para
   if (my_tiles > 0) {
     mbar_wait(&bar_done, 0);
     fence_after_sync();
-    flush_acc_q(tm + m.lane_off + m.c0, p.grad + GB_E_W1, 384, m);
+    flush_acc_bulk(tm + m.lane_off + m.c0, p.grad + GB_E_W1, 384, smem, m, policy_evict_last());
   }
   fence_before_sync();
   __syncthreads();

@@ -204,6 +204,33 @@ __device__ __forceinline__ void add_row32_linear(uint8_t* tile, const Map& m, fl
   }
 }
 
+// Resident 128 x 128 fp32 accumulator (all 16 warps' quarters) += into a [128][ld] fp32 global matrix: rows pass through a
+// row-linear 64 KB staging tile and leave as bulk reductions performed at L2 (one 64 KB copy when the destination rows
+// are contiguous, else one 512-byte copy per row) -- a row-owner red.add touches 32 distinct lines per instruction and
+// costs ~5 k cycles of the load/store path per matrix.  All NT threads call; `lin32` must be dead; ends with a barrier
+// after the copies have read it.
+__device__ __forceinline__ void flush_acc_bulk(uint32_t taddr, float* __restrict__ dst, int ld, uint8_t* lin32,
+                                               const Map& m, uint64_t pol) {
+  float v[32];
+  tmem_ld32(taddr, v);
+  tmem_ld_wait();
+  store_row32_linear(lin32, m, v);
+  fence_async_smem();
+  __syncthreads();
+  if (ld == 128) {
+    if (m.tid == 0) {
+      bulk_red_add_f32(dst, lin32, 128 * 512, pol);
+      bulk_commit();
+      bulk_wait_read0();
+    }
+  } else if (m.tid < 128) {
+    bulk_red_add_f32(dst + (long long)m.tid * ld, lin32 + m.tid * 512, 512, pol);
+    bulk_commit();
+    bulk_wait_read0();
+  }
+  __syncthreads();
+}
+
 // ReLU backward in place (tile: h -> fp16(acc * [h > 0])) plus an fp32 copy of the result in a linear tile
 __device__ __forceinline__ void epi_relu_mask_q32(uint32_t taddr, uint8_t* tile, uint8_t* lin32, const Map& m) {
   float v[32], h[32];

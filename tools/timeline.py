@@ -29,7 +29,7 @@ P = ops.p_fwd(x, packed, b[0])
 aggr = torch.empty(N, 128, device=dev)
 which = sys.argv[1] if len(sys.argv) > 1 else "edge"
 fine = int(sys.argv[2]) if len(sys.argv) > 2 else 0      # stamps per tile of a -DMGN_FINE_TL build
-cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19
+cap = 11 * 19 + 8 if which != "edge_bwd" else 8 * 19 + 2
 if which == "edge_pp":
     cap = 6 * 21
 if which == "edge_hl":
@@ -99,6 +99,8 @@ if fine:
 if which.endswith("_raw"):
     print("entry->loop", t[1] - t[0], "tiles", np.diff(t[1:-1]).tolist(), "loop total", t[-2] - t[1], "kernel cycles", t[-2] - t[0])
     sys.exit(0)
+if which == "edge_bwd" and len(t) == 8 * 19 + 2:
+    print("after last tile -> loop done", t[-2] - t[-3], "flush", t[-1] - t[-2], "kernel body", t[-1] - t[0])
 ntile = len(t) // per
 print("tiles seen", ntile)
 for k in range(ntile):
