@@ -96,6 +96,11 @@ struct EdgeBwdParams {
   int dbg_skip;             // developer experiments only (MGN_DEBUG_SKIP): bit mask of memory operations to leave out
 };
 
+// FAST = the processor loop's case (upstream g_e tile contiguous: no rowmap, g_eout given, e images given): the operand
+// g = fp16(g_eout + g_aggr[receiver]) is built under product R2 from a bulk-loaded copy of the upstream tile (row-owner
+// mapping, g_aggr chunks read directly -- rows of one receiver are consecutive), so no thread issues or waits for loads
+// of the g_e stream and the "next tile's g in four pieces" schedule of the general path disappears.
+template <bool FAST>
 __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
@@ -113,6 +118,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_e = tail->bar[4];
   uint64_t& bar_g = tail->bar[5];
+  uint64_t& bar_g2 = tail->bar[6];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
 
@@ -122,6 +128,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_e, 1);
     mbar_init(&bar_g, 1);
+    mbar_init(&bar_g2, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -224,10 +231,16 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   Idx cur = load_idx(blockIdx.x);
   if (p.e16 != nullptr && m.tid == 0) issue_e16(blockIdx.x);
   stage_pj(cur);
+  if (!FAST) {
 #pragma unroll
-  for (int q4 = 0; q4 < 4; ++q4) g_store(g_issue(cur, q4), q4);
+    for (int q4 = 0; q4 < 4; ++q4) g_store(g_issue(cur, q4), q4);
+  }
   GPiece gq;                            // the piece in flight (next tile's g)
   bool gq_pending = false;              // first tile: nothing left over from a previous tile
+  auto tile_rows_bytes = [&](long long tile_) -> uint32_t {
+    const long long r0 = tile_ * TILE_ROWS;
+    return (uint32_t)(((p.E - r0) < TILE_ROWS ? (p.E - r0) : TILE_ROWS) * 512);
+  };
   Idx nxt = load_idx((long long)blockIdx.x + gridDim.x);
 
   uint32_t it = 0;
@@ -241,7 +254,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tl.stamp();   // 1
 
-    if (gq_pending) g_store(gq, 3);       // last piece of this tile's g
+    if (!FAST && gq_pending) g_store(gq, 3);       // last piece of this tile's g
     // ---- R1: z1 = e We^T + P_i[recv] + P_j[send]
     if (m.tid == 0) {
       if (it == 0) mbar_wait(&bar_wA, 0);
@@ -249,6 +262,11 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       fence_after_sync();
       umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
       mma_commit(&bar_mma);
+      if (FAST) {               // upstream rows of this tile -> lin32, once the previous tile's g_e store has left it
+        bulk_wait_read0();
+        mbar_arrive_expect_tx(&bar_g2, tile_rows_bytes(tile));
+        bulk_g2s(lin32, p.g_eout + tile * TILE_ROWS * H, tile_rows_bytes(tile), &bar_g2);
+      }
     }
     {
       // under the product: P_j rows -> sH1 (staging, overwritten in place by h1), P_i rows -> registers
@@ -262,7 +280,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       mma_wait();
       if (m.tid == 0) {
         load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
-        if (has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);   // sE is dead: the next tile's e image
+        // sE is dead: the next tile's e image (FAST: requested later, at D4 -- here it would compete with the
+        // upstream tile the g build is about to wait for)
+        if (!FAST && has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);
       }
       float v[32], b[32];
       tmem_ld32(tm_W + qoff, v);
@@ -277,7 +297,17 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       }
       store_row_chunk_f16(sH1, 128, m.row, m.c0, v);
     }
-    if (m.tid == 0) bulk_wait_read0();    // the previous tile's g_e store has read lin32 (= sH2 + sH3)
+    if (!FAST && m.tid == 0) bulk_wait_read0();    // the previous tile's g_e store has read lin32 (= sH2 + sH3)
+    // FAST: this row's g_aggr chunks (chunk order rotated by lane & 7, see the g build under R2), requested a barrier,
+    // the prefetches and a product issue ahead of their use
+    float4 gag[8];
+    if (FAST) {
+      const int kx = m.lane & 7;
+      const bool ok = cur.rcv_o >= 0;
+      const float* ga = p.g_aggr + (long long)(ok ? cur.rcv_o : 0) * H + m.c0;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) gag[c] = ok ? ld_f4_hint(ga + 4 * (c ^ kx), pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     tile_ready();
     tl.stamp();   // 2 R1 done
     // L2 prefetch of the next tile's streamed rows: the upstream tile is contiguous without a rowmap (one bulk
@@ -305,6 +335,25 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         fence_after_sync();
         umma_tile(tm_W, uH1, 128, 0, uWB, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
+      }
+      if (FAST) {
+        // g = fp16(g_eout + g_aggr[receiver]) for this thread's 32 columns.  lin32 is row-linear with the 16-byte
+        // chunks of a row rotated by (lane & 7) on access (bank-conflict free); the same rotation picks the g_aggr
+        // chunk and the destination columns, so nothing is permuted in registers.
+        const int kx = m.lane & 7;
+        const bool ok = cur.rcv_o >= 0;
+        const float4 (&a)[8] = gag;
+        mbar_wait(&bar_g2, it & 1);
+        const uint8_t* base = lin32 + m.row * 512 + m.c0 * 4;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 u = ok ? *reinterpret_cast<const float4*>(base + 16 * (c ^ kx)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          uint2 pk;
+          pk.x = pack_h2(u.x + a[c].x, u.y + a[c].y);
+          pk.y = pack_h2(u.z + a[c].z, u.w + a[c].w);
+          *reinterpret_cast<uint2*>(sG + tile_off(128, m.row, m.c0 + 4 * (c ^ kx))) = pk;
+        }
+        __syncthreads();        // every thread has read lin32 before the epilogue below writes sH2
       }
       float4 bb[8];
       load_vec32(p.b2, m.c0, bb);
@@ -353,7 +402,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
-    if (m.tid == 0) load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
+    if (m.tid == 0) {
+      load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
+      if (FAST && has_next) issue_e16(tile + gridDim.x);
+    }
     epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
     // ---- D3
@@ -363,7 +415,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
-    if (has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
+    if (!FAST && has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
@@ -377,7 +429,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
-    if (has_next) {
+    if (!FAST && has_next) {
       g_store(gq, 0);
       gq = g_issue(nxt, 1);
     }
@@ -408,13 +460,13 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     const Idx done = cur;
     cur = nxt;
-    if (has_next) {
+    if (!FAST && has_next) {
       g_store(gq, 1);
       gq = g_issue(cur, 2);
     }
     nxt = load_idx(tile + 2 * (long long)gridDim.x);
     mma_wait();
-    if (has_next) {
+    if (!FAST && has_next) {
       g_store(gq, 2);
       gq = g_issue(cur, 3);
     }
@@ -1043,11 +1095,16 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
   p.dbg_skip = dbg_skip;
   static bool attr = false;
   if (!attr) {
-    MGN_CUDA(cudaFuncSetAttribute(edge_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
-  edge_bwd_kernel<<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
+  static const bool no_fast = getenv("MGN_EDGE_BWD_GENERAL") != nullptr;      // developer switch: always the general path
+  if (!no_fast && rowmap == nullptr && g_eout != nullptr && e16 != nullptr)
+    edge_bwd_kernel<true><<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
+  else
+    edge_bwd_kernel<false><<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
