@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_e = tail->bar[4];
   uint64_t& bar_g = tail->bar[5];
   uint64_t& bar_g2 = tail->bar[6];
+  uint64_t& bar_wC = tail->bar[7];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
 
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_e, 1);
     mbar_init(&bar_g, 1);
     mbar_init(&bar_g2, 1);
+    mbar_init(&bar_wC, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -148,7 +150,15 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   if (m.tid == 0) {
     load_w_slot(sWA, p.W, 0, &bar_wA);
     load_w_slot(sWB, p.W, 1, &bar_wB);
+    // FAST: the e image travels through sG (dead from D4 of one tile to the g build of the next), which frees sE as
+    // a THIRD weight slot: W2 and W3 stay resident for the whole kernel and only slot A alternates We <-> W4, so a
+    // tile streams 64 KB of weights instead of 192 KB
+    if (FAST) load_w_slot(sE, p.W, 2, &bar_wC);
   }
+  const uint32_t uW3 = FAST ? uE : uWA;           // where W3 sits for R3 / D3
+  const uint32_t uW4 = FAST ? uWA : uWB;          // where W4 sits for R4 / D4
+  uint8_t* const sEimg = FAST ? sG : sE;          // where the e image lands
+  const uint32_t uEimg = FAST ? uG : uE;
   auto mma_wait = [&]() {
     mbar_wait(&bar_mma, phase);
     phase ^= 1;
@@ -217,7 +227,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   // e tile: the forward kernel's fp16 tile image (one 32 KB bulk copy), else converted from the fp32 rows
   auto issue_e16 = [&](long long tile_) {      // thread 0
     mbar_arrive_expect_tx(&bar_e, SLOT);
-    bulk_g2s(sE, reinterpret_cast<const uint8_t*>(p.e16) + (size_t)tile_ * SLOT, SLOT, &bar_e);
+    bulk_g2s(sEimg, reinterpret_cast<const uint8_t*>(p.e16) + (size_t)tile_ * SLOT, SLOT, &bar_e);
   };
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
@@ -260,13 +270,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       if (it == 0) mbar_wait(&bar_wA, 0);
       if (p.e16 != nullptr) mbar_wait(&bar_e, it & 1);
       fence_after_sync();
-      umma_tile(tm_W, uE, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
+      umma_tile(tm_W, uEimg, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
       mma_commit(&bar_mma);
-      if (FAST) {               // upstream rows of this tile -> lin32, once the previous tile's g_e store has left it
-        bulk_wait_read0();
-        mbar_arrive_expect_tx(&bar_g2, tile_rows_bytes(tile));
-        bulk_g2s(lin32, p.g_eout + tile * TILE_ROWS * H, tile_rows_bytes(tile), &bar_g2);
-      }
     }
     {
       // under the product: P_j rows -> sH1 (staging, overwritten in place by h1), P_i rows -> registers
@@ -279,7 +284,12 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       __syncthreads();      // the staged P_j rows (issued during the previous tile) are visible to every thread
       mma_wait();
       if (m.tid == 0) {
-        load_w_slot(sWA, p.W, 2, &bar_wA);   // W3 -> A
+        if (FAST) {             // upstream rows of this tile -> lin32, once the previous tile's g_e store has left it
+          bulk_wait_read0();    // (not earlier: while thread 0 sits here the other warps wait at the next barrier)
+          mbar_arrive_expect_tx(&bar_g2, tile_rows_bytes(tile));
+          bulk_g2s(lin32, p.g_eout + tile * TILE_ROWS * H, tile_rows_bytes(tile), &bar_g2);
+        }
+        load_w_slot(sWA, p.W, FAST ? 3 : 2, &bar_wA);   // W3 -> A (FAST: W4 -> A, W3 is resident in slot C)
         // sE is dead: the next tile's e image (FAST: requested later, at D4 -- here it would compete with the
         // upstream tile the g build is about to wait for)
         if (!FAST && has_next && p.e16 != nullptr) issue_e16(tile + gridDim.x);
@@ -358,16 +368,17 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       float4 bb[8];
       load_vec32(p.b2, m.c0, bb);
       mma_wait();
-      if (m.tid == 0) load_w_slot(sWB, p.W, 3, &bar_wB);     // W4 -> B
+      if (!FAST && m.tid == 0) load_w_slot(sWB, p.W, 3, &bar_wB);     // W4 -> B
       epi_bias_relu_q(tm_W + qoff, bb, sH2, m, nullptr, 0);
       tile_ready();
     }
     // ---- R3
     {
       if (m.tid == 0) {
-        mbar_wait(&bar_wA, 1);
+        if (!FAST) mbar_wait(&bar_wA, 1);
+        else if (it == 0) mbar_wait(&bar_wC, 0);
         fence_after_sync();
-        umma_tile(tm_W, uH2, 128, 0, uWA, 128, 0, 0, 128, 8, 0);
+        umma_tile(tm_W, uH2, 128, 0, uW3, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
       }
       float4 bb[8];
@@ -380,9 +391,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     // ---- R4 + RMSNorm backward
     {
       if (m.tid == 0) {
-        mbar_wait(&bar_wB, 1);
+        mbar_wait(FAST ? &bar_wA : &bar_wB, 1);
         fence_after_sync();
-        umma_tile(tm_W, uH3, 128, 0, uWB, 128, 0, 0, 128, 8, 0);
+        umma_tile(tm_W, uH3, 128, 0, uW4, 128, 0, 0, 128, 8, 0);
         mma_commit(&bar_mma);
       }
       float4 bb[8], sc[8];
@@ -396,34 +407,39 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     // ---- D4: g_h3 = dz4 W4 ; dW4 += dz4^T h3
     if (m.tid == 0) {
       fence_after_sync();
-      umma_tile(tm_W, uG, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_W, uG, 128, 0, uW4, 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
     if (m.tid == 0) {
-      load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
-      if (FAST && has_next) issue_e16(tile + gridDim.x);
+      if (!FAST) load_w_slot(sWB, p.W, 1, &bar_wB);     // W2 -> B
+      if (FAST) {
+        load_w_slot(sWA, p.W, 0, &bar_wA);                 // W4 is done: We -> A for D1 (and the next tile's R1)
+      }
     }
     epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
     // ---- D3
     if (m.tid == 0) {
+      // FAST: sG is dead (D4's products are done and every thread is past its column sums of it, barrier above):
+      // the next tile's e image lands there
+      if (FAST && has_next) issue_e16(tile + gridDim.x);
       fence_after_sync();
-      umma_tile(tm_W, uH3, 128, 0, uWA, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_W, uH3, 128, 0, uW3, 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
     }
     if (!FAST && has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
-    if (m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
+    if (!FAST && m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
     epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
     // ---- D2
     if (m.tid == 0) {
-      mbar_wait(&bar_wB, 0);
+      if (!FAST) mbar_wait(&bar_wB, 0);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
