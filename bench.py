@@ -42,8 +42,8 @@ BYTES_EDGE_STEP, BYTES_NODE_STEP = 2568, 7168          # SURVEY.md 8(d), fwd+bwd
 FLOPS_EDGE_STEP, FLOPS_NODE_STEP = 589824, 491520
 EDGE_BWD_BYTES_EDGE, EDGE_BWD_BYTES_NODE = 1540, 2048  # the dominant kernel's share
 # dram__bytes_read.sum + dram__bytes_write.sum of one edge_bwd_kernel launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r01_ncu_edge_bwd_v4.md); not re-measured by bench.py
-EDGE_BWD_DRAM_BYTES_NCU = 458_341_120 + 212_472_320
+# `ncu --set full` capture (profiles/r01_ncu_edge_bwd_v6.md); not re-measured by bench.py
+EDGE_BWD_DRAM_BYTES_NCU = 338_405_632 + 209_580_800
 
 
 def load_mesh():
@@ -202,8 +202,10 @@ def workload_config(n_gpus, copies=32, copies_note=None):
                        "block-diagonal batch; MGN processor (only_processor=True), H=128, 15 steps, fwd+bwd",
            "nodes_per_gpu": 1923 * copies, "edges_per_gpu": 11070 * copies, "hidden": H, "mp_steps": STEPS_MP,
            "parallelism": f"dp{n_gpus}",
-           "numerics": "fp16 tensor-core operands, fp32 accumulation, fp32 residual streams / RMSNorm / aggregation",
-           "l2": "inputs larger than L2: each of the 15 saved edge-latent versions is 181 MB (L2 126 MB)"}
+           "numerics": "fp16 tensor-core operands, fp32 accumulation; residual adds, RMSNorm, aggregation and gradients in "
+                       "fp32; edge stream held between steps as fp16 image + fp16 remainder (>= 21 bits)",
+           "l2": "inputs larger than L2: every step streams a 181 MB edge-latent version (91 MB image + 91 MB remainder) "
+                 "and a 181 MB edge-gradient version; 3.5 GB of saved state per fwd+bwd (L2 126 MB)"}
     if copies_note:
         cfg["sample"] = copies_note
     return cfg
@@ -403,7 +405,7 @@ def run_b200(args):
             "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "edge_bwd_kernel", "achieved": ach, "peak": hbm, "unit": "GB/s",
                          "frac": ach / hbm, "traffic": EDGE_BWD_DRAM_BYTES_NCU if copies == 32 else None,
-                         "traffic_source": "ncu --set full, profiles/r01_ncu_edge_bwd_v4.md (bytes per launch)",
+                         "traffic_source": "ncu --set full, profiles/r01_ncu_edge_bwd_v6.md (bytes per launch)",
                          "peak_source": which,
                          "ms_per_launch": edge_bwd_ms, "launches_timed": len(durs),
                          "timed_in": "eager pass of the same steps (one CUDA event pair per launch) run before the "
