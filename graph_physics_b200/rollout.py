@@ -1,0 +1,137 @@
+"""Autoregressive rollout: the forward-only loop of the reference's validation / predict steps
+(`LightningModule._make_prediction`, graphphysics/training/lightning_module.py:168-202, driven by `validation_step`
+:204-232 and `predict_step` :300-329) with everything a trajectory shares kept on the device -- topology and its CSR,
+packed weights, every buffer -- and ONE captured CUDA graph replayed per time step.
+
+Reference semantics of one step (batch size 1, topology constant along the trajectory):
+
+    batch = batch.clone()
+    if last_prediction is not None:
+        batch.x[:, out_start:out_end] = last_prediction
+        if use_previous_data: batch.x[:, prev_start:prev_end] = last_previous_data_prediction
+    mask = build_mask(param, batch)            # NOT (NORMAL or OUTFLOW): boundary nodes, from batch.x[:, node_type_index]
+    current_output = batch.x[:, out_start:out_end]
+    predicted = model(batch)                   # no_grad
+    predicted[mask] = target[mask]             # boundary nodes reset to the ground truth
+    last_prediction = predicted
+    last_previous_data_prediction = predicted - current_output
+
+Here the first step is made uniform with the others by initialising `last_prediction` / `last_previous_data_prediction`
+from the first frame's own columns (overwriting a column with itself), so a single graph serves the whole trajectory.
+A batch of a few hundred sequential steps on a ~2 k-node mesh is launch-latency bound when run eagerly (~150 kernel
+launches of a few microseconds each per step); the replay removes that.
+
+`predict_fn(graph) -> [N, d]` is any forward-only callable built on this package's modules (e.g. an
+`EncodeProcessDecode` wrapped with the simulator's pre / post-processing); it must read `graph.x` (and
+`graph.edge_attr`, `graph.edge_index`) from the tensors it is handed, because those are the static buffers of the capture.
+"""
+from __future__ import annotations
+
+from typing import Callable, Iterable, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib as L
+
+# reference graphphysics/utils/nodetype.py:4-12
+NODE_NORMAL, NODE_OUTFLOW = 0, 5
+
+
+def boundary_mask(x: torch.Tensor, node_type_index: int) -> torch.Tensor:
+    """`build_mask` (lightning_module.py:17-25): True where the node is neither NORMAL nor OUTFLOW."""
+    nt = x[:, 0, node_type_index] if x.dim() > 2 else x[:, node_type_index]
+    return torch.logical_not(torch.logical_or(nt == NODE_NORMAL, nt == NODE_OUTFLOW))
+
+
+class Rollout:
+    """rollout = Rollout(predict_fn, graph, out_slice=(s, e), node_type_index=i, prev_slice=None)
+    preds = rollout.run(frames)          # frames: iterable of (x_t [N,F], y_t [N,d]); -> [T,N,d] on the device
+
+    `graph` is duck typed (`.x`, `.edge_attr`, `.edge_index`, optional `.pos`); its tensors become the static
+    buffers.  `capture=False` runs the same step eagerly (the check the tests compare the replay against)."""
+
+    def __init__(self, predict_fn: Callable, graph, out_slice: Tuple[int, int], node_type_index: int,
+                 prev_slice: Optional[Tuple[int, int]] = None, capture: bool = True, warmup: int = 2):
+        L.require_device(graph.x)
+        self.predict_fn = predict_fn
+        self.graph = graph
+        self.o0, self.o1 = int(out_slice[0]), int(out_slice[1])
+        self.prev = (int(prev_slice[0]), int(prev_slice[1])) if prev_slice is not None else None
+        self.nt = int(node_type_index)
+        n, d = graph.x.shape[0], self.o1 - self.o0
+        dev = graph.x.device
+        self.y = torch.zeros((n, d), dtype=graph.x.dtype, device=dev)
+        self.last = torch.zeros((n, d), dtype=graph.x.dtype, device=dev)
+        self.last_prev = torch.zeros((n, d), dtype=graph.x.dtype, device=dev) if self.prev is not None else None
+        self.pred = torch.zeros((n, d), dtype=graph.x.dtype, device=dev)
+        self.capture = bool(capture)
+        self.warmup = int(warmup)
+        self._graph = None
+
+    # one step on the static buffers (graph.x already holds frame t's features, self.y its target)
+    def _step(self):
+        x = self.graph.x
+        x[:, self.o0:self.o1] = self.last
+        if self.prev is not None:
+            x[:, self.prev[0]:self.prev[1]] = self.last_prev
+        mask = boundary_mask(x, self.nt)
+        cur = x[:, self.o0:self.o1].clone()
+        with torch.no_grad():
+            out = self.predict_fn(self.graph)
+        out = torch.where(mask.unsqueeze(-1), self.y, out)
+        if self.prev is not None:
+            self.last_prev.copy_(out - cur)
+        self.last.copy_(out)
+        self.pred.copy_(out)
+
+    def _ensure_captured(self):
+        if self._graph is not None or not self.capture:
+            return
+        keep = [t.clone() for t in (self.graph.x, self.last, self.pred)]
+        keep_prev = self.last_prev.clone() if self.last_prev is not None else None
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(self.warmup):
+                self._step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self._step()
+        self._graph = g
+        # the warm-up / capture runs advanced the state: put it back
+        self.graph.x.copy_(keep[0]); self.last.copy_(keep[1]); self.pred.copy_(keep[2])
+        if keep_prev is not None:
+            self.last_prev.copy_(keep_prev)
+
+    def reset(self, x0: torch.Tensor):
+        """Start of a trajectory (`_reset_validation_trajectory`, lightning_module.py:163-166): no previous prediction;
+        the first step then keeps the first frame's own output / previous-data columns."""
+        x0 = x0.to(self.graph.x.device)
+        self.last.copy_(x0[:, self.o0:self.o1])
+        if self.prev is not None:
+            self.last_prev.copy_(x0[:, self.prev[0]:self.prev[1]])
+
+    def step(self, x_t: torch.Tensor, y_t: torch.Tensor) -> torch.Tensor:
+        """One `_make_prediction` call: frame features and target in, prediction out (a view of a static buffer:
+        copy it if it must survive the next step)."""
+        self.graph.x.copy_(x_t, non_blocking=True)
+        self.y.copy_(y_t, non_blocking=True)
+        if self.capture:
+            self._ensure_captured()
+            self._graph.replay()
+        else:
+            self._step()
+        return self.pred
+
+    def run(self, frames: Iterable[Sequence[torch.Tensor]]) -> torch.Tensor:
+        out = []
+        first = True
+        for x_t, y_t in frames:
+            if first:
+                self.graph.x.copy_(x_t, non_blocking=True)      # (the capture warm-up must see real features)
+                self.reset(x_t)
+                first = False
+            out.append(self.step(x_t, y_t).clone())
+        return torch.stack(out) if out else torch.empty((0,) + tuple(self.pred.shape), device=self.pred.device)
