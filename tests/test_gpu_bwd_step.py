@@ -131,3 +131,51 @@ def test_ragged_random_graphs_bwd(n, e):
     g = torch.Generator().manual_seed(n * 1000 + e)
     ei = torch.randint(0, n, (2, e), generator=g).numpy()
     _check(ei, n, e, 3, True)
+
+
+def test_processor_loop_edge_backward_equals_general_path(golden_dir):
+    """edge_bwd_kernel<true> (no rowmap, upstream gradient and e images given: g built from a bulk-loaded upstream tile,
+    three weight slots) against edge_bwd_kernel<false> forced by an identity rowmap, same inputs: same products on the
+    same operands -> identical g_e and dz1 images; weight gradients equal up to the order of the cross-CTA reductions."""
+    import numpy as np
+    from graph_physics_b200 import graph as G, ops
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    n1 = z["points"].shape[0]
+    ei = G.tile_batch(torch.as_tensor(z["edge_index"].astype(np.int64)).cuda(), n1, 5)
+    N, E = n1 * 5, ei.shape[1]
+    assert E % 128 != 0
+    csr = G.build_csr(ei, N)
+    dev = "cuda"
+    torch.manual_seed(11)
+    ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    b = [torch.randn(128, device=dev) * 0.05 for _ in range(4)]
+    sc = 1.0 + 0.1 * torch.randn(128, device=dev)
+    packed = ops.pack_block(ew, nw)
+    x = torch.randn(N, 128, device=dev)
+    e = torch.randn(E, 128, device=dev)
+    P = ops.p_fwd(x, packed, b[0])
+    e16 = ops.e16_image(E, dev)
+    ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e16_out=e16)
+    ge = torch.randn(E, 128, device=dev)
+    g_aggr = torch.randn(N, 128, device=dev)
+    ident = torch.arange(E, dtype=torch.int32, device=dev)
+    outs = []
+    for rowmap in (None, ident):
+        grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
+        dz16 = ops.e16_image(E, dev).zero_()
+        g_e, _ = ops.edge_bwd(None, rowmap, ge, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc,
+                              grad, dz16=dz16, e16=e16)
+        torch.cuda.synchronize()
+        outs.append((g_e, ops.image_rows(dz16, E), grad))
+    (ge_f, dz_f, gr_f), (ge_g, dz_g, gr_g) = outs
+    assert torch.equal(ge_f, ge_g)
+    assert torch.equal(dz_f, dz_g)
+    assert float((gr_f - gr_g).abs().max()) <= 1e-5 * float(gr_g.abs().max())
+    # in place (what the processor loop does): same result
+    ge_ip = ge.clone()
+    grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, device=dev)
+    ops.edge_bwd(None, None, ge_ip, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, grad,
+                 dz16=ops.e16_image(E, dev), e16=e16, inplace=True)
+    torch.cuda.synchronize()
+    assert torch.equal(ge_ip, ge_f)
