@@ -36,8 +36,9 @@ class PartitionEngine:
     the halo rows of `g_ext()` to their owners after `bwd_step(k)`."""
 
     def __init__(self, part: Partition, block_params: Sequence[Sequence[torch.Tensor]], need_grad: bool = True,
-                 csr: Optional[G.CSRGraph] = None):
+                 csr: Optional[G.CSRGraph] = None, need_edges: bool = True):
         self.part, self.K, self.need_grad = part, len(block_params), need_grad
+        self.need_edges = bool(need_edges)      # False: the fp32 rows of the final edge latents are never written
         if part.num_owned == 0:
             raise ValueError("a partition must own at least one node")
         self.csr = csr if csr is not None else G.build_csr(part.edge_index, part.num_ext)
@@ -60,7 +61,12 @@ class PartitionEngine:
         x0[:part.num_owned] = x_owned.detach()
         self.xs: List[Optional[torch.Tensor]] = [x0]
         self.e = e_local.detach().contiguous()
-        self.e_bufs = [torch.empty_like(self.e) for _ in range(min(K, 2))]
+        # between steps the edge stream is an fp16 image + fp16 remainder (csrc/edge_fwd_hl.cu, as in processor.py):
+        # only step 0 reads fp32 rows, only the last step writes them (and only if somebody wants them)
+        self.hl = ops.EDGE_FWD_HL and self.E > 0
+        self.e_bufs = [torch.empty_like(self.e) for _ in range(min(K, 2))] if not self.hl else None
+        self.e_last = torch.empty_like(self.e) if (self.hl and (self.need_edges or K == 1)) else None
+        self.lo_bufs = [ops.e16_image(self.E, dev) for _ in range(min(K - 1, 2))] if self.hl else None
         self.aggrs, self.Ps, self.saves, self.e16s = [], [], [], []
         self.img = None
         if not self.need_grad:
@@ -85,22 +91,32 @@ class PartitionEngine:
             P, aggr, sv = self.P, self.aggr, None
         _timed("p_fwd", ops.p_fwd, x, self.packed[k], b[1], out=P)
         if E > 0:
-            e_out = self.e_bufs[k & 1]
+            last = k + 1 == K
+            e_out = (self.e_last if last else None) if self.hl else self.e_bufs[k & 1]
             if k == 0:
                 self.img = ops.e16_image(E, dev) if ng else self.img_bufs[1 % len(self.img_bufs)]
                 img_self, img_in = self.img, None
             else:
                 img_self, img_in = None, self.img
             img_next = None
-            if k + 1 < K:
+            if not last:
                 img_next = ops.e16_image(E, dev) if ng else self.img_bufs[k & 1]
+            lo_next = self.lo_bufs[k & 1] if (self.hl and not last) else None
             rowmap = csr.perm if (k == 0 and not csr.identity) else None
-            _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
-                   b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
-                   e16_next=img_next, out_in_csr_order=True)
+            if self.hl and k > 0:
+                _timed("edge_fwd", ops.edge_fwd_hl, img_in, self.lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers,
+                       n_ext, self.packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out,
+                       aggr=aggr)
+            else:
+                _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
+                       b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
+                       e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
+                       write_rows=not (self.hl and e_out is None))
             if ng:
                 self.e16s.append(self.img)
-            self.e, self.img = e_out, img_next
+            self.img = img_next
+            if e_out is not None:
+                self.e = e_out
         else:
             aggr.zero_()
             if ng:
@@ -117,6 +133,8 @@ class PartitionEngine:
         x = self.xs[-1][:self.part.num_owned]
         if not need_edges:
             return x, self.e.new_empty((0, H))
+        if not self.need_edges and self.hl and self.K > 1:
+            raise ValueError("this engine was built with need_edges=False: the final edge rows were not written")
         if self.csr.identity or self.E == 0:
             return x, self.e
         e_ret = torch.empty_like(self.e)
@@ -212,7 +230,7 @@ class PartitionedProcessorFn(torch.autograd.Function):
         K = int(num_steps)
         blocks = [params[18 * k:18 * (k + 1)] for k in range(K)]
         need_grad = any(ctx.needs_input_grad)
-        eng = PartitionEngine(part, blocks, need_grad=need_grad, csr=csr)
+        eng = PartitionEngine(part, blocks, need_grad=need_grad, csr=csr, need_edges=need_edges)
         halo = HaloExchange(part, group)
         eng.fwd_begin(x_owned, e_local)
         for k in range(K):
