@@ -564,6 +564,7 @@ struct NodeBwdParams {
   const float* b4;
   const float* scale;
   float* grad;
+  int no_norm;              // the block has no RMSNorm (decoder): dz4 = g, no scale gradient
 };
 
 __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
@@ -653,7 +654,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       load_vec32(p.b4, m.c0, bb);
       load_vec32(p.scale, m.c0, sc);
       mma_wait();
-      dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);
+      if (!p.no_norm) dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);      // else sG already holds dz4 = g
       tile_ready();
     }
     // ---- D4
@@ -1126,9 +1127,10 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
 }
 
 // Backward of the node update (autograd of layers.py:733-746, 699) from the fp16 hidden saves.
-extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
-                            float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                            const float* scale, float* grad_block, void* stream_) {
+// flags bit 0: the block has no RMSNorm (see mgn_node_fwd2)
+extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                             float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                             const float* scale, float* grad_block, int flags, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && g_xout && h1 && h2 && h3 && g_x && g_aggr && dz1 && packed && b4 && scale && grad_block,
                 "node_bwd: bad args");
@@ -1136,7 +1138,7 @@ extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, cons
   p.N = N; p.g_xout = g_xout; p.h1 = (const __half*)h1; p.h2 = (const __half*)h2; p.h3 = (const __half*)h3;
   p.g_x = g_x; p.g_aggr = g_aggr; p.dz1 = (__half*)dz1;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
-  p.b4 = b4; p.scale = scale; p.grad = grad_block;
+  p.b4 = b4; p.scale = scale; p.grad = grad_block; p.no_norm = flags & 1;
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(node_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_BWD_SMEM));
@@ -1146,6 +1148,12 @@ extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, cons
   node_bwd_kernel<<<grid, NT, NODE_BWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
+}
+
+extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                            float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                            const float* scale, float* grad_block, void* stream_) {
+  return mgn_node_bwd2(N, g_xout, h1, h2, h3, g_x, g_aggr, dz1, packed, b4, scale, grad_block, 0, stream_);
 }
 
 // Backward of the gathers x[col], x[row]: dP [N,256] fp16 = [sum of dz1 over received edges | over sent edges] from

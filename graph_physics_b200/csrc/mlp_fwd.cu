@@ -43,6 +43,7 @@ struct FwdParams {
                               // the residual stream as image + remainder); `out` may then be null
   long long* dbg;             // developer timeline (null = off)
   int dbg_cap;
+  int no_norm;                // node: the block has no RMSNorm (the decoder, build_mlp(..., layer_norm=False)): out = in0 + z4
 };
 
 template <bool EDGE>
@@ -324,7 +325,12 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       float4 sc[8];
       load_vec32(p.scale, m.c0, sc);
       ss = row_sum4(ss, tail->red, m);
-      const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+      float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+      if (!EDGE && p.no_norm) {
+        inv = 1.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sc[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float4 o;
@@ -606,9 +612,11 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
 }
 
 // GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).
-extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
-                            const float* b1, const float* b2, const float* b3, const float* b4,
-                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
+// flags bit 0: no RMSNorm (x_out = x + MLP(...) with the last layer's bias only; `scale` is ignored but must be valid)
+extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                             const float* b1, const float* b2, const float* b3, const float* b4,
+                             const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags,
+                             void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && x && aggr && x_out && packed && b1 && b2 && b3 && b4 && scale, "node_fwd: bad args");
   MGN_CHECK_ARG(x != x_out, "node_fwd: in-place not supported");
@@ -619,6 +627,7 @@ extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float*
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
   p.b1 = b1; p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
+  p.no_norm = flags & 1;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
@@ -629,6 +638,12 @@ extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float*
   mlp_fwd_kernel<false><<<grid, NT, NODE_FWD_SMEM, stream>>>(p);
   MGN_LAUNCH_CHECK();
   return MGN_OK;
+}
+
+extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                            const float* b1, const float* b2, const float* b3, const float* b4,
+                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
+  return mgn_node_fwd2(N, x, aggr, x_out, packed, b1, b2, b3, b4, scale, save_h1, save_h2, save_h3, 0, stream_);
 }
 
 // per-node layer-1 partial products of the edge block: P = [x W_i^T + b1 | x W_j^T] (fp16)

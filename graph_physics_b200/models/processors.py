@@ -10,7 +10,8 @@ torch_geometric `Data` / `Batch` or any object with those attributes).  The 15-b
 (`processors.py:130-131`) runs as one fused autograd node on the sm_100a kernels
 (graph_physics_b200.processor); the two encoder MLPs run on the fused node kernels
 (graph_physics_b200.encoder) when their shape allows (input width <= 128) and
-`fused_encoders` is left on; the decoder (no RMSNorm, 2-3 outputs, N rows only) is a plain torch module.
+`fused_encoders` is left on; the decoder (no RMSNorm, 2-3 outputs) runs on the same kernels with their no-norm flag
+(last layer zero-padded to 128 rows).
 """
 from __future__ import annotations
 
@@ -81,4 +82,6 @@ class EncodeProcessDecode(nn.Module):
                                        need_edges=False)
         if self.only_processor:
             return x
+        if self.fused_encoders and x.is_cuda and _enc.decoder_supported(self.decode_module):
+            return _enc.run_decoder(self.decode_module, x)
         return self.decode_module(x)

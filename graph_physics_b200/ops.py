@@ -140,16 +140,16 @@ def image_rows(img: torch.Tensor, num_rows: int) -> torch.Tensor:
 
 
 def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
-             x_out: Optional[torch.Tensor] = None, saves=None) -> torch.Tensor:
-    """saves: `node_saves(N)` buffers (tile images), or None."""
+             x_out: Optional[torch.Tensor] = None, saves=None, norm: bool = True) -> torch.Tensor:
+    """saves: `node_saves(N)` buffers (tile images), or None.  norm=False: the block has no RMSNorm (decoder)."""
     N = x.shape[0]
     if saves is not None and any(sv.numel() < ((N + 127) // 128) * 128 * H for sv in saves):
         raise ValueError("node_fwd: saves must be node_saves(N) tile-image buffers")
     if x_out is None:
         x_out = torch.empty_like(x)
     s1, s2, s3 = saves if saves is not None else (None, None, None)
-    L.check(L.lib().mgn_node_fwd(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
-                                 L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.stream()))
+    L.check(L.lib().mgn_node_fwd2(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
+                                  L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.i32(0 if norm else 1), L.stream()))
     return x_out
 
 
@@ -198,7 +198,7 @@ def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, pac
     return g_e, dz16
 
 
-def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None):
+def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None, norm: bool = True):
     """-> (g_x direct part, g_aggr, dz1 fp16)."""
     N = g_xout.shape[0]
     if g_x is None:
@@ -208,8 +208,8 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
     if dz1 is None:
         dz1 = torch.empty((N, H), dtype=torch.float16, device=g_xout.device)
     h1, h2, h3 = saves
-    L.check(L.lib().mgn_node_bwd(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
-                                 L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
+    L.check(L.lib().mgn_node_bwd2(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
+                                  L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.i32(0 if norm else 1), L.stream()))
     return g_x, g_aggr, dz1
 
 

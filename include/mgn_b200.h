@@ -150,6 +150,11 @@ int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, 
 int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                  const float* b1, const float* b2, const float* b3, const float* b4,
                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream);
+/* mgn_node_fwd with flags: bit 0 = the block has no RMSNorm (build_mlp(..., layer_norm=False), the decoder of
+ * EncodeProcessDecode, processors.py:85-90): x_out = x + MLP(cat[x, aggr]); `scale` is ignored. */
+int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                  const float* b1, const float* b2, const float* b3, const float* b4,
+                  const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags, void* stream);
 
 /* ------------------------------------------------------------------ backward of the step
  * What torch.autograd derives from GraphNetBlock.forward in the reference.  Parameter gradients of
@@ -162,6 +167,10 @@ int64_t mgn_grad_block_floats(void);
 int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                  float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
                  const float* scale, float* grad_block, void* stream);
+/* mgn_node_bwd with flags: bit 0 = no RMSNorm (see mgn_node_fwd2): dz4 = g_xout, no scale gradient. */
+int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                  float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                  const float* scale, float* grad_block, int flags, void* stream);
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);

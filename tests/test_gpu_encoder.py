@@ -102,3 +102,34 @@ def test_fused_encoder_gradients_through_the_same_active_set():
         errs[name] = _rel(prm.grad, p64["enc." + name].grad)
     bad = {k: v for k, v in errs.items() if not v < 5e-3}
     assert not bad, bad
+
+
+@pytest.mark.parametrize("rows,dout", [(1923, 2), (500, 3), (130, 128), (5, 1)])
+def test_fused_decoder_matches_eager_module(rows, dout):
+    """decode_module = build_mlp(128, 128, out, layer_norm=False) (processors.py:85-90) on the node kernels with the
+    no-RMSNorm flag, against the same nn.Sequential in fp64."""
+    from graph_physics_b200 import encoder as ENC
+    from graph_physics_b200.models.layers import build_mlp
+    torch.manual_seed(rows + dout)
+    mlp = build_mlp(128, 128, dout, layer_norm=False).cuda()
+    assert ENC.decoder_supported(mlp) and not ENC.decoder_supported(build_mlp(128, 128, 2).cuda())
+    ref = copy.deepcopy(mlp).double()
+    lat = torch.randn(rows, 128, device="cuda")
+    g = torch.randn(rows, dout, device="cuda") / (rows * dout) ** 0.5
+    l1 = lat.clone().requires_grad_(True)
+    out = ENC.run_decoder(mlp, l1)
+    assert out.shape == (rows, dout)
+    out.backward(g)
+    l2 = lat.double().requires_grad_(True)
+    want = ref(l2)
+    want.backward(g.double())
+    assert _rel(out.detach(), want.detach()) < 2e-3
+    errs = {"input": _rel(l1.grad, l2.grad)}
+    for (name, p), (_, q) in zip(mlp.named_parameters(), ref.named_parameters()):
+        assert p.grad is not None and p.grad.shape == p.shape, name
+        errs[name] = _rel(p.grad, q.grad)
+    bad = {k: v for k, v in errs.items() if not v < 6e-2}
+    assert not bad, bad
+    with torch.no_grad():
+        out2 = ENC.run_decoder(mlp, lat)
+    assert torch.equal(out2, out.detach())
