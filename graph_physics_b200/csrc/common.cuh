@@ -55,3 +55,33 @@ static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b;
 // developer timeline buffer (abi_core.cu); kernels receive it through their parameter struct
 extern long long* g_mgn_timeline_host;
 extern int g_mgn_timeline_cap_host;
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every step kernel is launched with cudaLaunchAttributeProgrammaticStreamSerialization (MGN_PDL=0 switches it off):
+// its CTAs may be scheduled as soon as every CTA of the previous kernel in the stream has passed pdl_launch() or has
+// exited -- i.e. while the tail of that kernel still runs -- and they block in pdl_wait() until the previous kernel
+// has completed and its writes are visible.  Everything before pdl_wait() (barrier init, TMEM allocation) therefore
+// overlaps the previous kernel's last wave, and the launch latency between dependent kernels disappears.  A kernel
+// must not touch global memory before pdl_wait().
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+#include <stdlib.h>
+template <class P>
+static inline cudaError_t mgn_launch(void (*kernel)(P), int grid, int block, size_t smem, cudaStream_t stream,
+                                     const P& p) {
+  static const bool pdl = !(getenv("MGN_PDL") && atoi(getenv("MGN_PDL")) == 0);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+#endif

@@ -67,6 +67,8 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tmem_acc = tmem_slot;
   const uint32_t taddr = tmem_acc + m.lane_off + m.c0;
   const uint32_t tmem_a = tmem_acc + 128;
@@ -368,7 +370,7 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
-  edge_fwd_hl_kernel<<<grid, NT, EDGE_HL_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(edge_fwd_hl_kernel, grid, NT, EDGE_HL_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

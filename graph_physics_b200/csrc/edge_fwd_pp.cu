@@ -67,6 +67,8 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_pp_kernel(const EdgePPParams p
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tm = tmem_slot;
   const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW), sPj_u32 = smem_u32(sPj);
   if (m.tid == 0) {
@@ -393,7 +395,7 @@ extern "C" int mgn_edge_fwd_pp(int64_t E, int64_t N, const float* e_in, const vo
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
-  edge_fwd_pp_kernel<<<grid, NT, EDGE_PP_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(edge_fwd_pp_kernel, grid, NT, EDGE_PP_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

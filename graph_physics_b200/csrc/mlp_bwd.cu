@@ -137,6 +137,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
   const uint32_t qoff = m.lane_off + m.c0;
   const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
@@ -593,6 +595,8 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
   const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t uW[2] = {smem_u32(sW[0]), smem_u32(sW[1])};
@@ -796,6 +800,8 @@ __device__ __forceinline__ uint4 ld_dz16_chunk(const __half* img, int pos, int l
 
 // One half-warp per (node, side): a plain high-occupancy streaming kernel (no shared memory), fp32 sums, 4 rows in flight
 __global__ void __launch_bounds__(256) dp_gather_kernel(const DpGatherParams p) {
+  pdl_wait();
+  pdl_launch();
   const int l = threadIdx.x & 15;
   const long long ntask = 2 * p.N;
   for (long long task = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4; task < ntask;
@@ -863,6 +869,8 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t tm_W = tmem_slot, tm_dWi = tmem_slot + 128, tm_dWj = tmem_slot + 256;
   if (m.tid == 0) {
@@ -971,6 +979,8 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t tm = tmem_slot;
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
@@ -1047,6 +1057,8 @@ __global__ void __launch_bounds__(NT, 1) edge_wgrad1_kernel(const EdgeWgrad1Para
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tm = tmem_slot;
   const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
   const uint32_t my_tiles = blockIdx.x < num_tiles ? (uint32_t)((num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
@@ -1119,9 +1131,9 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
   static const bool no_fast = getenv("MGN_EDGE_BWD_GENERAL") != nullptr;      // developer switch: always the general path
   if (!no_fast && rowmap == nullptr && g_eout != nullptr && e16 != nullptr)
-    edge_bwd_kernel<true><<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
+    MGN_CUDA(mgn_launch(edge_bwd_kernel<true>, grid, NT, EDGE_BWD_SMEM, stream, p));
   else
-    edge_bwd_kernel<false><<<grid, NT, EDGE_BWD_SMEM, stream>>>(p);
+    MGN_CUDA(mgn_launch(edge_bwd_kernel<false>, grid, NT, EDGE_BWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -1145,7 +1157,7 @@ extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, con
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  node_bwd_kernel<<<grid, NT, NODE_BWD_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(node_bwd_kernel, grid, NT, NODE_BWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -1165,7 +1177,7 @@ extern "C" int mgn_dp_gather(int64_t N, const void* dz16, const int32_t* rowptr,
   DpGatherParams p{N, (const __half*)dz16, rowptr, rowptr_s, out_pos, (__half*)dP};
   const int64_t blocks = ceil_div64(2 * N * 16, 256);
   const int grid = (int)std::min<int64_t>(blocks, (int64_t)mgn_num_sms() * 8);
-  dp_gather_kernel<<<grid, 256, 0, stream>>>(p);
+  MGN_CUDA(mgn_launch(dp_gather_kernel, grid, 256, 0, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -1183,7 +1195,7 @@ extern "C" int mgn_p_bwd(int64_t N, const void* dP, const float* x, float* g_x, 
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  p_bwd_kernel<<<grid, NT, P_BWD_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(p_bwd_kernel, grid, NT, P_BWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -1200,7 +1212,7 @@ extern "C" int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  node_wgrad1_kernel<<<grid, NT, NODE_WGRAD1_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(node_wgrad1_kernel, grid, NT, NODE_WGRAD1_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -1219,7 +1231,7 @@ extern "C" int mgn_edge_wgrad1(int64_t E, const void* dz16, const void* e16, flo
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
-  edge_wgrad1_kernel<<<grid, NT, EDGE_WGRAD1_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(edge_wgrad1_kernel, grid, NT, EDGE_WGRAD1_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tmem_acc = tmem_slot;
   const uint32_t taddr = tmem_acc + m.lane_off + m.c0;
   const uint32_t tmem_a = tmem_acc + 128;
@@ -426,6 +428,8 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
+  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tmem_acc = tmem_slot;
   if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, 2 * TILE_BYTES);
@@ -507,6 +511,8 @@ struct PackParams {
 };
 
 __global__ void pack_block_kernel(const PackParams p) {
+  pdl_wait();
+  pdl_launch();
   // one thread per 8 consecutive columns (one 16-byte chunk)
   const int total_chunks = (int)(PK_BYTES / 16);
   for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < total_chunks; c += gridDim.x * blockDim.x) {
@@ -552,7 +558,7 @@ extern "C" int mgn_pack_block(const float* eW1, const float* eW2, const float* e
                               void* packed, void* stream) {
   MGN_CHECK_ARG(eW1 && eW2 && eW3 && eW4 && nW1 && nW2 && nW3 && nW4 && packed, "pack_block: null pointer");
   PackParams p{{eW1, eW2, eW3, eW4}, {nW1, nW2, nW3, nW4}, (uint8_t*)packed};
-  pack_block_kernel<<<88, 256, 0, (cudaStream_t)stream>>>(p);
+  MGN_CUDA(mgn_launch(pack_block_kernel, 88, 256, 0, (cudaStream_t)stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -596,7 +602,7 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
-  mlp_fwd_kernel<true><<<grid, NT, EDGE_FWD_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(mlp_fwd_kernel<true>, grid, NT, EDGE_FWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -635,7 +641,7 @@ extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  mlp_fwd_kernel<false><<<grid, NT, NODE_FWD_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(mlp_fwd_kernel<false>, grid, NT, NODE_FWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
@@ -659,7 +665,7 @@ extern "C" int mgn_p_fwd(int64_t N, const float* x, const void* packed, const fl
     attr = true;
   }
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(N, TILE_ROWS));
-  p_fwd_kernel<<<grid, NT, P_FWD_SMEM, stream>>>(p);
+  MGN_CUDA(mgn_launch(p_fwd_kernel, grid, NT, P_FWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }
