@@ -410,11 +410,17 @@ struct PFwdParams {
 };
 
 __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
+  // The P rows leave through a shared-memory staging tile and one 512-byte bulk copy per row: a row-owner store of the
+  // accumulator mapping (a thread owns 32 columns of ONE row) touches 32 distinct lines per instruction and cost more
+  // than the product.  Staging rows are padded to 528 bytes so that the 16-byte chunks of consecutive rows fall into
+  // different banks (conflict-free row-owner writes); the copies are issued by threads 0..127, one row each.
+  constexpr uint32_t PITCH = 528;
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW = smem;                   // 64 KB
   uint8_t* sA = smem + 2 * TILE_BYTES;  // 32 KB
-  Tail2* tail = reinterpret_cast<Tail2*>(smem + 3 * TILE_BYTES);
+  uint8_t* sP = smem + 3 * TILE_BYTES;  // 128 x 528 B staging of the output rows
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 3 * TILE_BYTES + 128 * PITCH);
   uint64_t& wbar = tail->bar[0];
   uint64_t& mbar = tail->bar[1];
   uint32_t& tmem_slot = tail->tmem_slot;
@@ -448,9 +454,10 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
       const long long g = row0 + m.warp * 8 + i;
       return g < p.N ? g : -1;
     }, pol_keep);
-    {
-      const long long ng = row0 + (long long)gridDim.x * TILE_ROWS + m.row;
-      if (ng < p.N) prefetch_l2(reinterpret_cast<const char*>(p.x + ng * H) + 128 * m.cq);
+    if (m.tid == 0 && tile + gridDim.x < num_tiles) {      // next tile's rows into L2: one bulk prefetch
+      const long long n0 = (tile + gridDim.x) * TILE_ROWS;
+      const long long nr = (p.N - n0) < TILE_ROWS ? (p.N - n0) : TILE_ROWS;
+      bulk_prefetch_l2(p.x + n0 * H, (uint32_t)(nr * 512));
     }
     fence_async_smem();
     fence_before_sync();
@@ -464,9 +471,11 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
       umma_tile(tmem_acc, smem_u32(sA), 128, 0, smem_u32(sW), 256, 0, 0, 256, 8, 0);
       mma_commit(&mbar);
     }
+    if (m.tid < 128) bulk_wait_read0();      // this thread's row copy of the previous tile has left the staging tile
     mbar_wait(&mbar, phase);
     phase ^= 1;
     fence_after_sync();
+    __syncthreads();                         // (publishes the wait above to the threads that write the staging rows)
     const long long grow = row0 + m.row;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -479,22 +488,27 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
           v[4 * j] += bb[j].x; v[4 * j + 1] += bb[j].y; v[4 * j + 2] += bb[j].z; v[4 * j + 3] += bb[j].w;
         }
       }
-      if (grow < p.N) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint4 pk;
-          pk.x = pack_h2(v[8 * j + 0], v[8 * j + 1]);
-          pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
-          pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]);
-          pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
-          st_u4_hint(p.P + grow * 256 + half * 128 + m.c0 + 8 * j, pk, pol_keep);
-        }
+      for (int j = 0; j < 4; ++j) {
+        uint4 pk;
+        pk.x = pack_h2(v[8 * j + 0], v[8 * j + 1]);
+        pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
+        pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]);
+        pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
+        *reinterpret_cast<uint4*>(sP + m.row * PITCH + (half * 128 + m.c0 + 8 * j) * 2) = pk;
       }
     }
+    fence_async_smem();
     fence_before_sync();
     __syncthreads();
+    if (m.tid < 128 && row0 + m.tid < p.N) {
+      bulk_s2g(p.P + (row0 + m.tid) * 256, sP + m.tid * PITCH, 512, pol_keep);
+      bulk_commit();
+    }
+    (void)grow;
   }
   if (!w_ready) mbar_wait(&wbar, 0);
+  if (m.tid < 128) bulk_wait0();
   fence_before_sync();
   __syncthreads();
   if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
@@ -565,7 +579,7 @@ extern "C" int mgn_pack_block(const float* eW1, const float* eW2, const float* e
 
 static constexpr int EDGE_FWD_SMEM = 4 * 32768 + 32768 + 2 * 32768 + TAIL_BYTES;
 static constexpr int NODE_FWD_SMEM = 5 * 32768 + 2 * 32768 + TAIL_BYTES;
-static constexpr int P_FWD_SMEM = 3 * 32768 + TAIL_BYTES;
+static constexpr int P_FWD_SMEM = 3 * 32768 + 128 * 528 + TAIL_BYTES;
 
 // GraphNetBlock edge update + aggregation (layers.py:687-698).  e_in/e_out [E,128] fp32 in
 // the caller's edge order when rowmap (= CSR perm) is given, else already in CSR order.
