@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     mbar_init(&bar_lo, 1);
     mbar_init_fence();
   }
-  if (m.warp == 0) tmem_alloc<256>(&tmem_slot);
+  if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
@@ -74,6 +74,22 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
   const uint32_t tmem_a = tmem_acc + 128;
   const uint32_t taddr_a = tmem_a + m.lane_off + (m.c0 >> 1);
   const uint32_t taddr_park = tmem_acc + 192 + m.lane_off + (m.c0 >> 1);
+  // row sums of the RMSNorm across the four column quarters go through four tensor-memory columns (one per quarter,
+  // lanes = rows) instead of shared memory; the 2 KB this frees hold b2, b3, b4 and scale, so no epilogue waits for a
+  // global load of its bias behind the gathers in the load/store queue
+  const uint32_t taddr_rs = tmem_acc + 256 + m.lane_off;
+  float* svec = tail->red;                     // [4][128]: b2, b3, b4, scale
+  if (m.tid < 128) {
+    svec[m.tid] = __ldg(p.b2 + m.tid);
+    svec[128 + m.tid] = __ldg(p.b3 + m.tid);
+    svec[256 + m.tid] = __ldg(p.b4 + m.tid);
+    svec[384 + m.tid] = __ldg(p.scale + m.tid);
+  }
+  __syncthreads();
+  auto vec32 = [&](int which, float4 (&b)[8]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b[j] = *reinterpret_cast<const float4*>(svec + which * 128 + m.c0 + 4 * j);
+  };
   const uint32_t sW_u32 = smem_u32(sW), sHi_u32 = smem_u32(sHi);
 
   const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
@@ -216,7 +232,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
 #pragma unroll 1
     for (int layer = 1; layer < 3; ++layer) {
       float4 bb[8];
-      load_vec32(layer == 1 ? p.b2 : p.b3, m.c0, bb);
+      vec32(layer == 1 ? 0 : 1, bb);
       mma_wait();
       epi_bias_relu_tmem_q(taddr, taddr_a, bb, m, nullptr, 0);
       acts_ready();
@@ -235,11 +251,11 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     float y[32];
     {
       float4 bb[8];
-      load_vec32(p.b4, m.c0, bb);
+      vec32(2, bb);
       mma_wait();
       tmem_ld32(taddr, y);
       float4 sc[8];
-      load_vec32(p.scale, m.c0, sc);
+      vec32(3, sc);
       tmem_ld_wait();
       float ss = 0.f;
 #pragma unroll
@@ -247,9 +263,18 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
         y[4 * j] += bb[j].x; y[4 * j + 1] += bb[j].y; y[4 * j + 2] += bb[j].z; y[4 * j + 3] += bb[j].w;
         ss += y[4 * j] * y[4 * j] + y[4 * j + 1] * y[4 * j + 1] + y[4 * j + 2] * y[4 * j + 2] + y[4 * j + 3] * y[4 * j + 3];
       }
-      fence_before_sync();        // the accumulator is read: the barriers below order this before the next product 1
-      cp_async_wait_all();        // (the barriers inside row_sum4 make every thread's staged P_j rows visible)
-      ss = row_sum4(ss, tail->red, m);
+      cp_async_wait_all();        // (the barrier below makes every thread's staged P_j rows visible)
+      tmem_st1(taddr_rs + m.cq, __float_as_uint(ss));
+      tmem_st_wait();
+      fence_before_sync();        // the accumulator is read: the barrier orders this before the next product 1
+      __syncthreads();
+      fence_after_sync();
+      {
+        float q4[4];
+        tmem_ld4(taddr_rs, q4);
+        tmem_ld_wait();
+        ss = (q4[0] + q4[1]) + (q4[2] + q4[3]);
+      }
       fetch_pj();                 // next tile's P_j chunk of this thread's row; the same bytes then take the new image
       const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
 #pragma unroll
@@ -336,7 +361,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
 
   fence_before_sync();
   __syncthreads();
-  if (m.warp == 0) tmem_dealloc<256>(tmem_slot);
+  if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
 static constexpr int EDGE_HL_SMEM = 7 * 32768 + TAIL_BYTES;
