@@ -63,6 +63,59 @@ def build_mlp(in_size: int, hidden_size: int, out_size: int, nb_of_layers: int =
     return module
 
 
+class Normalizer(nn.Module):
+    """Running-statistics feature normaliser of the reference (layers.py:265-393): same constructor arguments, buffers
+    (`_acc_count`, `_num_accumulations`, `_acc_sum`, `_acc_sum_squared`: the state-dict keys of a reference
+    checkpoint), `forward(batched_data, accumulate=True)`, `inverse` and `get_variable`.
+
+    The reference decides `_num_accumulations < _max_accumulations` on the host, i.e. one device -> host read per call
+    (three per training step through the Simulator), which also makes the step impossible to capture in a CUDA graph.
+    Here the test stays on the device: the batch statistics are multiplied by the 0 / 1 outcome before they are added,
+    so the accumulation is a fixed sequence of device operations with the same result."""
+
+    def __init__(self, size: int, max_accumulations: int = 10 ** 5, std_epsilon: float = 1e-8,
+                 name: str = "Normalizer", device="cuda"):
+        super().__init__()
+        self.name = name
+        self.device = device
+        self._max_accumulations = max_accumulations
+        self._std_epsilon = torch.tensor(std_epsilon, dtype=torch.float32, requires_grad=False, device=device)
+        self.register_buffer("_acc_count", torch.tensor(0.0, device=device))
+        self.register_buffer("_num_accumulations", torch.tensor(0.0, device=device))
+        self.register_buffer("_acc_sum", torch.zeros((1, size), dtype=torch.float32, device=device))
+        self.register_buffer("_acc_sum_squared", torch.zeros((1, size), dtype=torch.float32, device=device))
+
+    def forward(self, batched_data: torch.Tensor, accumulate: bool = True) -> torch.Tensor:
+        if accumulate:
+            self._accumulate(batched_data.detach())
+        return (batched_data - self._mean()) / self._std_with_epsilon()
+
+    def inverse(self, normalized_batch_data: torch.Tensor) -> torch.Tensor:
+        return normalized_batch_data * self._std_with_epsilon() + self._mean()
+
+    @torch.no_grad()
+    def _accumulate(self, batched_data: torch.Tensor):
+        # gate = 1 while fewer than max_accumulations batches were seen (layers.py:329-332), else 0: no host read
+        gate = (self._num_accumulations < self._max_accumulations).to(torch.float32)
+        self._acc_sum += gate * torch.sum(batched_data, dim=0, keepdim=True)
+        self._acc_sum_squared += gate * torch.sum(batched_data ** 2, dim=0, keepdim=True)
+        self._acc_count += gate * batched_data.shape[0]
+        self._num_accumulations += gate
+
+    def _mean(self) -> torch.Tensor:
+        return self._acc_sum / torch.clamp(self._acc_count, min=1.0)
+
+    def _std_with_epsilon(self) -> torch.Tensor:
+        variance = self._acc_sum_squared / torch.clamp(self._acc_count, min=1.0) - self._mean() ** 2
+        std = torch.sqrt(torch.clamp(variance, min=0.0))
+        return torch.max(std, self._std_epsilon.to(std.device))
+
+    def get_variable(self):
+        return {"_max_accumulations": self._max_accumulations, "_std_epsilon": self._std_epsilon,
+                "_acc_count": self._acc_count, "_num_accumulations": self._num_accumulations,
+                "_acc_sum": self._acc_sum, "_acc_sum_squared": self._acc_sum_squared, "name": self.name}
+
+
 def block_param_list(block: "GraphNetBlock"):
     """The 18 parameters of a block in ops.GRAD_LAYOUT (= state-dict) order."""
     eb, nb = block.edge_block, block.node_block
