@@ -82,6 +82,16 @@ def csr_for(edge_index: torch.Tensor, num_nodes: int) -> G.CSRGraph:
     return csr
 
 
+def register_csr(edge_index: torch.Tensor, num_nodes: int, csr: G.CSRGraph) -> None:
+    """Hands `csr_for` a CSR that was assembled elsewhere for this tensor (batch.collate: the concatenation of the
+    samples' cached CSRs), so the sort is not launched for it."""
+    if csr.num_nodes != int(num_nodes) or csr.num_edges != int(edge_index.shape[1]):
+        raise ValueError("register_csr: the CSR does not match edge_index / num_nodes")
+    if len(_csr_cache) > 16:
+        _csr_cache.clear()
+    _csr_cache[id(edge_index)] = (weakref.ref(edge_index), edge_index._version, int(num_nodes), csr)
+
+
 def _check_inputs(x, e, params, num_steps):
     L.require_device(x)
     if x.dtype != torch.float32 or e.dtype != torch.float32:
