@@ -1,0 +1,329 @@
+"""Trajectory datasets: the reference's on-disk layout -- one group per trajectory, one flat array
+per feature, a `meta.json` that gives each feature's dtype, `[frames, -1, width]` shape and static / dynamic kind
+(graphphysics/utils/hierarchical.py:11-154, dataset/h5_dataset.py:15-119, dataset/dataset.py:66-85) -- read into graphs
+with the reference's frame semantics, and kept RESIDENT on the device.
+
+What the reference does per sample (`H5Dataset.__getitem__`, h5_dataset.py:66-114): read EVERY feature of the whole
+trajectory from the file, cast and reshape it, cut one frame out on the host, build the node-feature matrix with numpy,
+copy it to the device, then run FaceToEdge / edge features / K-hop there.  For a 600-frame trajectory that is 600x the
+bytes a sample needs, per sample, on the host.
+
+Here a trajectory is decoded once: its per-frame node features and targets are assembled into `[T, N, F]` device tensors
+(a 600 x 1,923-node cylinder trajectory is 23 MB of the 180 GB), its topology goes through the device graph set-up once
+(`graph.face_to_edge` -> `edge_index`, `graph.edge_features`, the receiver-sorted CSR via `processor.csr_for`), and frame
+`t` of the dataset is a pair of views `x[t]`, `y[t]` plus the shared `edge_index` tensor object -- no host work, no
+host -> device copy and no sort per sample; `batch.collate(samples, csrs=...)` then assembles a batch's CSR from the
+cached ones.  A least-recently-used budget (bytes) bounds what stays resident.
+
+Layers, bottom up:
+  * `traj_as_meshes`, `frame_as_mesh`, `meshdata_to_graph`, `frame_as_graph`: the reference's host functions, same
+    results (pinned by tests/golden/ref_dataset.npz, which the reference's own code wrote), numpy / CPU torch only;
+  * `open_container(path)`: trajectory groups from a `.npz` (keys `"<trajectory>/<feature>"`) or, when `h5py` is
+    importable, an `.h5` file.  h5py is not in this image: asking for an `.h5` raises ImportError, nothing falls back;
+  * `ResidentTrajectory`, `TrajectoryDataset`: the device-resident form and the `__len__` / `get_traj_frame` /
+    `__getitem__` surface of the reference's `BaseDataset` (device kernels: needs the B200 library).
+"""
+from __future__ import annotations
+
+import json
+from collections import OrderedDict
+from typing import Any, Dict, Mapping, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .models.processors import Graph
+
+_TOPOLOGY_KEYS = ("mesh_pos", "cells", "node_type")
+
+
+# ---------------------------------------------------------------------------------------------------- host functions
+def load_meta(meta_path: str) -> Dict[str, Any]:
+    with open(meta_path, "r") as fp:
+        return json.load(fp)
+
+
+def traj_as_meshes(group: Mapping[str, Any], meta: Dict[str, Any]) -> Dict[str, np.ndarray]:
+    """`get_traj_as_meshes` (hierarchical.py:38-64): every feature of `meta["features"]`, cast to its dtype and
+    reshaped to its `[frames, -1, width]` shape, in meta order."""
+    meshes = {}
+    for key, field in meta["features"].items():
+        data = np.asarray(group[key][()]).astype(field["dtype"])
+        meshes[key] = data.reshape(field["shape"])
+    return meshes
+
+
+def frame_as_mesh(traj: Mapping[str, np.ndarray], frame: int, meta: Dict[str, Any],
+                  frame_target: Optional[int] = None):
+    """`get_frame_as_mesh` (hierarchical.py:67-123): (mesh_pos, cells, point_data, target_point_data).  Point data =
+    every feature but the topology keys at `frame`, then `node_type` of frame 0 LAST (that fixes the column order of
+    x); targets = `meta["target_features"]` if given, else every dynamic feature, at `frame_target`."""
+    target_point_data = None
+    if frame_target is not None:
+        names = meta.get("target_features")
+        if names is None:
+            names = [k for k, f in meta["features"].items() if f["type"] == "dynamic"]
+        target_point_data = {k: traj[k][frame_target] for k in names}
+    point_data = {k: traj[k][frame] for k in traj.keys() if k not in _TOPOLOGY_KEYS}
+    point_data["node_type"] = traj["node_type"][0]
+    mesh_pos = traj["mesh_pos"][frame] if traj["mesh_pos"].ndim > 1 else traj["mesh_pos"]
+    cells = traj["cells"][frame] if traj["cells"].ndim > 1 else traj["cells"]
+    return mesh_pos, cells, point_data, target_point_data
+
+
+def _stack_features(arrays, extra=None) -> torch.Tensor:
+    """Columns of a node-feature matrix (torch_graph.py:140-165): side by side if any array is 2-D, else each 1-D
+    array is one column; computed in numpy's promoted dtype and rounded to fp32 once, as the reference does."""
+    arrays = list(arrays)
+    if any(a.ndim > 1 for a in arrays):
+        cols = arrays + ([extra.reshape((-1, 1))] if extra is not None else [])
+        mat = np.hstack(cols)
+    else:
+        mat = np.vstack(arrays + ([extra] if extra is not None else [])).T
+    return torch.tensor(mat, dtype=torch.float32)
+
+
+def faces_of_cells(cells: torch.Tensor) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """[C, 3] triangles or [C, 4] tetrahedra -> (face [3, F], tetra [4, C] or None); a tetrahedron gives its four
+    triangles (v0v1v2, v1v2v3, v2v3v0, v3v0v1), grouped by kind (torch_graph.py:170-186)."""
+    c = cells.t()
+    if c.shape[0] == 4:
+        face = torch.cat([c[0:3], c[1:4], torch.stack([c[2], c[3], c[0]]), torch.stack([c[3], c[0], c[1]])], dim=1)
+        return face, c
+    if c.shape[0] == 3:
+        return c, None
+    raise ValueError(f"cells must be triangles or tetrahedra, got {tuple(cells.shape)}")
+
+
+def meshdata_to_graph(points: np.ndarray, cells: np.ndarray, point_data: Optional[Mapping[str, np.ndarray]],
+                      time=1, target: Optional[Mapping[str, np.ndarray]] = None,
+                      return_only_node_features: bool = False, id: Optional[str] = None):
+    """`meshdata_to_graph` (torch_graph.py:114-193): x = [point data ... | time], y = target columns, pos, face, tetra."""
+    if point_data is not None:
+        x = _stack_features(point_data.values(), np.full((len(points),), time))
+    else:
+        x = torch.zeros((len(points), 1), dtype=torch.float32)
+    if return_only_node_features:
+        return x
+    y = _stack_features(target.values()) if target is not None else None
+    face, tetra = faces_of_cells(torch.as_tensor(np.asarray(cells)))
+    return Graph(x=x, face=face, tetra=tetra, y=y, pos=torch.tensor(np.asarray(points), dtype=torch.float32), id=id)
+
+
+def frame_as_graph(traj: Mapping[str, np.ndarray], frame: int, meta: Dict[str, Any],
+                   frame_target: Optional[int] = None):
+    """`get_frame_as_graph` (hierarchical.py:126-154): time = frame * meta.get("dt", 1)."""
+    points, cells, point_data, target = frame_as_mesh(traj, frame, meta, frame_target)
+    return meshdata_to_graph(points=points, cells=cells, point_data=point_data, time=frame * meta.get("dt", 1),
+                             target=target)
+
+
+# ------------------------------------------------------------------------------------------------------- containers
+class NpzContainer:
+    """Trajectory groups in one `.npz`: arrays named `"<trajectory>/<feature>"` (what `save_npz_container` writes).
+    `keys()` keeps the file's order, like `h5py.File.keys()` (get_h5_dataset, hierarchical.py:11-35)."""
+
+    def __init__(self, path: str):
+        self._z = np.load(path)
+        self._index: "OrderedDict[str, Dict[str, str]]" = OrderedDict()
+        for name in self._z.files:
+            traj, _, feat = name.partition("/")
+            if not feat:
+                raise ValueError(f"{path}: array `{name}` is not `<trajectory>/<feature>`")
+            self._index.setdefault(traj, {})[feat] = name
+
+    def keys(self):
+        return list(self._index.keys())
+
+    def __getitem__(self, traj: str) -> Dict[str, np.ndarray]:
+        return {feat: self._z[name] for feat, name in self._index[traj].items()}
+
+    def close(self):
+        self._z.close()
+
+
+def save_npz_container(path: str, trajectories: Mapping[str, Mapping[str, np.ndarray]]) -> None:
+    np.savez(path, **{f"{t}/{k}": np.asarray(v) for t, g in trajectories.items() for k, v in g.items()})
+
+
+def open_container(path: str):
+    """`.npz` -> NpzContainer; `.h5` / `.hdf5` -> `h5py.File(path, "r")` (ImportError if h5py is not installed)."""
+    if path.endswith(".npz"):
+        return NpzContainer(path)
+    if path.endswith((".h5", ".hdf5")):
+        try:
+            import h5py
+        except ImportError as exc:
+            raise ImportError("graph_physics_b200.dataset: reading .h5 trajectories needs h5py, which is not installed "
+                              "in this environment; convert the file to the .npz container "
+                              "(save_npz_container) or install h5py") from exc
+        return h5py.File(path, "r")
+    raise ValueError(f"unknown trajectory container: {path}")
+
+
+# ------------------------------------------------------------------------------------------------- resident on device
+def trajectory_tensors(traj: Mapping[str, np.ndarray], meta: Dict[str, Any]):
+    """All frames of a decoded trajectory at once: x [T, N, F] and y [T, N, D] as `frame_as_graph` builds them per
+    frame (y[t] = the targets AT frame t: sample (t, t+1) reads y[t + 1]), pos [T or 1, N, dim], cells [T or 1, C, k].
+    Host tensors; `ResidentTrajectory` moves them."""
+    T = int(meta["trajectory_length"])
+    dt = meta.get("dt", 1)
+    names = meta.get("target_features")
+    if names is None:
+        names = [k for k, f in meta["features"].items() if f["type"] == "dynamic"]
+    feats = [k for k in traj.keys() if k not in _TOPOLOGY_KEYS]
+    n = traj["node_type"][0].shape[0]
+
+    def per_frame(a: np.ndarray) -> np.ndarray:          # [T, N, w] whatever the stored frame count
+        if a.shape[0] not in (1, T):
+            raise ValueError(f"a feature has {a.shape[0]} frames, the trajectory {T}")
+        return np.broadcast_to(a, (T,) + a.shape[1:])
+
+    cols = [per_frame(traj[k]) for k in feats]
+    cols.append(np.broadcast_to(traj["node_type"][0][None], (T, n) + traj["node_type"].shape[2:]))
+    time = (np.arange(T) * dt).reshape(T, 1, 1)
+    cols.append(np.broadcast_to(time, (T, n, 1)))
+    x = torch.tensor(np.concatenate(cols, axis=2), dtype=torch.float32)
+    y = torch.tensor(np.concatenate([per_frame(traj[k]) for k in names], axis=2), dtype=torch.float32)
+    pos = torch.tensor(traj["mesh_pos"], dtype=torch.float32)
+    cells = torch.as_tensor(traj["cells"])
+    return x, y, pos, cells
+
+
+class ResidentTrajectory:
+    """One trajectory on the device: `x`, `y` ([T, N, .]), `pos`, and the topology run through the device set-up once.
+    `moving_mesh` = positions or cells differ between frames; then edge_index / edge features are built per frame on
+    demand (and cached), otherwise once."""
+
+    def __init__(self, traj: Mapping[str, np.ndarray], meta: Dict[str, Any], device, add_edge_features: bool = True,
+                 khop: int = 1):
+        from . import _lib as L
+        x, y, pos, cells = trajectory_tensors(traj, meta)
+        pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
+        self.x = pin(x).to(device, non_blocking=True)
+        self.y = pin(y).to(device, non_blocking=True)
+        self.pos = pos.to(device)
+        self.cells = cells.to(device)
+        L.require_device(self.x)
+        self.add_edge_features = add_edge_features
+        self.khop = int(khop)
+        self.num_frames, self.num_nodes = int(x.shape[0]), int(x.shape[1])
+        same_cells = cells.shape[0] == 1 or bool((cells == cells[:1]).all())
+        same_pos = pos.shape[0] == 1 or bool((pos == pos[:1]).all())
+        self.moving_mesh = not (same_cells and same_pos)
+        self._same_cells = same_cells
+        self._topo: Dict[int, Tuple[torch.Tensor, Optional[torch.Tensor], torch.Tensor, Optional[torch.Tensor]]] = {}
+        self.nbytes = sum(t.numel() * t.element_size() for t in (self.x, self.y, self.pos, self.cells))
+
+    def topology(self, frame: int):
+        """(edge_index, edge_attr or None, face, tetra) of `frame`; one entry serves every frame of a fixed mesh.  The
+        SAME `edge_index` tensor object comes back every time, so `processor.csr_for` hits its cache."""
+        from . import graph as G
+        key = frame if self.moving_mesh else 0
+        hit = self._topo.get(key)
+        if hit is None:
+            ci = key if self.cells.shape[0] > 1 else 0
+            pi = key if self.pos.shape[0] > 1 else 0
+            cells_key = 0 if self._same_cells else ci
+            face, tetra = faces_of_cells(self.cells[ci])
+            reuse = self._topo.get(("ei", cells_key))
+            if reuse is None:
+                ei = G.face_to_edge(face.contiguous(), self.num_nodes)
+                if self.khop > 1:
+                    ei = G.compute_k_hop_edge_index(ei, self.khop, self.num_nodes)
+                self._topo[("ei", cells_key)] = ei
+            else:
+                ei = reuse
+            ea = G.edge_features(self.pos[pi].contiguous(), ei) if self.add_edge_features else None
+            hit = (ei, ea, face, tetra)
+            self._topo[key] = hit
+            self.nbytes += sum(t.numel() * t.element_size() for t in (ei, ea) if t is not None)
+        return hit
+
+    def sample(self, frame: int, frame_target: Optional[int], use_previous_data: bool = False):
+        """The graph `H5Dataset.__getitem__` hands on after its preprocessing (x, y, pos, face, tetra, edge_index,
+        edge_attr; `previous_data` when asked): views of the resident tensors."""
+        if not 0 <= frame < self.num_frames or (frame_target is not None and not 0 <= frame_target < self.num_frames):
+            raise IndexError(f"frame {frame} / target {frame_target} outside a {self.num_frames}-frame trajectory")
+        ei, ea, face, tetra = self.topology(frame)
+        g = Graph(x=self.x[frame], y=None if frame_target is None else self.y[frame_target],
+                  pos=self.pos[frame if self.pos.shape[0] > 1 else 0], face=face, tetra=tetra, edge_index=ei,
+                  edge_attr=ea)
+        if use_previous_data:
+            g.previous_data = self.x[frame - 1]
+        return g
+
+
+class TrajectoryDataset:
+    """`H5Dataset` surface (h5_dataset.py:15-119, dataset.py:19-85) over resident trajectories:
+
+        ds = TrajectoryDataset("train.npz", "meta.json", device="cuda")
+        len(ds) == size_dataset * (trajectory_length - 1);   ds[i] -> Graph of (trajectory, frame), target = frame + 1
+
+    `get_traj_frame` is the reference's index arithmetic, including its `use_previous_data` shift.  `graph.traj_index`
+    is set as in the reference; `graph.csr` is the trajectory's cached receiver-sorted CSR (for `batch.collate`).
+    Noise, world edges, random edges and masking are the callables of graph.py applied by the caller, as the
+    reference's `preprocessing` callable is."""
+
+    def __init__(self, container_path: str, meta_path: str, device="cuda", preprocessing=None, khop: int = 1,
+                 add_edge_features: bool = True, use_previous_data: bool = False, switch_to_val: bool = False,
+                 resident_bytes: int = 64 << 30):
+        if switch_to_val:
+            container_path = container_path.replace("train", "test")
+        self.meta = load_meta(meta_path)
+        self.trajectory_length = int(self.meta["trajectory_length"])
+        self.dt = self.meta.get("dt", 1) or 1
+        self.container = open_container(container_path)
+        self.datasets_index = list(self.container.keys())
+        self.device = torch.device(device)
+        self.preprocessing = preprocessing
+        self.khop = khop
+        self.add_edge_features = add_edge_features
+        self.use_previous_data = use_previous_data
+        self.resident_bytes = int(resident_bytes)
+        self._resident: "OrderedDict[int, ResidentTrajectory]" = OrderedDict()
+
+    @property
+    def size_dataset(self) -> int:
+        return len(self.datasets_index)
+
+    def get_traj_frame(self, index: int) -> Tuple[int, int]:
+        traj = index // (self.trajectory_length - 1)
+        frame = index % (self.trajectory_length - 1) + int(self.use_previous_data)
+        return traj, frame
+
+    def __len__(self) -> int:
+        return self.size_dataset * (self.trajectory_length - 1)
+
+    def trajectory(self, traj_index: int) -> ResidentTrajectory:
+        hit = self._resident.get(traj_index)
+        if hit is not None:
+            self._resident.move_to_end(traj_index)
+            return hit
+        group = self.container[self.datasets_index[traj_index]]
+        rt = ResidentTrajectory(traj_as_meshes(group, self.meta), self.meta, self.device,
+                                add_edge_features=self.add_edge_features, khop=self.khop)
+        self._resident[traj_index] = rt
+        while len(self._resident) > 1 and sum(t.nbytes for t in self._resident.values()) > self.resident_bytes:
+            self._resident.popitem(last=False)
+        return rt
+
+    def __getitem__(self, index: int):
+        if not 0 <= index < len(self):
+            raise IndexError(index)
+        traj_index, frame = self.get_traj_frame(index)
+        rt = self.trajectory(traj_index)
+        g = rt.sample(frame, frame + 1, use_previous_data=self.use_previous_data)
+        if self.preprocessing is not None:
+            g = self.preprocessing(g)
+        if hasattr(g, "previous_data"):
+            del g.previous_data
+        g.traj_index = traj_index
+        from . import processor as _proc
+        g.csr = _proc.csr_for(g.edge_index, rt.num_nodes)
+        return g
+
+    def close(self):
+        if getattr(self, "container", None) is not None:
+            self.container.close()
+            self.container = None

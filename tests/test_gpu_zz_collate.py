@@ -31,3 +31,37 @@ def test_concat_csr_equals_device_build(golden_dir):
         assert torch.equal(getattr(b.csr, name), getattr(want, name)), name
     assert b.csr.identity == want.identity
     assert proc.csr_for(b.edge_index, b.num_nodes) is b.csr
+
+
+def test_resident_trajectory_dataset_serves_the_reference_frames(golden_dir, tmp_path):
+    """`TrajectoryDataset` (device-resident trajectories) against the host functions that tests/test_cpu_dataset.py pins
+    to the reference: sample i is frame (i mod T-1) with target frame + 1; one edge_index object and one CSR per
+    trajectory; a batch of samples collates without a sort."""
+    import json
+    from graph_physics_b200 import batch as B, dataset as D, graph as G
+    z = np.load(os.path.join(golden_dir, "ref_dataset.npz"))
+    meta = json.loads(bytes(z["cyl2d.meta"]).decode())
+    group = {k[len("cyl2d.raw."):]: z[k] for k in z.files if k.startswith("cyl2d.raw.")}
+    path = os.path.join(tmp_path, "train.npz")
+    D.save_npz_container(path, {"t0": group, "t1": group})
+    meta_path = os.path.join(tmp_path, "meta.json")
+    with open(meta_path, "w") as fp:
+        json.dump(meta, fp)
+    ds = D.TrajectoryDataset(path, meta_path, device="cuda")
+    traj = D.traj_as_meshes(group, meta)
+    T = meta["trajectory_length"]
+    assert len(ds) == 2 * (T - 1)
+    samples = [ds[i] for i in (0, 3, T - 1 + 2)]
+    for s, frame in zip(samples, (0, 3, 2)):
+        want = D.frame_as_graph(traj, frame, meta, frame_target=frame + 1)
+        assert torch.equal(s.x.cpu(), want.x) and torch.equal(s.y.cpu(), want.y) and torch.equal(s.pos.cpu(), want.pos)
+        ei = G.face_to_edge(want.face.cuda().contiguous(), want.x.shape[0])
+        assert torch.equal(s.edge_index, ei)
+        assert torch.equal(s.edge_attr, G.edge_features(want.pos.cuda(), ei))
+        assert s.csr.num_edges == ei.shape[1] and not hasattr(s, "previous_data")
+    assert samples[0].edge_index is samples[1].edge_index and samples[0].csr is samples[1].csr     # same trajectory
+    assert samples[0].traj_index == 0 and samples[2].traj_index == 1
+    b = B.collate(samples, csrs=[s.csr for s in samples])
+    want = G.build_csr(b.edge_index, b.num_nodes)
+    assert torch.equal(b.csr.perm, want.perm) and torch.equal(b.csr.rowptr, want.rowptr)
+    ds.close()
