@@ -1,8 +1,8 @@
 """GPU: the CSR of a collated batch assembled from the samples' device-built CSRs (`batch.concat_csr`) is bit-identical
 to `mgn_build_csr` run on the batch's own `edge_index`, and the processor picks the registered CSR up.
 
-(Written after the round's GPU budget was spent: the logic is device independent and covered by tests/test_cpu_batch.py
-against the oracle; this file sorts last so that it cannot hide the results of the kernel tests.)"""
+(The logic is device independent and covered by tests/test_cpu_batch.py against the oracle; this file checks it on the
+device-built structures.)"""
 import os
 
 import numpy as np
