@@ -210,6 +210,10 @@ int mgn_selftest_umma(const void* a, const void* b, float* d, int a_cols, int b_
 /* probe of shapes the fused kernels do not use yet: UMMA M = 64 (m), A operand from tensor memory (a_tmem 1/2 =
  * packing of two fp16 per 32-bit column); d [128 TMEM lanes][n] (tools/umma_probe2.py) */
 int mgn_selftest_umma2(const void* a, const void* b, float* d, int n, int ksteps, int m, int a_tmem, void* stream);
+/* probe of the CTA-pair product planned for the round-2 edge kernels: D[256][n] = A[256][16 ksteps] * B[n][..]^T by one
+ * tcgen05.mma.cta_group::2 stream on a cluster of two CTAs, each holding half of B (a_tmem 1 = A operand in tensor
+ * memory).  Not used by any product kernel; run only on request (tests/test_gpu_umma.py, MGN_TEST_PAIR=1) */
+int mgn_selftest_umma_pair(const void* a, const void* b, float* d, int n, int ksteps, int a_tmem, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 """GPU: pins the tcgen05 shared-memory descriptor conventions of csrc/tc05.cuh
 (one 128-row tile product per case) against an fp64 CPU product."""
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -90,3 +91,23 @@ def test_m64_accumulator_lanes():
     assert float((d[lanes] - want[:64]).abs().max() / want.abs().max()) < 2e-3
     rest = [i for i in range(128) if i not in lanes]
     assert float(d[rest].abs().max()) == 0.0
+
+
+@pytest.mark.skipif(os.environ.get("MGN_TEST_PAIR", "0") != "1",
+                    reason="CTA-pair probe (round-2 preparation): not yet confirmed on a B200; run with MGN_TEST_PAIR=1")
+@pytest.mark.parametrize("n,ksteps,a_tmem", [(128, 8, 0), (128, 8, 1), (256, 8, 0), (64, 4, 1)])
+def test_cta_pair_product(n, ksteps, a_tmem):
+    """tcgen05.mma.cta_group::2 on a cluster of two CTAs (selftest.cu: umma_selftest_pair_kernel): M = 256, every CTA
+    holds its 128 rows of A and HALF of B's rows -- the weight split DESIGN.md plans for the edge kernels."""
+    from graph_physics_b200 import _lib as L
+    L.require_device()
+    g = torch.Generator().manual_seed(n + ksteps + a_tmem)
+    a = (torch.randn(256, 128, generator=g) * 0.5).half()
+    b = (torch.randn(n, 128, generator=g) * 0.5).half()
+    d = torch.full((256, n), float("nan"), device="cuda")
+    ad, bd = a.cuda(), b.cuda()
+    L.check(L.lib().mgn_selftest_umma_pair(L.p(ad), L.p(bd), L.p(d), n, ksteps, a_tmem, L.stream()))
+    torch.cuda.synchronize()
+    K = 16 * ksteps
+    want = a.double()[:, :K] @ b.double()[:, :K].t()
+    assert float((d.cpu().double() - want).abs().max() / want.abs().max()) < 2e-3
