@@ -97,6 +97,22 @@ class Simulator(nn.Module):
                                       "MeshGraphNet processor path")
         return network_output, target_delta_normalized, self._build_outputs(inputs, network_output)
 
+    @torch.no_grad()
+    def predict(self, inputs) -> torch.Tensor:
+        """The `outputs` of an evaluation-mode `forward` for a graph that has no target (`inputs.y` is not read and no
+        normaliser accumulates): what a rollout step needs -- `rollout.Rollout(predict_fn=simulator.predict, ...)`
+        replays it from one CUDA graph per time step."""
+        if getattr(self.model, "K", 0) != 0:
+            raise NotImplementedError("graph_physics_b200: mixture-density sampling (model.K > 0) is not part of the "
+                                      "MeshGraphNet processor path")
+        node_features = self._build_node_features(inputs, self._get_one_hot_type(inputs))
+        edge_attr = inputs.edge_attr
+        if self._edge_normalizer is not None:
+            edge_attr = self._edge_normalizer(edge_attr, False)
+        graph = Graph(x=self._node_normalizer(node_features, False), pos=getattr(inputs, "pos", None),
+                      edge_attr=edge_attr, edge_index=inputs.edge_index)
+        return self._build_outputs(inputs, self.model(graph))
+
     def freeze_all(self) -> None:
         for param in self.model.parameters():
             param.requires_grad = False

@@ -195,3 +195,21 @@ def test_checkpoint_round_trip_keeps_reference_layout(tmp_path):
     assert all(torch.equal(u, v) for u, v in zip(a, b))
     sim.freeze_all()
     assert not any(p.requires_grad for p in sim.model.parameters())
+
+
+def test_predict_equals_the_evaluation_outputs_without_a_target():
+    sim = _simulator()
+    sim.train()
+    for c in range(2):
+        x, y, ea, ei, pos = G["inputs"](c)
+        sim(Graph(x=x, y=y, edge_attr=ea, edge_index=ei, pos=pos))
+    sim.eval()
+    x, y, ea, ei, pos = G["inputs"](2)
+    before = {k: v.clone() for k, v in sim.state_dict().items()}
+    _, _, outputs = sim(Graph(x=x, y=y, edge_attr=ea, edge_index=ei, pos=pos))
+    got = sim.predict(Graph(x=x, edge_attr=ea, edge_index=ei, pos=pos))          # no y
+    assert torch.equal(got, outputs)
+    sim.train()
+    assert torch.equal(sim.predict(Graph(x=x, edge_attr=ea, edge_index=ei)), outputs)   # never accumulates
+    for k, v in sim.state_dict().items():
+        assert torch.equal(v, before[k]), k
