@@ -118,6 +118,13 @@ def frame_as_graph(traj: Mapping[str, np.ndarray], frame: int, meta: Dict[str, A
                              target=target)
 
 
+def masked_indexes(num_nodes: int, masking_ratio: float = 0.15, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """`get_masked_indexes` (utils/torch_graph.py:285-302): the first int((1 - ratio) n) entries of a host
+    `randperm(n)` -- the indices of the nodes that are KEPT."""
+    keep = int((1 - masking_ratio) * num_nodes)
+    return torch.randperm(num_nodes, generator=generator)[:keep]
+
+
 # ------------------------------------------------------------------------------------------------------- containers
 class NpzContainer:
     """Trajectory groups in one `.npz`: arrays named `"<trajectory>/<feature>"` (what `save_npz_container` writes).
@@ -262,12 +269,13 @@ class TrajectoryDataset:
 
     `get_traj_frame` is the reference's index arithmetic, including its `use_previous_data` shift.  `graph.traj_index`
     is set as in the reference; `graph.csr` is the trajectory's cached receiver-sorted CSR (for `batch.collate`).
-    Noise, world edges, random edges and masking are the callables of graph.py applied by the caller, as the
-    reference's `preprocessing` callable is."""
+    `preprocessing` is the callable of `preprocessing.build_preprocessing` (noise, world edges, ...), applied as the
+    reference applies its own; `new_edges_ratio` and `masking_ratio` act as in `BaseDataset` (dataset.py:104-137, 190-
+    200: with a masking ratio an item is the pair (graph, kept node indices))."""
 
     def __init__(self, container_path: str, meta_path: str, device="cuda", preprocessing=None, khop: int = 1,
                  add_edge_features: bool = True, use_previous_data: bool = False, switch_to_val: bool = False,
-                 resident_bytes: int = 64 << 30):
+                 resident_bytes: int = 64 << 30, masking_ratio: Optional[float] = None, new_edges_ratio: float = 0.0):
         if switch_to_val:
             container_path = container_path.replace("train", "test")
         self.meta = load_meta(meta_path)
@@ -281,6 +289,8 @@ class TrajectoryDataset:
         self.add_edge_features = add_edge_features
         self.use_previous_data = use_previous_data
         self.resident_bytes = int(resident_bytes)
+        self.masking_ratio = masking_ratio
+        self.new_edges_ratio = new_edges_ratio
         self._resident: "OrderedDict[int, ResidentTrajectory]" = OrderedDict()
 
     @property
@@ -316,11 +326,24 @@ class TrajectoryDataset:
         g = rt.sample(frame, frame + 1, use_previous_data=self.use_previous_data)
         if self.preprocessing is not None:
             g = self.preprocessing(g)
+        if 0.0 < self.new_edges_ratio <= 1.0:
+            g = self._add_random_edges(g, rt.num_nodes)
         if hasattr(g, "previous_data"):
             del g.previous_data
         g.traj_index = traj_index
         from . import processor as _proc
         g.csr = _proc.csr_for(g.edge_index, rt.num_nodes)
+        if self.masking_ratio is not None:
+            return g, masked_indexes(rt.num_nodes, self.masking_ratio)
+        return g
+
+    def _add_random_edges(self, g, num_nodes: int):
+        """`BaseDataset._add_random_edges` (dataset.py:104-137): round(E p) // 2 random undirected pairs appended, edge
+        features recomputed on the new edge set (a per-sample edge_index: its CSR is sorted per sample)."""
+        from . import graph as G
+        g.edge_index, _ = G.add_random_edges(g.edge_index, self.new_edges_ratio, num_nodes)
+        if self.add_edge_features:
+            g.edge_attr = G.edge_features(g.pos.contiguous(), g.edge_index)
         return g
 
     def close(self):

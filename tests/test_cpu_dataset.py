@@ -104,3 +104,13 @@ def test_npz_container_and_index_arithmetic(golden_dir, tmp_path):
     with pytest.raises(RuntimeError):
         ds[0]                 # the resident form needs the device library: no CPU path
     ds.close()
+
+
+def test_masked_indexes_match_the_reference_formula():
+    """utils/torch_graph.py:285-302: int((1 - ratio) n) entries of randperm(n) from the global torch generator."""
+    for n, ratio in ((1923, 0.15), (10, 0.5), (7, 0.0), (5, 1.0)):
+        torch.manual_seed(3)
+        want = torch.randperm(n)[: int((1 - ratio) * n)]
+        torch.manual_seed(3)
+        got = D.masked_indexes(n, ratio)
+        assert torch.equal(got, want) and got.unique().numel() == got.numel()
