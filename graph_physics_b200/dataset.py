@@ -18,8 +18,10 @@ cached ones.  A least-recently-used budget (bytes) bounds what stays resident.
 Layers, bottom up:
   * `traj_as_meshes`, `frame_as_mesh`, `meshdata_to_graph`, `frame_as_graph`: the reference's host functions, same
     results (pinned by tests/golden/ref_dataset.npz, which the reference's own code wrote), numpy / CPU torch only;
-  * `open_container(path)`: trajectory groups from a `.npz` (keys `"<trajectory>/<feature>"`) or, when `h5py` is
-    importable, an `.h5` file.  h5py is not in this image: asking for an `.h5` raises ImportError, nothing falls back;
+  * `open_container(path)`: trajectory groups from a `.npz` (keys `"<trajectory>/<feature>"`) or an `.h5` file --
+    through h5py when it is importable, else through `h5lite`, this package's read-only decoder of the subset of the
+    format h5py writes by default (anything else raises `H5Unsupported`); `xdmf_frame_as_graph` = the XDMF dataset's
+    frame semantics over `xdmf.XdmfTimeSeries`;
   * `ResidentTrajectory`, `TrajectoryDataset`: the device-resident form and the `__len__` / `get_traj_frame` /
     `__getitem__` surface of the reference's `BaseDataset` (device kernels: needs the B200 library).
 """
@@ -118,6 +120,54 @@ def frame_as_graph(traj: Mapping[str, np.ndarray], frame: int, meta: Dict[str, A
                              target=target)
 
 
+def xdmf_frame_as_graph(reader, frame: int, meta: Dict[str, Any], target_step: int = 1, previous_step: Optional[int] = None,
+                        mesh_id: Optional[str] = None):
+    """The graph `XDMFDataset.__getitem__` builds from a time-series reader (xdmf_dataset.py:97-165) for given step
+    offsets (the reference draws them at random in [1, random_next] / [1, random_prev]; here they are arguments):
+    point data = the meta features present in the file, in META order, cast to the meta dtype, 1-D arrays as columns;
+    targets = the dynamic ones at `frame + target_step`; x = [point data | time of the frame]; `target_dt` (and
+    `previous_data`, `previous_dt` with `previous_step`) as the reference sets them.  `reader` = xdmf.XdmfTimeSeries or
+    meshio's TimeSeriesReader."""
+    num_steps = reader.num_steps
+    if previous_step is not None and frame - previous_step < 0:
+        previous_step = 1
+    if frame + target_step > num_steps - 1:
+        target_step = 1
+    if frame >= num_steps - 1:
+        raise IndexError(f"Frame index {frame} out of bounds for a trajectory with {num_steps} frames.")
+    points, cells_dict = reader.read_points_cells()
+    if not isinstance(cells_dict, dict):                       # meshio: a list of CellBlock
+        cells_dict = {c.type: c.data for c in cells_dict}
+    time, point_data, _ = reader.read_data(frame)
+    _, target_point_data, _ = reader.read_data(frame + target_step)
+    if "triangle" in cells_dict:
+        cells = cells_dict["triangle"]
+    elif "tetra" in cells_dict:
+        cells = cells_dict["tetra"]
+    else:
+        raise ValueError("Unsupported cell type. Only 'triangle' and 'tetra' cells are supported.")
+    feats = meta["features"]
+
+    def pick(src, dynamic_only: bool):
+        out = {}
+        for k in feats:
+            if k in src and (not dynamic_only or feats[k]["type"] == "dynamic"):
+                v = np.array(src[k]).astype(feats[k]["dtype"])
+                out[k] = v.reshape(-1, 1) if v.ndim == 1 else v
+        return out
+
+    graph = meshdata_to_graph(points=np.asarray(points).astype(np.float32), cells=np.asarray(cells),
+                              point_data=pick(point_data, False), time=time, target=pick(target_point_data, True),
+                              id=mesh_id)
+    dt = meta.get("dt", 1) or 1
+    graph.target_dt = target_step * dt
+    if previous_step is not None:
+        _, previous_data, _ = reader.read_data(frame - previous_step)
+        graph.previous_data = pick(previous_data, True)
+        graph.previous_dt = -previous_step * dt
+    return graph
+
+
 def masked_indexes(num_nodes: int, masking_ratio: float = 0.15, generator: Optional[torch.Generator] = None) -> torch.Tensor:
     """`get_masked_indexes` (utils/torch_graph.py:285-302): the first int((1 - ratio) n) entries of a host
     `randperm(n)` -- the indices of the nodes that are KEPT."""
@@ -154,17 +204,16 @@ def save_npz_container(path: str, trajectories: Mapping[str, Mapping[str, np.nda
 
 
 def open_container(path: str):
-    """`.npz` -> NpzContainer; `.h5` / `.hdf5` -> `h5py.File(path, "r")` (ImportError if h5py is not installed)."""
+    """`.npz` -> NpzContainer; `.h5` / `.hdf5` -> `h5py.File(path, "r")`, or `h5lite.File` where h5py is not installed."""
     if path.endswith(".npz"):
         return NpzContainer(path)
     if path.endswith((".h5", ".hdf5")):
         try:
             import h5py
-        except ImportError as exc:
-            raise ImportError("graph_physics_b200.dataset: reading .h5 trajectories needs h5py, which is not installed "
-                              "in this environment; convert the file to the .npz container "
-                              "(save_npz_container) or install h5py") from exc
-        return h5py.File(path, "r")
+            return h5py.File(path, "r")
+        except ImportError:
+            from . import h5lite                # this package's read-only decoder (files written with default settings)
+            return h5lite.File(path)
     raise ValueError(f"unknown trajectory container: {path}")
 
 
