@@ -32,6 +32,13 @@ def test_h5lite_contiguous_file_matches_the_vtu_route(golden_dir):
         assert np.array_equal(f[f"data{3 + 2 * t}"][()], vel[t, :, 1])
     with pytest.raises(KeyError):
         f["nope"]
+    # a group reached through its object header (symbol-table message) -- the route every nested group takes -- lists
+    # the same links as the root reached through the superblock's cached addresses
+    r = f._r
+    root_header = r.addr(24 + 4 * r.O + r.O)
+    again = f._object(root_header, "/")
+    assert isinstance(again, h5lite.Group) and again.keys() == f.keys()
+    assert np.array_equal(again["data2"][()], f["data2"][()])
     f.close()
 
 
