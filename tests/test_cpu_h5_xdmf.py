@@ -123,3 +123,42 @@ def test_xdmf_inline_data_and_h5lite_errors(tmp_path):
         h5lite.File(newer)
     with pytest.raises(ValueError):
         h5lite.File(bad, "w")
+
+
+def test_xdmf_writer_round_trip(golden_dir, tmp_path):
+    """Writer (binary heavy data) -> reader: the series `_save_trajectory_to_xdmf` would write for a predicted
+    trajectory comes back bit-identical, times included."""
+    import torch
+    from graph_physics_b200.models import Graph
+    from graph_physics_b200.xdmf import XdmfTimeSeriesWriter, write_trajectory
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    vel = np.load(os.path.join(golden_dir, "cylinder_velocity_frames.npz"))["velocity"]
+    pos = torch.as_tensor(z["points"][:, :2])
+    face = torch.as_tensor(z["face"].astype(np.int64))
+    traj = [Graph(x=torch.as_tensor(vel[t]), y=torch.as_tensor(vel[t + 1]), pos=pos, face=face, tetra=None)
+            for t in range(5)]
+    path = write_trajectory(os.path.join(tmp_path, "pred"), "graph_epoch_0", traj, timestep=0.01)
+    assert path.endswith("graph_epoch_0.xdmf") and os.path.exists(path[:-5] + ".bin")
+    with XdmfTimeSeries(path) as r:
+        assert r.num_steps == 5
+        points, cells = r.read_points_cells()
+        assert np.array_equal(points[:, :2], z["points"][:, :2]) and not points[:, 2].any()
+        assert np.array_equal(cells["triangle"], z["cells"])
+        for t in range(5):
+            time, pd, cd = r.read_data(t)
+            assert time == pytest.approx(0.01 * (t + 1)) and cd == {} and list(pd) == ["x0", "x1", "y0", "y1"]
+            assert np.array_equal(pd["x1"], vel[t, :, 1]) and np.array_equal(pd["y0"], vel[t + 1, :, 0])
+    with XdmfTimeSeries(write_trajectory(os.path.join(tmp_path, "pred"), "prev", traj[:2], 0.5, True)) as r:
+        assert r.read_data(0)[0] == 1.0 and r.read_data(1)[0] == 1.5
+    with pytest.raises(ValueError):
+        XdmfTimeSeriesWriter(os.path.join(tmp_path, "x.h5"))
+    with XdmfTimeSeriesWriter(os.path.join(tmp_path, "v.xdmf")) as w:
+        with pytest.raises(ValueError):
+            w.write_data(0.0, point_data={})
+        w.write_points_cells(np.zeros((3, 3), np.float32), [("triangle", np.array([[0, 1, 2]]))])
+        with pytest.raises(ValueError):
+            w.write_data(0.0, point_data={"bad": np.zeros(7)})
+        w.write_data(0.0, point_data={"vec": np.ones((3, 3))}, cell_data={"c": np.array([5], dtype=np.int32)})
+    with XdmfTimeSeries(os.path.join(tmp_path, "v.xdmf")) as r:
+        _, pd, cd = r.read_data(0)
+        assert pd["vec"].shape == (3, 3) and np.array_equal(cd["c"], [5])
