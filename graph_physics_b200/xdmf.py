@@ -188,6 +188,11 @@ class XdmfTimeSeriesWriter:
     def write_data(self, t: float, point_data=None, cell_data=None) -> None:
         if not self._has_mesh:
             raise ValueError("XdmfTimeSeriesWriter: write_points_cells first")
+        for center, data, n in (("node", point_data or {}, self._num_points), ("cell", cell_data or {}, self._num_cells)):
+            for name, a in data.items():        # validate everything before the step is added to the document
+                a = np.asarray(a)
+                if a.ndim not in (1, 2) or a.shape[0] != n:
+                    raise ValueError(f"XdmfTimeSeriesWriter: `{name}` has shape {a.shape} for {n} {center}s")
         grid = ET.SubElement(self._collection, "Grid")
         inc = ET.SubElement(grid, "xi:include")
         inc.set("xpointer", 'xpointer(//Grid[@Name="mesh"]/*[self::Topology or self::Geometry])')
@@ -195,8 +200,6 @@ class XdmfTimeSeriesWriter:
         for center, data, n in (("Node", point_data or {}, self._num_points), ("Cell", cell_data or {}, self._num_cells)):
             for name, a in data.items():
                 a = np.asarray(a)
-                if a.shape[0] != n or a.ndim > 2:
-                    raise ValueError(f"XdmfTimeSeriesWriter: `{name}` has shape {a.shape} for {n} {center.lower()}s")
                 kind = "Scalar" if a.ndim == 1 or a.shape[1] == 1 else "Vector"
                 att = ET.SubElement(grid, "Attribute", Name=name, AttributeType=kind, Center=center)
                 self._item(att, a)
