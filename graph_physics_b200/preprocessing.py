@@ -110,6 +110,59 @@ def add_world_pos_features(graph, world_pos_index_start: int, world_pos_index_en
     return graph
 
 
+def compute_min_distance_to_type(graph, target_type: int, node_types: torch.Tensor) -> torch.Tensor:
+    """preprocessing.py:239-271: for every node the Euclidean distance to the nearest node of `target_type` ([N]).
+    The reference materialises an [N, M, 3] difference tensor; `cdist` without the matmul shortcut computes the same
+    sqrt(sum(diff^2)) in [N, M]."""
+    pos = graph.pos
+    targets = pos[node_types == int(target_type)]
+    return torch.cdist(pos, targets, compute_mode="donot_use_mm_for_euclid_dist").min(dim=1)[0]
+
+
+class Random3DRotate:
+    """preprocessing.py:274-366: one random rotation R (angles uniform in +-180 degrees from Python's `random`, the
+    reference's composition of the three axis rotations) applied as `v @ R` to the positions, to every listed
+    3-column feature range of x and to the first three target columns -- `y` is REPLACED by those three rotated columns,
+    as in the reference.  x is not modified in place (a sample may be a view of a resident trajectory)."""
+
+    def __init__(self, feature_indices=None) -> None:
+        self.feature_indices = feature_indices or []
+        for start_idx, end_idx in self.feature_indices:
+            assert end_idx - start_idx == 3, (
+                f"Each feature range must span exactly 3 features for xyz coordinates. Got range {start_idx}-{end_idx}")
+
+    def _get_random_angles(self):
+        import random
+        return [math.radians(random.uniform(-180, 180)) for _ in range(3)]
+
+    @staticmethod
+    def _build_rotation_matrix(alpha: float, beta: float, gamma: float) -> torch.Tensor:
+        ca, sa, cb, sb, cg, sg = (math.cos(alpha), math.sin(alpha), math.cos(beta), math.sin(beta), math.cos(gamma),
+                                  math.sin(gamma))
+        return torch.tensor([[ca * cb, ca * sb * sg + sa * cg, -ca * sb * cg + sa * sg],
+                             [-sa * cb, -sa * sb * sg + ca * cg, sa * sb * cg + ca * sg],
+                             [sb, -cb * sg, cb * cg]])
+
+    def __call__(self, data):
+        return self.forward(data)
+
+    def forward(self, data):
+        matrix = self._build_rotation_matrix(*self._get_random_angles())
+        if getattr(data, "pos", None) is not None:
+            pos = data.pos.view(-1, 1) if data.pos.dim() == 1 else data.pos
+            assert pos.size(-1) == 3, "Node positions must be 3-dimensional"
+            data.pos = pos @ matrix.to(pos.device, pos.dtype)
+        if getattr(data, "x", None) is not None and self.feature_indices:
+            x = data.x.clone()
+            for start_idx, end_idx in self.feature_indices:
+                x[:, start_idx:end_idx] = x[:, start_idx:end_idx] @ matrix.to(x.device, x.dtype)
+            data.x = x
+        if getattr(data, "y", None) is not None and getattr(data, "x", None) is not None:
+            target = data.y[:, 0:3]
+            data.y = target @ matrix.to(target.device, target.dtype)
+        return data
+
+
 class Compose:
     """T.Compose: applies the transforms in order; `.transforms` is the list (as PyG exposes it)."""
 

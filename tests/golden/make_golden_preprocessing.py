@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Fixture for the feature transforms of the per-sample preprocessing: runs the REFERENCE's own
-`add_noise`, `add_obstacles_next_pos` and `build_preprocessing` (graphphysics/dataset/preprocessing.py:47-89, 177-236,
-364-446) from /root/reference on seeded inputs and writes tests/golden/ref_preprocessing.npz (+ the order of the
+`add_noise`, `add_obstacles_next_pos`, `compute_min_distance_to_type`, `Random3DRotate` and `build_preprocessing`
+(graphphysics/dataset/preprocessing.py:47-89, 177-446) from /root/reference on seeded inputs and writes tests/golden/ref_preprocessing.npz (+ the order of the
 transforms `build_preprocessing` composes, as names).
 
     python tests/golden/make_golden_preprocessing.py
@@ -37,7 +37,8 @@ def _name(t):
 def main():
     Data = _install_stubs()
     sys.path.insert(0, REF)
-    from graphphysics.dataset.preprocessing import add_noise, add_obstacles_next_pos, build_preprocessing
+    from graphphysics.dataset.preprocessing import (Random3DRotate, add_noise, add_obstacles_next_pos,
+                                                    build_preprocessing, compute_min_distance_to_type)
 
     out = {}
     x, y = inputs()
@@ -53,6 +54,17 @@ def main():
     g = add_obstacles_next_pos(Data(x=x.clone(), y=y.clone()), world_pos_index_start=0, world_pos_index_end=3,
                                node_type_index=10)
     out["obstacles"] = g.x.numpy()
+    # extra features of the 3-D (aneurysm) configurations: min distance to a node type, random rigid rotation
+    import random
+    g3 = torch.Generator().manual_seed(8)
+    pos3 = torch.randn(N, 3, generator=g3)
+    types = torch.randint(0, 7, (N,), generator=g3)
+    out["pos3"], out["types3"] = pos3.numpy(), types.numpy()
+    out["min_dist_inflow"] = compute_min_distance_to_type(Data(pos=pos3), 4, types).numpy()
+    random.seed(5)
+    rot = Random3DRotate(feature_indices=[(0, 3), (4, 7)])
+    gr = rot(Data(x=x.clone(), y=y.clone(), pos=pos3.clone()))
+    out["rot_x"], out["rot_y"], out["rot_pos"] = gr.x.numpy(), gr.y.numpy(), gr.pos.numpy()
     orders = {}
     wp = {"world_pos_index_start": 0, "world_pos_index_end": 3, "node_type_index": 10, "radius": 0.05}
     nz = {"noise_index_start": 0, "noise_index_end": 2, "noise_scale": 0.02, "node_type_index": 7}

@@ -74,3 +74,23 @@ def test_build_preprocessing_order(golden_dir):
     ei, ea = torch.zeros((2, 3), dtype=torch.int64), torch.zeros((3, 3))
     g = P.build_preprocessing()(Graph(x=torch.zeros(4, 2), edge_index=ei, edge_attr=ea, face=None, pos=None))
     assert g.edge_index is ei and g.edge_attr is ea
+
+
+def test_min_distance_and_random_rotation(golden_dir):
+    """preprocessing.py:239-366 (the extra features of the 3-D configurations)."""
+    import random
+    z = np.load(os.path.join(golden_dir, "ref_preprocessing.npz"))
+    pos3, types = torch.from_numpy(z["pos3"]), torch.from_numpy(z["types3"])
+    d = P.compute_min_distance_to_type(Graph(pos=pos3), 4, types)
+    np.testing.assert_allclose(d.numpy(), z["min_dist_inflow"], rtol=1e-6, atol=0)
+    assert float(d[types == 4].max()) == 0.0
+    x, y = torch.from_numpy(z["x"]), torch.from_numpy(z["y"])
+    random.seed(5)
+    keep = x.clone()
+    g = P.Random3DRotate(feature_indices=[(0, 3), (4, 7)])(Graph(x=keep, y=y.clone(), pos=pos3.clone()))
+    assert np.array_equal(g.x.numpy(), z["rot_x"]) and np.array_equal(g.y.numpy(), z["rot_y"])
+    assert np.array_equal(g.pos.numpy(), z["rot_pos"]) and torch.equal(keep, x) and g.y.shape[1] == 3
+    # a rotation: lengths are kept
+    assert torch.allclose(g.pos.norm(dim=1), pos3.norm(dim=1), rtol=1e-5)
+    with pytest.raises(AssertionError):
+        P.Random3DRotate(feature_indices=[(0, 2)])
