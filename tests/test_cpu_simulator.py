@@ -213,3 +213,33 @@ def test_predict_equals_the_evaluation_outputs_without_a_target():
     assert torch.equal(sim.predict(Graph(x=x, edge_attr=ea, edge_index=ei)), outputs)   # never accumulates
     for k, v in sim.state_dict().items():
         assert torch.equal(v, before[k]), k
+
+
+def test_training_step_function_matches_the_reference_loss_fixture(golden_dir):
+    """training/lightning_module.py:112-123 as a function: the fixture's L2 losses (reference Simulator + L2Loss on the
+    same three accumulating calls), and the gradient reaches the network."""
+    from graph_physics_b200.training import rollout_rmse, training_step
+    z = np.load(os.path.join(golden_dir, "ref_simulator.npz"))
+
+    class Net(torch.nn.Module):
+        K = 0
+
+        def __init__(self):
+            super().__init__()
+            w, b = G["net_weight"]()
+            self.w, self.b = torch.nn.Parameter(w), torch.nn.Parameter(b)
+
+        def forward(self, graph):
+            return graph.x @ self.w + self.b + 0.01 * graph.edge_attr.sum()
+
+    sim = _simulator(Net()).train()
+    for c in range(G["N_CALLS"]):
+        x, y, ea, ei, pos = G["inputs"](c)
+        loss = training_step(sim, Graph(x=x, y=y, edge_attr=ea, edge_index=ei, pos=pos), L2Loss(),
+                             [NodeType.NORMAL, NodeType.OUTFLOW])
+        _close(loss.detach(), z[f"train{c}_l2"])
+    loss.backward()
+    assert sim.model.w.grad is not None and float(sim.model.w.grad.abs().sum()) > 0
+    pred = torch.zeros(3, 5, 2)
+    tgt = [torch.full((5, 2), float(i)) for i in range(3)]
+    assert torch.allclose(rollout_rmse(pred, tgt), torch.tensor([0.0, 1.0, 2.0]))

@@ -18,6 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from graph_physics_b200 import graph as G, processor as proc  # noqa: E402
 from graph_physics_b200.models import EncodeProcessDecode, Graph, Simulator  # noqa: E402
+from graph_physics_b200.training import training_step  # noqa: E402
 from graph_physics_b200.utils import L2Loss, NodeType  # noqa: E402
 
 z = np.load(os.path.join(ROOT, "tests", "golden", "cylinder_mesh.npz"))
@@ -47,8 +48,7 @@ loss_out = torch.zeros((), device=dev)
 def step():
     for p in params:
         p.grad = None
-    network_output, target, _ = sim(batch)
-    loss = loss_fn(target, network_output, batch.x[:, sim.node_type_index], masks=masks)
+    loss = training_step(sim, batch, loss_fn, masks)
     loss.backward()
     loss_out.copy_(loss.detach())
 
