@@ -21,6 +21,7 @@ sm_100 device and the library is built.
 """
 from __future__ import annotations
 
+import collections
 import weakref
 from typing import List, Optional, Sequence
 
@@ -61,7 +62,20 @@ def _timed(name, fn, *a, **kw):
     return fn(*a, **kw)
 
 
-_csr_cache: dict = {}
+_csr_cache: "collections.OrderedDict" = collections.OrderedDict()      # least recently used first
+CSR_CACHE_ENTRIES = 64
+
+
+def _csr_cache_put(edge_index: torch.Tensor, num_nodes: int, csr: G.CSRGraph) -> None:
+    """Entries whose tensor is gone are dropped first, then the least recently used ones: a stream of short-lived batch
+    tensors (batch.collate registers one per batch) must not push out the CSRs of the trajectories they are built
+    from."""
+    for k in [k for k, v in _csr_cache.items() if v[0]() is None]:
+        del _csr_cache[k]
+    _csr_cache[id(edge_index)] = (weakref.ref(edge_index), edge_index._version, int(num_nodes), csr)
+    _csr_cache.move_to_end(id(edge_index))
+    while len(_csr_cache) > CSR_CACHE_ENTRIES:
+        _csr_cache.popitem(last=False)
 
 
 def csr_for(edge_index: torch.Tensor, num_nodes: int) -> G.CSRGraph:
@@ -74,11 +88,10 @@ def csr_for(edge_index: torch.Tensor, num_nodes: int) -> G.CSRGraph:
     if hit is not None:
         ref, version, n, csr = hit
         if ref() is edge_index and version == edge_index._version and n == int(num_nodes):
+            _csr_cache.move_to_end(key)
             return csr
-    if len(_csr_cache) > 16:
-        _csr_cache.clear()
     csr = G.build_csr(edge_index, num_nodes)
-    _csr_cache[key] = (weakref.ref(edge_index), edge_index._version, int(num_nodes), csr)
+    _csr_cache_put(edge_index, num_nodes, csr)
     return csr
 
 
@@ -87,9 +100,7 @@ def register_csr(edge_index: torch.Tensor, num_nodes: int, csr: G.CSRGraph) -> N
     samples' cached CSRs), so the sort is not launched for it."""
     if csr.num_nodes != int(num_nodes) or csr.num_edges != int(edge_index.shape[1]):
         raise ValueError("register_csr: the CSR does not match edge_index / num_nodes")
-    if len(_csr_cache) > 16:
-        _csr_cache.clear()
-    _csr_cache[id(edge_index)] = (weakref.ref(edge_index), edge_index._version, int(num_nodes), csr)
+    _csr_cache_put(edge_index, num_nodes, csr)
 
 
 def _check_inputs(x, e, params, num_steps):

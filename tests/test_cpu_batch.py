@@ -81,3 +81,28 @@ def test_batch_csr_from_sample_csrs_is_the_stable_receiver_sort(golden_dir):
     wrong = _csr(ss[1].edge_index, 7)
     with pytest.raises(ValueError):
         B.collate(ss[:2], csrs=[wrong, wrong])
+
+
+def test_csr_cache_keeps_live_trajectories_over_dead_batches():
+    """processor.csr_for / register_csr: entries of tensors that no longer exist go first, then the least recently used;
+    a long stream of per-batch registrations must not evict the CSR of a tensor that is still in use."""
+    proc._csr_cache.clear()
+    keep_ei = torch.randint(0, 9, (2, 20))
+    keep = _csr(keep_ei, 9)
+    proc.register_csr(keep_ei, 9, keep)
+    for _ in range(4 * proc.CSR_CACHE_ENTRIES):                    # short-lived batch tensors
+        ei = torch.randint(0, 5, (2, 7))
+        proc.register_csr(ei, 5, _csr(ei, 5))
+        assert proc.csr_for(keep_ei, 9) is keep
+    assert len(proc._csr_cache) <= 2
+    live = [torch.randint(0, 5, (2, 7)) for _ in range(proc.CSR_CACHE_ENTRIES + 5)]
+    for ei in live:                                                # more live tensors than entries: oldest unused go
+        proc.register_csr(ei, 5, _csr(ei, 5))
+    assert len(proc._csr_cache) == proc.CSR_CACHE_ENTRIES
+    assert id(live[-1]) in proc._csr_cache and id(live[0]) not in proc._csr_cache
+    # a tensor modified in place is not a hit (version counter): the lookup falls through to the device build
+    proc.register_csr(keep_ei, 9, keep)
+    keep_ei[0, 0] = 1
+    with pytest.raises(RuntimeError):
+        proc.csr_for(keep_ei, 9)
+    proc._csr_cache.clear()
