@@ -67,8 +67,6 @@ def test_resident_trajectory_dataset_serves_the_reference_frames(golden_dir, tmp
     ds.close()
 
 
-@pytest.mark.skipif(os.environ.get("MGN_TEST_UNVERIFIED", "0") != "1",
-                    reason="written after round 1's GPU budget was spent; run with MGN_TEST_UNVERIFIED=1, then un-gate")
 def test_preprocessing_pipeline_on_device(golden_dir):
     """`preprocessing.build_preprocessing` on a raw sample (x, y, pos, face): the composed graph equals the graph.py
     functions called by hand, with and without world edges."""
