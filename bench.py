@@ -72,6 +72,51 @@ def peaks():
         return 6650.0, 1590.0, "fallback"
 
 
+class Progress:
+    """Flushed stderr marker before every phase, and a watchdog thread: a phase that exceeds `limit` seconds (a kernel
+    that never finishes holds the process inside a CUDA call, which no signal interrupts) gets the phase name, the
+    library's hang record and whatever result line exists printed, and the process exits 3 instead of sitting on the
+    GPU until the caller's limit."""
+
+    def __init__(self, limit, rank=0):
+        self.limit, self.rank = float(limit), rank
+        self.t00 = self.t0 = time.time()
+        self.name = "start"
+        self.partial = None          # result line so far (printed by the watchdog if a later phase stalls)
+        self.done = False
+        if self.limit > 0:
+            threading.Thread(target=self._watch, daemon=True).start()
+
+    def phase(self, name):
+        self.name, self.t0 = name, time.time()
+        if self.rank == 0:
+            print(f"[bench +{self.t0 - self.t00:6.1f}s] {name}", file=sys.stderr, flush=True)
+
+    def finish(self):
+        self.done = True
+        self.phase("done")
+
+    def _watch(self):
+        while not self.done:
+            time.sleep(1.0)
+            if self.done or time.time() - self.t0 <= self.limit:
+                continue
+            msg = f"phase '{self.name}' exceeded {self.limit:.0f} s"
+            try:
+                from graph_physics_b200 import _lib as L
+                hr = L.hang_report()
+                if hr:
+                    msg += " | " + hr
+            except Exception:
+                pass
+            print(f"[bench] WATCHDOG rank {self.rank}: {msg}", file=sys.stderr, flush=True)
+            if self.rank == 0:
+                line = dict(self.partial) if self.partial else {"metric": METRIC, "value": None}
+                line["error"] = msg
+                print(json.dumps(line), flush=True)
+            os._exit(3)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -225,6 +270,8 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    prog = Progress(args.phase_timeout, rank)
+    prog.phase("init: device, process group, library")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -232,6 +279,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     L.require_device()
 
+    prog.phase("set-up: mesh batch, model, pinned inputs")
     copies = args.copies
     ei1, n1 = load_mesh()
     ei = G.tile_batch(ei1.to(dev), n1, copies)
@@ -343,10 +391,12 @@ def run_b200(args):
         step_resident()
         after_replay()
 
+    prog.phase("csr build + eager pass (per-launch events of edge_bwd)")
     ms_eager, launches, ev = timed(step_eager, args.steps, args.warmup, with_events=True)
     # (2) the timed region of `value`: the same step replayed from a CUDA graph (no host launch gaps)
     step_fn, e2e_fn, graphed = step_eager, step_e2e, False
     if not args.no_cuda_graph:
+        prog.phase("cuda-graph capture (resident step, e2e steps)")
         try:
             cap_step = proc.CapturedStep(step_resident)
 
@@ -363,15 +413,18 @@ def run_b200(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
+    prog.phase("timed region: value (inputs resident)")
     ms, _, _ = timed(step_fn, args.steps, args.warmup)
     clk = clocks.stop() if rank == 0 else None
     e2e_steps = max(2, min(args.steps, 5))
+    prog.phase("timed region: e2e (pinned host inputs every step)")
     ms_e2e, _, _ = timed(e2e_fn, e2e_steps, 2)
     # forward only (inference / rollout step, SURVEY.md 8(d) "also report"): no_grad, ping-pong buffers, graph replay
     def fwd_only():
         with torch.no_grad():
             return model(Graph(x=x0, edge_index=ei, edge_attr=e0))
     fwd_fn = fwd_only
+    prog.phase("forward-only region")
     if graphed:
         try:
             fwd_fn = proc.CapturedStep(fwd_only)
@@ -416,12 +469,19 @@ def run_b200(args):
                               "algorithmic_GB_per_step": step_bytes / 1e9, "algorithmic_TFLOP_per_step": step_flops / 1e12,
                               "edge_bwd_share_of_step": edge_bwd_ms * STEPS_MP / ms_step},
         }
+        # the GPU numbers exist from here on: a stall in the baseline legs below cannot take them along (the watchdog
+        # prints this line); stderr carries it at once
+        prog.partial = line
+        print("[bench] result before the baseline legs: " + json.dumps(line), file=sys.stderr, flush=True)
         if args.cpu_seconds > 0 and world == 1:      # the CPU leg runs at N=1 only (rank 0 would hold N-1 ranks at a barrier)
+            prog.phase("cpu_baseline leg (oracle port on the host cores)")
             threads = os.cpu_count() or 1
             eps, t, e_cpu = cpu_oracle_run(args.cpu_copies, 2, 1, threads)
             line["cpu_baseline"] = {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port",
                                     "sample": f"{args.cpu_copies} of {copies} meshes ({e_cpu} edges), 15 steps fwd+bwd, "
                                               f"fp32 oracle port, median of 2 after 1 warm-up, {t:.2f} s per pass"}
+            prog.partial = line
+            prog.phase("eager-GPU baseline leg (oracle port's torch ops on this GPU, TF32)")
             try:
                 ms_eg = eager_gpu_run(ei, N, x0, e0, gx)
                 line["cpu_baseline"]["eager_gpu"] = {
@@ -447,9 +507,11 @@ def run_b200(args):
                 print(f"  {n:12s} n={len(d):3d} mean {1e3 * sum(d) / max(len(d), 1):8.1f} us  total {sum(d):7.3f} ms",
                       file=sys.stderr)
             print(f"  kernels {tot:.3f} ms of step {s0.elapsed_time(e0_):.3f} ms", file=sys.stderr)
+    prog.phase("teardown")
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    prog.finish()
 
 
 def main():
@@ -462,13 +524,26 @@ def main():
     ap.add_argument("--cpu-copies", type=int, default=1, help="meshes in the CPU sample")
     ap.add_argument("--cpu-seconds", type=float, default=1.0, help="0 disables the cpu_baseline leg")
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of a graph replay")
+    ap.add_argument("--phase-timeout", type=float, default=240.0,
+                    help="seconds one phase may take before the watchdog reports it and exits 3 (0 = off)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
-    else:
+        return
+    try:
         run_b200(args)
+    except Exception:
+        # a kernel that trapped on a starved barrier surfaces as a CUDA error here: say which wait it was
+        try:
+            from graph_physics_b200 import _lib as L
+            hr = L.hang_report()
+            if hr:
+                print("[bench] " + hr, file=sys.stderr, flush=True)
+        except Exception:
+            pass
+        raise
 
 
 if __name__ == "__main__":

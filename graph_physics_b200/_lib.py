@@ -48,10 +48,25 @@ def require_device(t: torch.Tensor | None = None) -> None:
         _device_ok = True
 
 
+def hang_report() -> str:
+    """One line describing the mbarrier wait that timed out inside a kernel (csrc/tc05.cuh: every wait is bounded and
+    traps after writing a record to host-mapped memory), or "" if none was recorded.  Readable after the CUDA context
+    has faulted."""
+    if _lib is None:
+        return ""
+    buf = ctypes.create_string_buffer(512)
+    if lib().mgn_hang_report(buf, ctypes.c_int(512)):
+        return buf.value.decode("utf-8", "replace")
+    return ""
+
+
 def check(rc: int) -> None:
     if rc == 0:
         return
     msg = lib().mgn_last_error().decode("utf-8", "replace")
+    hr = hang_report() if rc > 0 else ""
+    if hr:
+        msg = f"{msg} [{hr}]"
     if rc < 0:
         raise ValueError(f"libmgn_b200: {msg} (code {rc})")
     raise MgnError(f"libmgn_b200: {msg} (cudaError {rc})")

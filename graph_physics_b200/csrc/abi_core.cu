@@ -39,3 +39,49 @@ extern "C" int mgn_debug_set_timeline(long long* buf, int cap) {
   g_mgn_timeline_cap_host = cap;
   return MGN_OK;
 }
+
+// ---------------------------------------------------------------- hang record (tc05.cuh: bounded mbarrier waits)
+// Host-mapped pinned memory, so that the record survives the trap that follows it (device memory of a faulted context
+// cannot be read back).  Layout (u64): [0] magic, [1] tag = file id << 16 | line, [2] block << 32 | thread,
+// [3] barrier shared address << 32 | parity, [4] grid size << 32 | SM id.
+static unsigned long long* g_hang_host = nullptr;
+static bool g_hang_tried = false;
+
+void* mgn_hang_buffer() {
+  if (!g_hang_tried) {
+    g_hang_tried = true;
+    void* h = nullptr;
+    if (cudaHostAlloc(&h, 8 * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      memset(h, 0, 8 * sizeof(unsigned long long));
+      g_hang_host = (unsigned long long*)h;
+    } else {
+      (void)cudaGetLastError();
+    }
+  }
+  return g_hang_host;
+}
+
+static const char* hang_file(unsigned id) {
+  switch (id) {
+    case 1: return "mlp_fwd.cu";
+    case 2: return "edge_fwd_hl.cu";
+    case 3: return "mlp_bwd.cu";
+    case 4: return "selftest.cu";
+    default: return "?";
+  }
+}
+
+// Writes a one-line description of the recorded mbarrier time-out into buf (empty string if none); returns 1 if a
+// record exists.  Safe to call after a failed launch / synchronize: it only reads host memory.
+extern "C" int mgn_hang_report(char* buf, int n) {
+  if (buf && n > 0) buf[0] = 0;
+  const unsigned long long* h = g_hang_host;
+  if (h == nullptr || h[0] == 0) return 0;
+  if (buf && n > 0)
+    snprintf(buf, (size_t)n,
+             "mbarrier wait timed out: %s:%u block %u of %u thread %u sm %u barrier@smem 0x%x parity %u",
+             hang_file((unsigned)(h[1] >> 16)), (unsigned)(h[1] & 0xffff), (unsigned)(h[2] >> 32), (unsigned)(h[4] >> 32),
+             (unsigned)(h[2] & 0xffffffffu), (unsigned)(h[4] & 0xffffffffu), (unsigned)(h[3] >> 32),
+             (unsigned)(h[3] & 0xffffffffu));
+  return 1;
+}

@@ -68,10 +68,31 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 #include <stdlib.h>
+// ---------------------------------------------------------------- hang record (tc05.cuh: bounded mbarrier waits)
+// 8 x u64 of host-mapped pinned memory, allocated once per process (abi_core.cu).  Each translation unit keeps the
+// device pointer in its own __device__ variable, set on that unit's first launch.
+void* mgn_hang_buffer();                       // host pointer == device pointer (UVA), or null if the allocation failed
+static __device__ unsigned long long* g_mgn_hang_dev = nullptr;
+
+static inline cudaError_t mgn_register_hang_buffer(cudaStream_t stream) {
+  static bool done = false;
+  if (done) return cudaSuccess;
+  void* h = mgn_hang_buffer();
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { (void)cudaGetLastError(); return cudaSuccess; }
+  if (cs != cudaStreamCaptureStatusNone) return cudaSuccess;     // first launch under capture: try again later
+  cudaError_t e = cudaMemcpyToSymbolAsync(g_mgn_hang_dev, &h, sizeof(h), 0, cudaMemcpyHostToDevice, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);       // `h` is a stack variable
+  done = true;
+  return e;
+}
+
 template <class P>
 static inline cudaError_t mgn_launch(void (*kernel)(P), int grid, int block, size_t smem, cudaStream_t stream,
                                      const P& p) {
   static const bool pdl = !(getenv("MGN_PDL") && atoi(getenv("MGN_PDL")) == 0);
+  cudaError_t he = mgn_register_hang_buffer(stream);
+  if (he != cudaSuccess) return he;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
   cfg.blockDim = dim3((unsigned)block);

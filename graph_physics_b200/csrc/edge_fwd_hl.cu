@@ -14,6 +14,7 @@
 // products ahead), lo tile (updated in place), one output tile for the new hi (between tiles it stages the gathered
 // P_j rows of the next tile).  Tensor memory: accumulator (128
 // columns), the hidden activations as the next product's A operand (64), the parked hi chunk of every thread (64).
+#define MGN_FILE_ID 2
 #include <algorithm>
 
 #include "mlp_v2.cuh"

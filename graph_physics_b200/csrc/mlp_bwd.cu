@@ -18,6 +18,7 @@
 // (bulk async copies from L2), the remaining five slots hold the activation / gradient tiles of the
 // current 128-row tile.  512 threads per tile (mlp_v2.cuh mapping).  Gradients arrive pre-scaled by
 // a power of two (processor.py) so that fp16 operands keep their precision; all of this is linear in g.
+#define MGN_FILE_ID 3
 #include "mlp_v2.cuh"
 #include "mlp_fwd_abi.cuh"
 #include <cstdlib>

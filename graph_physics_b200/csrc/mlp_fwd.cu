@@ -11,6 +11,7 @@
 // as fp16 rows in the layer-1 epilogue, so the per-edge tensor work is e W_e^T only.
 // All products run on tcgen05 (fp16 operands, fp32 accumulation in TMEM); residual
 // streams, RMSNorm and the segmented sum are fp32.
+#define MGN_FILE_ID 1
 #include "mlp_v2.cuh"
 
 using namespace mgn;

@@ -2,6 +2,7 @@
 // shared-memory descriptor conventions of tc05.cuh (K-major / MN-major views of the
 // same swizzled tile, the N=16 "ones" operand used for bias gradients, K=256 and
 // N=256 shapes) against a CPU product before the fused kernels rely on them.
+#define MGN_FILE_ID 4
 #include "common.cuh"
 #include "tc05.cuh"
 

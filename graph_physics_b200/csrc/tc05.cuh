@@ -18,6 +18,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include "common.cuh"
+
 namespace tc05 {
 
 static constexpr uint32_t PANEL_COLS = 64;
@@ -102,18 +104,56 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_init_fence() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t a = smem_u32(bar);
+// ---- bounded mbarrier wait.  A lost arrive must become a CUDA error, not an endless spin: after MBAR_FAST_POLLS
+// failed polls the waiter reads %globaltimer on every further poll and, once MBAR_TIMEOUT_NS have passed, writes a record
+// {magic, tag (source file id << 16 | line of the wait), block, thread, barrier address, parity, SM} to the host-mapped
+// hang buffer (common.cuh: g_mgn_hang_dev, registered by mgn_launch) and traps.  The launch then fails with
+// cudaErrorLaunchFailure and mgn_hang_report() / mgn_last_error() name the wait that starved.
+static constexpr uint32_t MBAR_FAST_POLLS = 4096;
+static constexpr unsigned long long MBAR_TIMEOUT_NS = 4000000000ull;   // 4 s: a legitimate wait is microseconds
+static constexpr unsigned long long HANG_MAGIC = 0x4d474e48414e4721ull;  // "MGNHANG!"
+
+static __device__ __noinline__ void mbar_timeout(uint32_t bar_saddr, uint32_t parity, uint32_t tag) {
+  unsigned long long* h = g_mgn_hang_dev;
+  if (h != nullptr && atomicCAS(h, 0ull, HANG_MAGIC) == 0ull) {      // first reporter wins
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    h[1] = tag;
+    h[2] = ((unsigned long long)blockIdx.x << 32) | threadIdx.x;
+    h[3] = ((unsigned long long)bar_saddr << 32) | parity;
+    h[4] = ((unsigned long long)gridDim.x << 32) | smid;
+    __threadfence_system();
+  }
+  __trap();
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t a, uint32_t parity) {
+  uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}\n" ::"r"(a),
-      "r"(parity)
-      : "memory");
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+  return ok != 0;
 }
+__device__ __forceinline__ void mbar_wait_tagged(uint64_t* bar, uint32_t parity, uint32_t tag) {
+  const uint32_t a = smem_u32(bar);
+#pragma unroll 1
+  for (uint32_t i = 0; i < MBAR_FAST_POLLS; ++i)
+    if (mbar_try_wait(a, parity)) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+#pragma unroll 1
+  while (!mbar_try_wait(a, parity)) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t - t0 > MBAR_TIMEOUT_NS) mbar_timeout(a, parity, tag);
+  }
+}
+#ifndef MGN_FILE_ID
+#define MGN_FILE_ID 0
+#endif
+// every wait carries its source position: (file id << 16) | line
+#define mbar_wait(bar, parity) mbar_wait_tagged((bar), (parity), ((uint32_t)(MGN_FILE_ID) << 16) | (uint32_t)__LINE__)
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");

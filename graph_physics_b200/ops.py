@@ -51,12 +51,6 @@ def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
     return out
 
 
-# MGN_EDGE_FWD_PP=1 runs steps 1..K-1 on the two-tiles-in-flight edge kernel (csrc/edge_fwd_pp.cu).  Measured equal to
-# the one-tile kernel (12.83 vs 12.84 ms per 15-step fwd+bwd): the edge forward is bound by the SM's load/store path,
-# not by the issue-to-commit latency of the products, so it stays opt-in.
-EDGE_FWD_PP = bool(int(__import__("os").environ.get("MGN_EDGE_FWD_PP", "0")))
-
-
 def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor, senders: torch.Tensor,
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
              e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None,
@@ -82,12 +76,6 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
         e_out = torch.empty_like(e_in)
     if aggr is None:
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
-    if e16_in is not None and rowmap is None and saves is None and e16_out is None and EDGE_FWD_PP:
-        # steps 1..K-1: the two-tiles-in-flight kernel (csrc/edge_fwd_pp.cu)
-        L.check(L.lib().mgn_edge_fwd_pp(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16_in), L.p(e_out), L.p(e16_next),
-                                        L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3),
-                                        L.p(b4), L.p(scale), L.stream()))
-        return e_out, aggr
     L.check(L.lib().mgn_edge_fwd2(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
                                   L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
                                   L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next),

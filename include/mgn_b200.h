@@ -28,6 +28,10 @@ extern "C" {
 const char* mgn_last_error(void);
 int mgn_version(void);
 int mgn_check_device(void); /* 0 iff the current device is sm_100 */
+/* Every mbarrier wait inside the kernels is bounded (4 s): a wait that starves writes {source line, block, thread,
+ * barrier, parity} to host-mapped memory and traps, so the launch fails with a cudaError instead of spinning.
+ * mgn_hang_report copies a one-line description of that record into buf (returns 1 if there is one, else 0). */
+int mgn_hang_report(char* buf, int n);
 
 /* ------------------------------------------------------------------ graph set-up */
 /* meshdata_to_graph tet->4 triangles, graphphysics/utils/torch_graph.py:170-186.
@@ -120,13 +124,6 @@ int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap,
                  const void* packed, const float* b2, const float* b3, const float* b4,
                  const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
                  const void* e16_in, void* e16_next, int out_in_csr_order, void* stream);
-/* The same edge update for steps 1..K-1 of the processor loop (operand tile images of e_in available, rows in CSR
- * order): two tiles in flight per CTA, hidden activations in tensor memory (csrc/edge_fwd_pp.cu).  Results equal
- * mgn_edge_fwd(rowmap = NULL, e16_in) up to the summation order of the per-warp aggregation partials. */
-int mgn_edge_fwd_pp(int64_t E, int64_t N, const float* e_in, const void* e16_in, float* e_out, void* e16_next,
-                    const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
-                    const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
-                    void* stream);
 /* mgn_edge_fwd plus e16lo_next: tile images of  e_out - fp16(e_out)  (fp16), i.e. together with e16_next the
  * image + remainder form of the residual stream that mgn_edge_fwd_hl consumes.  With both images requested e_out
  * may be NULL (the fp32 rows are then not written at all). */
@@ -214,6 +211,9 @@ int mgn_selftest_umma2(const void* a, const void* b, float* d, int n, int ksteps
  * tcgen05.mma.cta_group::2 stream on a cluster of two CTAs, each holding half of B (a_tmem 1 = A operand in tensor
  * memory).  Not used by any product kernel; run only on request (tests/test_gpu_umma.py, MGN_TEST_PAIR=1) */
 int mgn_selftest_umma_pair(const void* a, const void* b, float* d, int n, int ksteps, int a_tmem, void* stream);
+/* Developer micro-benchmark (csrc/probe.cu, tools/probe.py): cycle counts of TMEM loads / stores by number of active
+ * warps and of product issue-to-completion latencies on one SM; out_dev [64] int64. */
+int mgn_probe_sm(long long* out_dev, int iters, void* stream);
 
 #ifdef __cplusplus
 }

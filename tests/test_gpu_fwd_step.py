@@ -94,48 +94,6 @@ def test_no_edges():
     assert mo.rel_l2(x1, xr) < TOL_STEP
 
 
-def test_two_tile_edge_kernel_equals_one_tile_kernel(golden_dir):
-    """csrc/edge_fwd_pp.cu (two tiles in flight, activations in tensor memory, output staged in two halves) against
-    mlp_fwd_kernel<true> on the same image-fed step: same products, same epilogue arithmetic, same 8-row aggregation
-    groups -> identical edge rows and tile images, aggregation equal up to the order of the red.add partials."""
-    import numpy as np
-    from graph_physics_b200 import graph as G, ops
-    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
-    n1 = z["points"].shape[0]
-    ei = G.tile_batch(torch.as_tensor(z["edge_index"].astype(np.int64)).cuda(), n1, 7)
-    N, E = n1 * 7, ei.shape[1]
-    assert E % 128 != 0
-    csr = G.build_csr(ei, N)
-    torch.manual_seed(4)
-    dev = "cuda"
-    ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
-    nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
-    b = [torch.randn(128, device=dev) * 0.05 for _ in range(4)]
-    sc = 1.0 + 0.1 * torch.randn(128, device=dev)
-    packed = ops.pack_block(ew, nw)
-    x = torch.randn(N, 128, device=dev)
-    e = torch.randn(E, 128, device=dev)
-    P = ops.p_fwd(x, packed, b[0])
-    img = ops.e16_image(E, dev)
-    ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e16_out=img)   # makes the image
-    outs = []
-    for pp in (False, True):
-        old = ops.EDGE_FWD_PP
-        ops.EDGE_FWD_PP = pp
-        try:
-            nxt = ops.e16_image(E, dev).zero_()
-            eo, ag = ops.edge_fwd(e, None, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, e16_in=img,
-                                  e16_next=nxt)
-            torch.cuda.synchronize()
-            outs.append((eo, ag, nxt))
-        finally:
-            ops.EDGE_FWD_PP = old
-    (e0, a0, i0), (e1, a1, i1) = outs
-    assert torch.equal(e0, e1)
-    assert torch.equal(i0, i1)
-    assert float((a0 - a1).abs().max()) <= 1e-5 * float(a0.abs().max())
-
-
 def _hl_setup(golden_dir, copies, seed):
     import numpy as np
     from graph_physics_b200 import graph as G, ops
