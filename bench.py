@@ -2,8 +2,16 @@
 """bench.py -- MGN processor edges/s, forward + backward, H=128, 15 message-passing steps
 (BASELINE.json metric) on N GPUs of one node.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config 2|3|4|5]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+--config picks the BASELINE.json workload (default 2 = the configuration the metric is quoted on):
+  2  32 x CylinderFlow mesh per GPU, data-parallel (weak scaling); the JSON line also carries a `partitioned` record:
+     the config-5 family point for this N (ONE Kuhn tetrahedral grid cut over the N GPUs, halo exchange every step;
+     ~0.5 M nodes / 6.9 M edges per GPU, so N = 1 is the weak-scaling base of the 159^3 mesh at N = 8)
+  3  16 x DeformingPlate-shaped tet mesh with mesh + world edges per GPU (synth.config3_batch), data-parallel
+  4  47^3 tet mesh, 2-hop adjacency, MeshMask keep-ratio 0.6 sub-graph (synth.config4_graph), one replica per GPU
+  5  the partitioned record alone as the headline value
 
 Workload (BASELINE.json configs[1]): per GPU a block-diagonal batch of 32 copies of
 the reference's own CylinderFlow test mesh (tests/mock_vtu/cylinder_0.vtu: 1,923 nodes, 11,070
@@ -41,9 +49,33 @@ METRIC = "mgn_processor_edges_per_s_fwd_bwd_h128_15steps"
 BYTES_EDGE_STEP, BYTES_NODE_STEP = 2568, 7168          # SURVEY.md 8(d), fwd+bwd per step
 FLOPS_EDGE_STEP, FLOPS_NODE_STEP = 589824, 491520
 EDGE_BWD_BYTES_EDGE, EDGE_BWD_BYTES_NODE = 1540, 2048  # the dominant kernel's share
-# dram__bytes_read.sum + dram__bytes_write.sum of one edge_bwd_kernel launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r01_ncu_edge_bwd_v6.md); not re-measured by bench.py
-EDGE_BWD_DRAM_BYTES_NCU = 338_405_632 + 209_580_800
+
+
+def kernel_source_hash():
+    """sha256 over csrc/*.cu, *.cuh: identifies the build an ncu capture belongs to."""
+    import hashlib
+    d = os.path.join(ROOT, "graph_physics_b200", "csrc")
+    h = hashlib.sha256()
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh")):
+            with open(os.path.join(d, f), "rb") as fh:
+                h.update(f.encode() + b"\0" + fh.read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(kernel, config):
+    """`roofline.traffic`: dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
+    `ncu --set full` capture (profiles/traffic.json, written by tools/ncu_traffic.py) -- only if that capture was made
+    on THIS build of the kernels (source hash) and this workload; otherwise None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        if t.get("source_hash") != kernel_source_hash():
+            return None, f"profiles/traffic.json is from build {t.get('source_hash')}, not this one"
+        rec = t["kernels"][kernel][f"config{config}"]
+        return int(rec["dram_bytes_per_launch"]), rec.get("source", "profiles/traffic.json")
+    except Exception as exc:
+        return None, f"no capture for this build ({type(exc).__name__})"
 
 
 def load_mesh():
@@ -162,16 +194,72 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+# ------------------------------------------------------------------ workloads (BASELINE.json configs)
+def workload_cpu_graph(config, copies):
+    """(edge_index int64 [2,E] on the CPU, N, description) of the workload's graph WITHOUT a GPU: what the reference
+    arm and the cpu_baseline leg run on.  Configs 3 / 4 use the oracle's numpy graph functions (same results as the
+    device set-up path, tests/test_gpu_setup.py)."""
+    if config in (2, 5):
+        ei1, n1 = load_mesh()
+        offs = (torch.arange(copies) * n1).view(1, copies, 1)
+        return (ei1.view(2, 1, -1) + offs).reshape(2, -1), n1 * copies, f"{copies} x cylinder mesh"
+    from graph_physics_b200 import synth
+    from oracle import graph_oracle as go
+    if config == 3:
+        eis, off = [], 0
+        for s_ in range(copies):
+            pos, cells, nt = synth.plate_sample(seed=s_, gap=0.012 + 0.014 * ((s_ * 7) % 16) / 15)
+            n = pos.shape[0]
+            ei = go.world_edges(go.face_to_edge(go.cells_to_faces(cells.numpy()), n), pos.numpy(), nt.numpy(), n,
+                                radius=0.03)
+            eis.append(torch.as_tensor(ei.astype(np.int64)) + off)
+            off += n
+        return torch.cat(eis, dim=1), off, f"{copies} x plate + obstacle sample (mesh + world edges)"
+    if config == 4:
+        g = copies          # grid edge length of the CPU sample
+        ei1 = synth.kuhn_grid_edges(g, g, g)
+        eik = go.k_hop_edge_index(ei1.numpy(), 2, g ** 3)
+        sel = torch.randperm(g ** 3, generator=torch.Generator().manual_seed(0))[:int(0.6 * g ** 3)].numpy()
+        eim = go.filter_edges(eik, sel)[0]
+        return torch.as_tensor(eim.astype(np.int64)), int(sel.size), f"{g}^3 tet grid, 2-hop, MeshMask keep 0.6"
+    raise ValueError(config)
+
+
+def workload_device_graph(config, copies, dev):
+    """(edge_index [2,E] on `dev`, N, config description dict) built with the device set-up kernels."""
+    from graph_physics_b200 import graph as G, synth
+    if config == 2:
+        ei1, n1 = load_mesh()
+        return G.tile_batch(ei1.to(dev), n1, copies), n1 * copies, {
+            "workload": f"BASELINE configs[1]: {copies} x CylinderFlow mesh (1923 nodes, 11070 directed edges) per GPU, "
+                        "block-diagonal batch; MGN processor (only_processor=True), H=128, 15 steps, fwd+bwd"}
+    if config == 3:
+        d = synth.config3_batch(copies=copies, device=dev)
+        return d["edge_index"], d["num_nodes"], {
+            "workload": f"BASELINE configs[2]: {copies} x DeformingPlate-shaped tet sample (plate 18x18x3 + obstacle "
+                        f"7x7x6 nodes) per GPU, mesh edges {d['mesh_edges']} + world edges {d['world_edges']} "
+                        "(radius 0.03), 8-dim raw edge features; MGN processor, H=128, 15 steps, fwd+bwd"}
+    if config == 4:
+        d = synth.config4_graph(grid=47, device=dev)
+        ei, n = d["masked"]
+        return ei, n, {
+            "workload": f"BASELINE configs[3]: 47^3 Kuhn tet mesh (103,823 nodes, {d['one_hop_edges']} 1-hop edges), 2-hop "
+                        f"adjacency ({d['full'][0].shape[1]} edges), MeshMask keep-ratio 0.6 sub-graph; one replica per "
+                        "GPU; MGN processor, H=128, 15 steps, fwd+bwd"}
+    raise ValueError(config)
+
+
+DEFAULT_COPIES = {2: 32, 3: 16, 4: 1, 5: 1}
+
+
 # ------------------------------------------------------------------ CPU oracle leg
-def cpu_oracle_run(copies, reps, warmup, threads):
-    """fwd+bwd through the 15 blocks with the CPU oracle (oracle/mgn_oracle.py: the same ATen ops as
-    the reference's PyTorch path) on `copies` meshes.  Returns (edges/s, seconds per pass, E)."""
+def cpu_oracle_run(ei, n, reps, warmup, threads, budget_s=None):
+    """fwd+bwd through the 15 blocks with the CPU oracle (oracle/mgn_oracle.py: the same ATen ops as the reference's
+    PyTorch path) on the graph `ei`.  Stops early once `budget_s` seconds of timed passes are in (at least one).
+    Returns (edges/s, seconds per pass, passes timed)."""
     from oracle import mgn_oracle as mo
     torch.set_num_threads(threads)
-    ei1, n1 = load_mesh()
-    offs = (torch.arange(copies) * n1).view(1, copies, 1)
-    ei = (ei1.view(2, 1, -1) + offs).reshape(2, -1)
-    n, e = n1 * copies, ei.shape[1]
+    e = ei.shape[1]
     p = mo.init_params(STEPS_MP, hidden=H, seed=0)
     for v in p.values():
         v.requires_grad_(True)
@@ -187,8 +275,10 @@ def cpu_oracle_run(copies, reps, warmup, threads):
         dt = time.perf_counter() - t0
         if it >= warmup:
             ts.append(dt)
+            if budget_s is not None and sum(ts) > budget_s:
+                break
     t = float(np.median(ts))
-    return e / t, t, e
+    return e / t, t, len(ts)
 
 
 def eager_gpu_run(ei, n, x0, e0, gx, reps=3, warmup=1):
@@ -217,43 +307,173 @@ def eager_gpu_run(ei, n, x0, e0, gx, reps=3, warmup=1):
         torch.backends.cuda.matmul.allow_tf32 = old
 
 
+def cpu_sample_copies(args):
+    """How much of the workload the CPU legs run: config 2 / 3 the whole per-GPU batch (same config as the GPU arm),
+    config 4 a 16^3 grid of the same family (the 47^3 graph takes minutes per pass on the host), config 5 the
+    config-2 batch (the reference cannot hold the 4 M-node mesh's autograd state on the host)."""
+    if args.cpu_copies > 0:
+        return args.cpu_copies
+    return {2: 32, 3: 16, 4: 16, 5: 32}[args.config]
+
+
 # ------------------------------------------------------------------ reference arm (CPU)
 def run_reference(args):
-    """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be
-    imported here or on the GPU box (torch_geometric absent, no network), so the timed
-    code is the oracle port of its PyTorch ops, with all host threads, on a bounded sample (one
-    mesh of the 32-mesh batch).  Rank 0 only."""
+    """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be imported here or on
+    the GPU box (torch_geometric absent, no network), so the timed code is the oracle port of its PyTorch
+    ops, with all host threads, on the SAME per-GPU workload as the B200 arm (all 32 meshes for config 2).  One step
+    = one fwd+bwd pass (several seconds on the host): at most `--steps` passes are timed and the run stops once
+    ~90 s of timed passes are in.  Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    prog = Progress(args.phase_timeout if args.phase_timeout > 0 else 0, 0)
+    prog.limit = max(prog.limit, 900.0)
     threads = os.cpu_count() or 1
-    copies = args.cpu_copies
-    eps, t, e = cpu_oracle_run(copies, args.steps, args.warmup, threads)
-    sample = f"{copies} of 32 meshes per step ({e} edges), oracle port of the reference's PyTorch ops, fp32"
+    copies = cpu_sample_copies(args)
+    prog.phase("reference arm: building the workload graph on the host")
+    ei, n, what = workload_cpu_graph(args.config, copies)
+    prog.phase(f"reference arm: oracle port fwd+bwd on {threads} threads, E={ei.shape[1]}")
+    eps, t, done = cpu_oracle_run(ei, n, max(1, args.steps), min(args.warmup, 1), threads, budget_s=90.0)
+    sample = (f"{what}: N={n}, E={ei.shape[1]} per pass, {done} timed passes (median), oracle port of the reference's "
+              "PyTorch ops, fp32")
+    cfg = {"workload": f"BASELINE config {args.config}: {what}; MGN processor, H=128, 15 steps, fwd+bwd",
+           "nodes_per_gpu": n, "edges_per_gpu": int(ei.shape[1]), "hidden": H, "mp_steps": STEPS_MP,
+           "parallelism": f"dp{args.gpus}", "sample": sample}
     line = {
         "impl": "reference", "metric": METRIC, "value": eps, "unit": "edges/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.gpus, copies_note=sample),
+        "steps": done, "warmup": min(args.warmup, 1), "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": eps, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+    prog.finish()
 
 
-def workload_config(n_gpus, copies=32, copies_note=None):
-    cfg = {"workload": f"BASELINE configs[1]: {copies} x CylinderFlow mesh (1923 nodes, 11070 directed edges) per GPU, "
-                       "block-diagonal batch; MGN processor (only_processor=True), H=128, 15 steps, fwd+bwd",
-           "nodes_per_gpu": 1923 * copies, "edges_per_gpu": 11070 * copies, "hidden": H, "mp_steps": STEPS_MP,
-           "parallelism": f"dp{n_gpus}",
-           "numerics": "fp16 tensor-core operands, fp32 accumulation; residual adds, RMSNorm, aggregation and gradients in "
-                       "fp32; edge stream held between steps as fp16 image + fp16 remainder (>= 21 bits)",
-           "l2": "inputs larger than L2: every step streams a 181 MB edge-latent version (91 MB image + 91 MB remainder) "
-                 "and a 181 MB edge-gradient version; 3.5 GB of saved state per fwd+bwd (L2 126 MB)"}
-    if copies_note:
-        cfg["sample"] = copies_note
+def workload_config(n_gpus, n, e, desc):
+    cfg = dict(desc)
+    cfg.update({
+        "nodes_per_gpu": n, "edges_per_gpu": e, "hidden": H, "mp_steps": STEPS_MP, "parallelism": f"dp{n_gpus}",
+        "numerics": "fp16 tensor-core operands, fp32 accumulation; residual adds, RMSNorm, aggregation and gradients in "
+                    "fp32; edge stream held between steps as fp16 image + fp16 remainder (>= 21 bits)",
+        "l2": f"inputs larger than L2: every step streams a {e * 512 / 1e6:.0f} MB edge-latent version and a "
+              f"{e * 512 / 1e6:.0f} MB edge-gradient version (L2 126 MB)"})
     return cfg
+
+
+# ------------------------------------------------------------------ config 5: one mesh cut over the GPUs
+def run_partitioned_point(args, prog, dev, rank, world, grid=0, steps=5, warmup=3):
+    """The config-5 family point for this world size (tools/bench_partitioned.py is the stand-alone form): ONE g^3 Kuhn
+    tetrahedral grid, node-partitioned by receiver over `world` GPUs (graph_physics_b200.partition), a halo exchange
+    of boundary node latents every message-passing step forward and of their gradients backward.  Default g: the cube
+    closest to world * 159^3 / 8 nodes (79, 100, 126, 159 at 1, 2, 4, 8 GPUs), i.e. ~0.5 M nodes / 6.9 M edges per
+    GPU -- weak scaling towards BASELINE's 4 M-node mesh with the 1-GPU point as base."""
+    import torch.distributed as dist
+
+    from graph_physics_b200 import dist_processor as DP
+    from graph_physics_b200 import graph as G
+    from graph_physics_b200 import partition as PT
+    from graph_physics_b200 import processor as proc
+    from graph_physics_b200 import synth
+    from graph_physics_b200.models import EncodeProcessDecode
+    from graph_physics_b200.models.layers import block_param_list
+
+    prog.phase("partitioned: grid edges, partition, local CSR")
+    g = grid or synth.grid_for_nodes(world * 159 ** 3 / 8)
+    n = g ** 3
+    ei = synth.kuhn_grid_edges(g, g, g, device=dev)
+    E = int(ei.shape[1])
+    part = PT.build_partition(ei, n, rank, world)
+    del ei
+    torch.manual_seed(0)
+    model = EncodeProcessDecode(STEPS_MP, H, H, H, hidden_size=H, only_processor=True).to(dev)
+    blocks = [block_param_list(b) for b in model.processor_list]
+
+    def rows(ids, seed):       # functions of the GLOBAL node / edge id: every world size sees the same problem
+        gen = torch.Generator(device=dev).manual_seed(seed)
+        base = torch.randn((1024, H), generator=gen, device=dev)
+        return base[ids % 1024] + 0.5 * base[(ids // 1024) % 1024].roll(1, dims=1)
+
+    def rms(t):
+        return t / (t.norm(dim=-1, keepdim=True) * H ** -0.5 + 1e-8)
+    own_ids = torch.arange(part.node_begin, part.node_begin + part.num_owned, device=dev)
+    x_own = rms(rows(own_ids, 1)).requires_grad_(True)
+    e_loc = rms(rows(part.edge_ids, 2)).requires_grad_(True)
+    gx = rows(own_ids, 3) / (n * H) ** 0.5
+    local_csr = G.build_csr(part.edge_index, part.num_ext)
+    if part.edge_index.shape[1]:
+        local_csr.by_sender
+
+    def step():
+        for p_ in model.parameters():
+            p_.grad = None
+        x_own.grad = None
+        e_loc.grad = None
+        xo, _ = DP.run_partitioned(x_own, e_loc, part, blocks, csr=local_csr, need_edges=False)
+        xo.backward(gx)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    prog.phase(f"partitioned: {g}^3 grid over {world} GPU(s), warm-up + timed steps")
+    for _ in range(warmup):
+        step()
+    sync()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = proc.LAUNCHES
+    t0.record()
+    for _ in range(steps):
+        step()
+    t1.record()
+    sync()
+    launches = proc.LAUNCHES - l0
+    ms = torch.tensor([t0.elapsed_time(t1) / steps], device=dev)
+    prog.phase("partitioned: halo exchanges alone")
+    hx = PT.HaloExchange(part)
+    buf = torch.zeros((part.num_ext, H), device=dev)
+    for _ in range(2):
+        hx.forward(buf)
+    sync()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record()
+    for _ in range(STEPS_MP):
+        hx.forward(buf)
+        hx.backward(buf)
+    h1.record()
+    sync()
+    halo_ms = torch.tensor([h0.elapsed_time(h1)], device=dev)
+    stats = torch.tensor([part.num_owned, part.num_halo, int(part.edge_ids.numel()),
+                          torch.cuda.max_memory_allocated(dev) / 2 ** 30], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(halo_ms, op=dist.ReduceOp.MAX)
+        allst = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(allst, stats)
+    else:
+        allst = [stats]
+    t = float(ms)
+    hbm, tf, which = peaks()
+    step_bytes = STEPS_MP * (E * BYTES_EDGE_STEP + n * BYTES_NODE_STEP)
+    rec = {
+        "value": E / (t * 1e-3), "unit": "edges/s", "ms_per_step": t, "steps": steps, "warmup": warmup,
+        "scaling": "weak", "n_gpus": world,
+        "workload": f"BASELINE configs[4] family: {g}^3 Kuhn tetrahedral grid, N={n}, E={E}, ONE mesh node-partitioned "
+                    f"by receiver over {world} GPU(s); 15 steps fwd+bwd; eager launches; 15 forward + 15 reverse halo "
+                    "exchanges (NCCL all-to-all-v) per step",
+        "nodes": n, "edges": E,
+        "per_rank": {"owned_nodes": [int(s_[0]) for s_ in allst], "halo_nodes": [int(s_[1]) for s_ in allst],
+                     "edges": [int(s_[2]) for s_ in allst], "max_mem_gib": [round(float(s_[3]), 1) for s_ in allst]},
+        "halo_exchange_ms_per_step": float(halo_ms), "halo_exchanges_per_step": 2 * STEPS_MP,
+        "gpu_launches": launches,
+        "step_hbm_frac_per_gpu": step_bytes / world / (t * 1e-3) / 1e9 / hbm,
+    }
+    del x_own, e_loc, gx, local_csr, part, model, blocks, buf
+    torch.cuda.empty_cache()
+    return rec
 
 
 # ------------------------------------------------------------------ B200 arm
@@ -261,7 +481,6 @@ def run_b200(args):
     import torch.distributed as dist
 
     from graph_physics_b200 import _lib as L
-    from graph_physics_b200 import graph as G
     from graph_physics_b200 import parallel, processor as proc
     from graph_physics_b200.models import EncodeProcessDecode, Graph
 
@@ -279,11 +498,29 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     L.require_device()
 
-    prog.phase("set-up: mesh batch, model, pinned inputs")
-    copies = args.copies
-    ei1, n1 = load_mesh()
-    ei = G.tile_batch(ei1.to(dev), n1, copies)
-    N, E = n1 * copies, ei.shape[1]
+    if args.config == 5:
+        rec = run_partitioned_point(args, prog, dev, rank, world, grid=args.grid, steps=max(3, min(args.steps, 10)),
+                                    warmup=args.warmup)
+        if rank == 0:
+            line = {"metric": METRIC, "value": rec["value"], "unit": "edges/s", "n_gpus": world, "steps": rec["steps"],
+                    "warmup": rec["warmup"], "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
+                    "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+                    "config": {"workload": rec["workload"], "parallelism": f"node-partition x{world}",
+                               "l2": "inputs larger than L2"},
+                    "gpu_launches": rec["gpu_launches"], "launch_mode": "eager", "partitioned": rec,
+                    "e2e": None, "roofline": None, "cpu_baseline": None}
+            print(json.dumps(line), flush=True)
+        prog.phase("teardown")
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        prog.finish()
+        return
+
+    prog.phase(f"set-up: config {args.config} graph (device set-up kernels), model, pinned inputs")
+    copies = args.copies if args.copies > 0 else DEFAULT_COPIES[args.config]
+    ei, N, desc = workload_device_graph(args.config, copies, dev)
+    E = int(ei.shape[1])
     torch.manual_seed(0)                                   # same weights on every rank
     model = EncodeProcessDecode(STEPS_MP, H, H, H, hidden_size=H, only_processor=True).to(dev)
     params = list(model.parameters())
@@ -368,7 +605,7 @@ def run_b200(args):
         for _ in range(warmup):
             fn()
         barrier()
-        proc.EVENTS = {"edge_bwd": []} if with_events else None
+        proc.EVENTS = {"edge_bwd": [], "edge_fwd": []} if with_events else None
         l0 = proc.LAUNCHES
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
@@ -391,7 +628,7 @@ def run_b200(args):
         step_resident()
         after_replay()
 
-    prog.phase("csr build + eager pass (per-launch events of edge_bwd)")
+    prog.phase("csr build + eager pass (per-launch events of the edge kernels)")
     ms_eager, launches, ev = timed(step_eager, args.steps, args.warmup, with_events=True)
     # (2) the timed region of `value`: the same step replayed from a CUDA graph (no host launch gaps)
     step_fn, e2e_fn, graphed = step_eager, step_e2e, False
@@ -432,21 +669,26 @@ def run_b200(args):
             fwd_fn = fwd_only
     ms_fwd, _, _ = timed(fwd_fn, args.steps, 3)
 
+    line = None
     if rank == 0:
         hbm, tf, which = peaks()
         ms_step = ms / args.steps
         value = world * E / (ms_step * 1e-3)
         durs = [a.elapsed_time(b) for a, b in ev["edge_bwd"]]
         edge_bwd_ms = float(np.mean(durs)) if durs else float("nan")
+        dfw = [a.elapsed_time(b) for a, b in ev["edge_fwd"]]
+        edge_fwd_ms = float(np.mean(dfw)) if dfw else float("nan")
         alg_bytes = E * EDGE_BWD_BYTES_EDGE + N * EDGE_BWD_BYTES_NODE
         ach = alg_bytes / (edge_bwd_ms * 1e-3) / 1e9
         step_bytes = STEPS_MP * (E * BYTES_EDGE_STEP + N * BYTES_NODE_STEP)
         step_flops = STEPS_MP * (E * FLOPS_EDGE_STEP + N * FLOPS_NODE_STEP)
+        traffic, traffic_src = measured_traffic("edge_bwd_kernel", args.config) if copies == DEFAULT_COPIES[args.config] \
+            else (None, "non-default batch")
         line = {
             "metric": METRIC, "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16",
-            "data": "synthetic", "config": workload_config(world, copies),
+            "data": "synthetic", "config": workload_config(world, N, E, desc),
             "e2e": {"value": world * E / (ms_e2e / e2e_steps * 1e-3), "unit": "edges/s",
                     "h2d_bytes_per_step": int(x0_h.numel() + e0_h.numel() + gx_h.numel()) * 4,
                     "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / e2e_steps},
@@ -457,29 +699,70 @@ def run_b200(args):
                              "ms_per_step": ms_fwd / args.steps, "what": "15 blocks forward under no_grad"},
             "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "edge_bwd_kernel", "achieved": ach, "peak": hbm, "unit": "GB/s",
-                         "frac": ach / hbm, "traffic": EDGE_BWD_DRAM_BYTES_NCU if copies == 32 else None,
-                         "traffic_source": "ncu --set full, profiles/r01_ncu_edge_bwd_v6.md (bytes per launch)",
+                         "frac": ach / hbm, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": which,
                          "ms_per_launch": edge_bwd_ms, "launches_timed": len(durs),
                          "timed_in": "eager pass of the same steps (one CUDA event pair per launch) run before the "
                                      "graph-replayed region of `value`",
-                         "algorithmic_bytes_per_launch": alg_bytes},
+                         "algorithmic_bytes_per_launch": alg_bytes,
+                         "edge_fwd_ms_per_launch": edge_fwd_ms},
             "step_roofline": {"hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / hbm,
                               "tensor_frac": step_flops / (ms_step * 1e-3) / 1e12 / tf,
                               "algorithmic_GB_per_step": step_bytes / 1e9, "algorithmic_TFLOP_per_step": step_flops / 1e12,
                               "edge_bwd_share_of_step": edge_bwd_ms * STEPS_MP / ms_step},
+            "kernel_source_hash": kernel_source_hash(),
         }
-        # the GPU numbers exist from here on: a stall in the baseline legs below cannot take them along (the watchdog
-        # prints this line); stderr carries it at once
+        # the GPU numbers exist from here on: a stall in the later legs cannot take them along (the watchdog prints
+        # this line); stderr carries it at once
         prog.partial = line
-        print("[bench] result before the baseline legs: " + json.dumps(line), file=sys.stderr, flush=True)
+        print("[bench] result before the partitioned / baseline legs: " + json.dumps(line), file=sys.stderr, flush=True)
+        if os.environ.get("MGN_BENCH_BREAKDOWN"):       # developer aid: per-kernel device time of one extra step (stderr)
+            names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "edge_wgrad1", "dp_gather", "p_bwd"]
+            proc.EVENTS = {n_: [] for n_ in names}
+            s0, e0_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            step_resident()
+            e0_.record()
+            torch.cuda.synchronize()
+            evs, proc.EVENTS = proc.EVENTS, None
+            tot = 0.0
+            for n_ in names:
+                d = [a.elapsed_time(b) for a, b in evs[n_]]
+                tot += sum(d)
+                print(f"  {n_:12s} n={len(d):3d} mean {1e3 * sum(d) / max(len(d), 1):8.1f} us  total {sum(d):7.3f} ms",
+                      file=sys.stderr)
+            print(f"  kernels {tot:.3f} ms of step {s0.elapsed_time(e0_):.3f} ms", file=sys.stderr)
+
+    # ---- the partitioned large-mesh point (config 5 family) for this world size, as a sub-record
+    if args.config == 2 and not args.no_partitioned:
+        x0_keep = (x0, e0, gx)
+        del step_e2e, fwd_fn, step_fn
+        try:
+            cap_step = None
+        except Exception:
+            pass
+        torch.cuda.empty_cache()
+        try:
+            rec = run_partitioned_point(args, prog, dev, rank, world, grid=args.grid)
+        except Exception as exc:
+            rec = {"unavailable": f"{type(exc).__name__}: {exc}"[:300]}
+            if world > 1:
+                raise
+        if rank == 0:
+            line["partitioned"] = rec
+            prog.partial = line
+        del x0_keep
+
+    if rank == 0:
         if args.cpu_seconds > 0 and world == 1:      # the CPU leg runs at N=1 only (rank 0 would hold N-1 ranks at a barrier)
             prog.phase("cpu_baseline leg (oracle port on the host cores)")
             threads = os.cpu_count() or 1
-            eps, t, e_cpu = cpu_oracle_run(args.cpu_copies, 2, 1, threads)
+            ccopies = cpu_sample_copies(args)
+            ei_c, n_c, what = workload_cpu_graph(args.config, ccopies)
+            eps, t, done = cpu_oracle_run(ei_c, n_c, 2, 1, threads, budget_s=30.0)
             line["cpu_baseline"] = {"value": eps, "unit": "edges/s", "cores": threads, "kind": "port",
-                                    "sample": f"{args.cpu_copies} of {copies} meshes ({e_cpu} edges), 15 steps fwd+bwd, "
-                                              f"fp32 oracle port, median of 2 after 1 warm-up, {t:.2f} s per pass"}
+                                    "sample": f"{what}: N={n_c}, E={ei_c.shape[1]}, 15 steps fwd+bwd, fp32 oracle port, "
+                                              f"median of {done} after 1 warm-up, {t:.2f} s per pass"}
             prog.partial = line
             prog.phase("eager-GPU baseline leg (oracle port's torch ops on this GPU, TF32)")
             try:
@@ -491,22 +774,6 @@ def run_b200(args):
             except Exception as exc:
                 line["cpu_baseline"]["eager_gpu"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
         print(json.dumps(line), flush=True)
-        if os.environ.get("MGN_BENCH_BREAKDOWN"):       # developer aid: per-kernel device time of one extra step (stderr)
-            names = ["pack", "p_fwd", "edge_fwd", "node_fwd", "node_bwd", "node_wgrad1", "edge_bwd", "edge_wgrad1", "dp_gather", "p_bwd"]
-            proc.EVENTS = {n: [] for n in names}
-            s0, e0_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s0.record()
-            step_resident()
-            e0_.record()
-            torch.cuda.synchronize()
-            evs, proc.EVENTS = proc.EVENTS, None
-            tot = 0.0
-            for n in names:
-                d = [a.elapsed_time(b) for a, b in evs[n]]
-                tot += sum(d)
-                print(f"  {n:12s} n={len(d):3d} mean {1e3 * sum(d) / max(len(d), 1):8.1f} us  total {sum(d):7.3f} ms",
-                      file=sys.stderr)
-            print(f"  kernels {tot:.3f} ms of step {s0.elapsed_time(e0_):.3f} ms", file=sys.stderr)
     prog.phase("teardown")
     if world > 1:
         dist.barrier()
@@ -520,8 +787,11 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--copies", type=int, default=32, help="meshes per GPU")
-    ap.add_argument("--cpu-copies", type=int, default=1, help="meshes in the CPU sample")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5], help="BASELINE.json workload (see the header)")
+    ap.add_argument("--copies", type=int, default=0, help="meshes per GPU (0 = the config's own batch: 32 / 16 / 1)")
+    ap.add_argument("--grid", type=int, default=0, help="partitioned point: grid edge length (0 = weak-scaling default)")
+    ap.add_argument("--no-partitioned", action="store_true", help="config 2: skip the partitioned sub-record")
+    ap.add_argument("--cpu-copies", type=int, default=0, help="meshes (config 4: grid edge) in the CPU sample; 0 = default")
     ap.add_argument("--cpu-seconds", type=float, default=1.0, help="0 disables the cpu_baseline leg")
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of a graph replay")
     ap.add_argument("--phase-timeout", type=float, default=240.0,

@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(512, 1) probe_kernel(ProbeArgs p) {
       for (int i = 0; i < p.iters; ++i) {
         tmem_ld32(tmem + lane_off + c0 + 128 * (i & 3), v);
         tmem_ld_wait();
-        sink += v[i & 31];
+        sink += v[0] + v[13] + v[31];
       }
     }
     __syncthreads();
@@ -59,14 +59,14 @@ __global__ void __launch_bounds__(512, 1) probe_kernel(ProbeArgs p) {
     __syncthreads();
     const long long t0 = clock64();
     if (warp < nw) {
-      for (int i = 0; i < p.iters; i += 4) {
-        float a[32], b[32], c[32], d[32];
-        tmem_ld32(tmem + lane_off + c0, a);
-        tmem_ld32(tmem + lane_off + c0 + 128, b);
-        tmem_ld32(tmem + lane_off + c0 + 256, c);
-        tmem_ld32(tmem + lane_off + c0 + 384, d);
+      for (int i = 0; i < p.iters; i += 2) {   // 4 x16 loads = 2 x32-equivalents per trip
+        float a[16], b[16], c[16], d[16];
+        tmem_ld16(tmem + lane_off + c0, a);
+        tmem_ld16(tmem + lane_off + c0 + 16, b);
+        tmem_ld16(tmem + lane_off + c0 + 128, c);
+        tmem_ld16(tmem + lane_off + c0 + 144, d);
         tmem_ld_wait();
-        sink += a[i & 31] + b[i & 31] + c[i & 31] + d[i & 31];
+        sink += a[0] + b[7] + c[9] + d[15];
       }
     }
     __syncthreads();
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(512, 1) probe_kernel(ProbeArgs p) {
       for (int i = 0; i < p.iters; ++i) {
         tmem_ld32(tmem + lane_off + ((warp >> 2) - 1) * 32, v);
         tmem_ld_wait();
-        sink += v[i & 31];
+        sink += v[0] + v[13] + v[31];
       }
     }
     __syncthreads();

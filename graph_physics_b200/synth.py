@@ -52,3 +52,82 @@ def grid_for_nodes(target_nodes: float) -> int:
     """Edge length of the cubic grid whose node count is closest to `target_nodes`."""
     g = max(2, round(target_nodes ** (1.0 / 3.0)))
     return min((g - 1, g, g + 1), key=lambda q: abs(q ** 3 - target_nodes)) if g > 2 else g
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE.json config 3: DeformingPlate-shaped samples (SURVEY.md 8(d)): per sample a thin plate (18 x 18 x 3 nodes)
+# and an obstacle block (7 x 7 x 6 nodes) hovering over it, both Kuhn-split tetrahedral grids; node types NORMAL (0,
+# plate), HANDLE (3, the plate's x = 0 face) and OBSTACLE (1).  The obstacle sits `gap` above the plate so that its
+# bottom nodes come within the world-edge radius (0.03, preprocessing.py:92-96) of plate nodes: ~1-3 % extra edges.
+PLATE_DIMS, OBSTACLE_DIMS = (18, 18, 3), (7, 7, 6)
+NODE_NORMAL, NODE_OBSTACLE, NODE_HANDLE = 0, 1, 3
+
+
+def _grid_points(dims, spacing, origin, gen, jitter=0.2):
+    nx, ny, nz = dims
+    ix, iy, iz = torch.meshgrid(torch.arange(nx), torch.arange(ny), torch.arange(nz), indexing="ij")
+    p = torch.stack([ix.flatten(), iy.flatten(), iz.flatten()], dim=1).double()
+    sp = torch.tensor(spacing, dtype=torch.float64)
+    p = p * sp + torch.tensor(origin, dtype=torch.float64)
+    p = p + (torch.rand(p.shape, generator=gen, dtype=torch.float64) * 2 - 1) * jitter * sp
+    return p
+
+
+def plate_sample(seed: int = 0, gap: float = 0.018):
+    """One config-3 sample on the CPU: (pos [n,3] fp32 = mesh = world positions, cells [T,4] int64, node_type [n]
+    int64).  n = 972 + 294 = 1,266 nodes, T = 6 (17*17*2 + 6*6*5) = 4,548 tetrahedra."""
+    gen = torch.Generator().manual_seed(1234 + seed)
+    psp, osp = (0.025, 0.025, 0.010), (0.020, 0.020, 0.020)
+    plate = _grid_points(PLATE_DIMS, psp, (0.0, 0.0, 0.0), gen)
+    top = psp[2] * (PLATE_DIMS[2] - 1)
+    off = torch.rand(2, generator=gen, dtype=torch.float64) * 0.2          # where over the plate the obstacle hangs
+    obst = _grid_points(OBSTACLE_DIMS, osp, (0.05 + float(off[0]), 0.05 + float(off[1]), top + gap), gen, jitter=0.1)
+    n_p = plate.shape[0]
+    cells = torch.cat([kuhn_grid_cells(*PLATE_DIMS), kuhn_grid_cells(*OBSTACLE_DIMS) + n_p], dim=0)
+    node_type = torch.cat([torch.full((n_p,), NODE_NORMAL), torch.full((obst.shape[0],), NODE_OBSTACLE)]).long()
+    ids = torch.arange(n_p).view(*PLATE_DIMS)
+    node_type[ids[0].reshape(-1)] = NODE_HANDLE
+    return torch.cat([plate, obst]).float(), cells, node_type
+
+
+def config3_batch(copies: int = 16, device="cuda", radius: float = 0.03):
+    """BASELINE.json config 3 (plate.json graph: mesh + world edges, 8-dim raw edge features) as one block-diagonal
+    batch built with the device set-up path the dataset uses (cells_to_faces -> face_to_edge -> add_world_edges per
+    sample -> edge_features + world_pos_features; graphphysics/dataset/preprocessing.py:401-427).
+    Returns dict(edge_index [2,E], num_nodes, edge_attr [E,8], node_type [N], pos [N,3], mesh_edges, world_edges)."""
+    from . import graph as G
+    eis, poss, types = [], [], []
+    n_off = mesh_e = 0
+    for s in range(copies):
+        pos, cells, nt = plate_sample(seed=s, gap=0.012 + 0.014 * ((s * 7) % copies) / max(copies - 1, 1))
+        pos, cells, nt = pos.to(device), cells.to(device), nt.to(device)
+        n = pos.shape[0]
+        ei_mesh = G.face_to_edge(G.cells_to_faces(cells), n)
+        ei = G.add_world_edges(ei_mesh, pos, nt, n, radius=radius, obstacle=NODE_OBSTACLE, normal=NODE_NORMAL)
+        mesh_e += ei_mesh.shape[1]
+        eis.append(ei + n_off)
+        poss.append(pos)
+        types.append(nt)
+        n_off += n
+    ei = torch.cat(eis, dim=1).contiguous()
+    pos = torch.cat(poss)
+    ea = G.world_pos_features(G.edge_features(pos, ei), pos, ei)
+    return {"edge_index": ei, "num_nodes": n_off, "edge_attr": ea, "node_type": torch.cat(types), "pos": pos,
+            "mesh_edges": mesh_e, "world_edges": ei.shape[1] - mesh_e}
+
+
+def config4_graph(grid: int = 47, device="cuda", num_hops: int = 2, masking_ratio: float = 0.4, seed: int = 0):
+    """BASELINE.json config 4: grid^3 Kuhn tetrahedral mesh (47^3 = 103,823 nodes), 2-hop adjacency
+    (compute_k_hop_edge_index, graphphysics/utils/torch_graph.py:16-53) and the MeshMask sub-graph of the kept nodes
+    (get_masked_indexes + build_masked_graph, torch_graph.py:285-302, utils/meshmask.py:9-70; masking_ratio 0.4 as
+    tests/graphphysics/dataset/test_h5dataset.py:34, torch.manual_seed(seed) randperm).
+    Returns dict(full=(edge_index, N), masked=(edge_index, N_kept), selected)."""
+    from . import graph as G
+    from .dataset import masked_indexes
+    n = grid ** 3
+    ei1 = kuhn_grid_edges(grid, grid, grid, device=device)
+    eik = G.compute_k_hop_edge_index(ei1, num_hops, n)
+    gen = torch.Generator().manual_seed(seed)
+    sel = masked_indexes(n, masking_ratio, generator=gen).to(device)
+    ei_m, _, _ = G.filter_edges(eik, sel)
+    return {"full": (eik, n), "masked": (ei_m.contiguous(), int(sel.numel())), "selected": sel, "one_hop_edges": ei1.shape[1]}

@@ -18,7 +18,7 @@ from oracle.synth import processor_inputs
 
 pytestmark = pytest.mark.gpu
 TOL_STEP, TOL_15 = 1e-3, 5e-3
-TOL_GRAD_15 = 0.35
+TOL_GRAD_15 = 0.08
 
 
 def _load(model, params):
