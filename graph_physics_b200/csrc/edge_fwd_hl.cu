@@ -33,6 +33,9 @@ struct EdgeHLParams {
   const int32_t* senders;
   const int32_t* receivers;
   float* aggr;              // [N,128] fp32, zero on entry
+  float* carry;             // [ceil(E/32),128] fp32: partial sums of runs that continue from an earlier 32-row slot
+                            // (deterministic aggregation, aggr_fixup_kernel below)
+  float inv_sqrt_d;         // RMSNorm: d^-1/2 of the TRUE hidden size (zero-padded narrower models, ops.py)
   const __half* W;          // We, W2, W3, W4 tiles
   const float* b2;
   const float* b3;
@@ -126,15 +129,17 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
   };
   // indices, requested one tile ahead: this thread's row (epilogue mapping) -> receiver; coalesced mapping (lane j < 8
   // of warp w stands for tile row 8w + j) -> sender
-  struct Idx { int rcv, snd_c; bool ok; };
+  struct Idx { int rcv, snd_c, prev; bool ok; };      // prev: receiver of the row before this warp's 32-row slot (-1: none)
   auto load_idx = [&](int k) -> Idx {
-    Idx ix{0, -1, false};
+    Idx ix{0, -1, -1, false};
     if (k >= K) return ix;
     const long long r0 = tile_of(k) * TILE_ROWS;
     if (r0 + m.row < p.E) {
       ix.rcv = __ldg(p.receivers + r0 + m.row);
       ix.ok = true;
     }
+    const long long s0 = r0 + m.lq * 32;
+    if (s0 > 0 && s0 < p.E) ix.prev = __ldg(p.receivers + s0 - 1);
     const long long g = r0 + m.warp * 8 + (m.lane & 7);
     if (g < p.E) ix.snd_c = __ldg(p.senders + g);
     return ix;
@@ -277,7 +282,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
         ss = (q4[0] + q4[1]) + (q4[2] + q4[3]);
       }
       fetch_pj();                 // next tile's P_j chunk of this thread's row; the same bytes then take the new image
-      const float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+      const float inv = 1.0f / (sqrtf(ss) * p.inv_sqrt_d + RMS_EPS);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         y[4 * j + 0] = sc[j].x * (y[4 * j + 0] * inv);
@@ -330,6 +335,8 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     tl.stamp();   // 6 stores + next product 1 issued
     // ---- next tile's indices / P rows, then the segmented sum of y over the receivers (sorted: runs of lanes)
     const int key = rvalid ? cur.rcv : -1 - m.lane;     // rows past the end never join a run
+    const int prev_rcv = cur.prev;
+    const long long slot = tile * 4 + m.lq;             // this warp's 32-row slot
     cur = nxt;
     if (has_next) load_pi(cur);
     nxt = load_idx(k + 2);
@@ -348,11 +355,18 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
       }
       tl.stamp();   // 8 scan done
       const int dn = __shfl_down_sync(0xffffffffu, key, 1);
-      if (rvalid && (m.lane == 31 || dn != key)) {       // last lane of a run holds its sum
-        float* dst = p.aggr + (long long)key * H + m.c0;
+      const int key0 = __shfl_sync(0xffffffffu, key, 0);
+      if (rvalid && (m.lane == 31 || dn != key)) {       // last lane of a run holds its sum over this slot
+        {
+          // deterministic: a run that starts in this slot owns its node's row of aggr (plain store: receivers are
+          // sorted, so no other slot starts a run of that node); a run that continues from an earlier slot leaves
+          // its partial in carry[slot], added to aggr in slot order by aggr_fixup_kernel after this kernel
+          const bool head = key == key0 && prev_rcv == key;
+          float* dst = head ? p.carry + slot * H + m.c0 : p.aggr + (long long)key * H + m.c0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          red_add_f4_hint(dst + 4 * j, make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]), pol_keep);
+          for (int j = 0; j < 8; ++j)
+            st_f4_hint(dst + 4 * j, make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]), pol_keep);
+        }
       }
     }
     tl.stamp();   // 9 aggregation issued
@@ -365,20 +379,72 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
   if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Deterministic aggregation, second half.  The edge kernels cut the receiver-sorted edge list into slots of
+// `slot_rows` rows (32: one warp's rows in edge_fwd_hl; 8: one warp's rows in mlp_fwd_kernel<true>).  A run of equal
+// receivers that STARTS in a slot is stored to aggr[node] by that slot; the partial sums of its continuation in later
+// slots sit in carry[slot].  Here one warp per slot finds the first continuation slot of each such run and adds the
+// chain carry[s], carry[s+1], ... to aggr[node] in slot order: one writer per node, fixed order, no atomics.
+struct AggrFixupParams {
+  long long E;
+  int slot_rows;
+  const int32_t* receivers;
+  const float* carry;
+  float* aggr;
+};
+
+__global__ void __launch_bounds__(256) aggr_fixup_kernel(const AggrFixupParams p) {
+  pdl_wait();
+  pdl_launch();
+  const int lane = threadIdx.x & 31;
+  const long long nslots = (p.E + p.slot_rows - 1) / p.slot_rows;
+  const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long s = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1; s < nslots; s += warps) {
+    const long long r0 = s * p.slot_rows;
+    const int k = __ldg(p.receivers + r0);
+    if (__ldg(p.receivers + r0 - 1) != k) continue;                       // this slot starts a new run: nothing carried
+    const long long q0 = r0 - p.slot_rows;                                 // previous slot: same chain if it is a
+    if (__ldg(p.receivers + q0) == k && q0 > 0 && __ldg(p.receivers + q0 - 1) == k) continue;   // continuation too
+    float4 acc = __ldg(reinterpret_cast<const float4*>(p.carry + s * H) + lane);
+    for (long long t = s + 1; t < nslots && __ldg(p.receivers + t * p.slot_rows) == k; ++t) {
+      const float4 c = __ldg(reinterpret_cast<const float4*>(p.carry + t * H) + lane);
+      acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
+    }
+    float4* dst = reinterpret_cast<float4*>(p.aggr + (long long)k * H) + lane;
+    float4 o = *dst;
+    o.x += acc.x; o.y += acc.y; o.z += acc.z; o.w += acc.w;
+    *dst = o;
+  }
+}
+
+int mgn_launch_aggr_fixup(int64_t E, int slot_rows, const int32_t* receivers, const float* carry, float* aggr,
+                          cudaStream_t stream) {
+  const int64_t nslots = ceil_div64(E, slot_rows);
+  if (nslots <= 1) return MGN_OK;
+  AggrFixupParams p{E, slot_rows, receivers, carry, aggr};
+  const int grid = (int)std::min<int64_t>(ceil_div64(nslots, 8), (int64_t)mgn_num_sms() * 8);
+  MGN_CUDA(mgn_launch(aggr_fixup_kernel, grid, 256, 0, stream, p));
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
 static constexpr int EDGE_HL_SMEM = 7 * 32768 + TAIL_BYTES;
 
 // Steps 1..K-1 of the processor loop with the edge stream as image + remainder (see the header of this file).
 // hi_out / lo_out (both or neither) receive the images of e_out; e_out (fp32 rows, CSR order) is optional.
+// carry: [ceil(E/32),128] fp32 workspace of the deterministic aggregation (plain stores + aggr_fixup_kernel: no
+// atomics).  norm_dim: the model's true hidden size (RMSNorm divides
+// by sqrt(norm_dim); 128 unless the caller zero-pads a narrower model into the 128-wide kernels).
 // Replaces the same reference lines as mgn_edge_fwd (graphphysics/models/layers.py:687-698).
 extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
                                float* e_out, const void* P, const int32_t* senders, const int32_t* receivers,
                                float* aggr, const void* packed, const float* b2, const float* b3, const float* b4,
-                               const float* scale, void* stream_) {
+                               const float* scale, float* carry, int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd_hl: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
   if (E == 0) return MGN_OK;
-  MGN_CHECK_ARG(hi_in && lo_in && P && senders && receivers && packed && b2 && b3 && b4 && scale,
+  MGN_CHECK_ARG(hi_in && lo_in && P && senders && receivers && packed && b2 && b3 && b4 && scale && carry,
                 "edge_fwd_hl: null pointer");
   MGN_CHECK_ARG((hi_out == nullptr) == (lo_out == nullptr), "edge_fwd_hl: hi_out and lo_out go together");
   MGN_CHECK_ARG(hi_out != hi_in && lo_out != lo_in, "edge_fwd_hl: in-place not supported");
@@ -388,6 +454,8 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   p.P = (const __half*)P; p.senders = senders; p.receivers = receivers; p.aggr = aggr;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "edge_fwd_hl: norm_dim must be in 1..128");
+  p.carry = carry; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
@@ -398,5 +466,5 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
   MGN_CUDA(mgn_launch(edge_fwd_hl_kernel, grid, NT, EDGE_HL_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
-  return MGN_OK;
+  return mgn_launch_aggr_fixup(E, 32, receivers, carry, aggr, stream);
 }

@@ -37,7 +37,8 @@ __device__ __forceinline__ void load_w_slot(uint8_t* slot, const __half* W, int 
 // acc = z - bias (TMEM), gtile row holds the upstream gradient g (fp16) and is overwritten with fp16(dz).
 // Returns this warp's column sum (over its 32 rows) of g*z*inv for column c0+lane (= dL/dscale part).
 __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb)[8], const float4 (&sc)[8],
-                                               uint8_t* gtile, float* red, const Map& m) {
+                                               uint8_t* gtile, float* red, const Map& m, float inv_sqrt_d,
+                                               float norm_d) {
   float z[32], g[32];
   tmem_ld32(taddr, z);
   load_row_chunk_f16(gtile, 128, m.row, m.c0, g);
@@ -56,9 +57,9 @@ __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb
   }
   ss = row_sum4(ss, red, m);
   dot = row_sum4(dot, red, m);
-  const float r = sqrtf(ss) * INV_SQRT_H;
+  const float r = sqrtf(ss) * inv_sqrt_d;
   const float inv = 1.0f / (r + RMS_EPS);
-  const float k = r > 0.f ? dot * inv * inv / ((float)H * r) : 0.f;
+  const float k = r > 0.f ? dot * inv * inv / (norm_d * r) : 0.f;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
@@ -71,6 +72,21 @@ __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb
   }
   store_row_chunk_f16(gtile, 128, m.row, m.c0, z);
   return warp_colsum32(g, m.lane);
+}
+
+// ReLU backward in place with the store held back: the dgrad product (accumulator) is complete, the weight-gradient
+// product issued right behind it may still be READING `tile` (h) as its operand -- so the accumulator and h are loaded
+// and masked first, and `tile` is only overwritten once `bar_wg` (the weight-gradient product's commit) has fired
+__device__ __forceinline__ void epi_relu_mask_after(uint32_t taddr, uint8_t* tile, const Map& m, uint64_t* bar_wg,
+                                                    uint32_t parity) {
+  float v[32], h[32];
+  tmem_ld32(taddr, v);
+  load_row_chunk_f16(tile, 128, m.row, m.c0, h);
+  tmem_ld_wait();
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = h[j] > 0.f ? v[j] : 0.f;
+  mbar_wait(bar_wg, parity);
+  store_row_chunk_f16(tile, 128, m.row, m.c0, v);
 }
 
 // ===================================================================================== edge
@@ -95,6 +111,7 @@ struct EdgeBwdParams {
   long long* dbg;
   int dbg_cap;
   int dbg_skip;             // developer experiments only (MGN_DEBUG_SKIP): bit mask of memory operations to leave out
+  float inv_sqrt_d, norm_d; // RMSNorm: true hidden size d and d^-1/2 (zero-padded narrower models)
 };
 
 // FAST = the processor loop's case (upstream g_e tile contiguous: no rowmap, g_eout given, e images given): the operand
@@ -117,6 +134,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_wA = tail->bar[0];
   uint64_t& bar_wB = tail->bar[1];
   uint64_t& bar_mma = tail->bar[2];
+  uint64_t& bar_wg = tail->bar[3];      // weight-gradient products (committed apart from the dgrad product before them)
   uint64_t& bar_e = tail->bar[4];
   uint64_t& bar_g = tail->bar[5];
   uint64_t& bar_g2 = tail->bar[6];
@@ -128,6 +146,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_wA, 1);
     mbar_init(&bar_wB, 1);
     mbar_init(&bar_mma, 1);
+    mbar_init(&bar_wg, 1);
     mbar_init(&bar_e, 1);
     mbar_init(&bar_g, 1);
     mbar_init(&bar_g2, 1);
@@ -147,7 +166,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
                  uH2 = smem_u32(sH2), uH3 = smem_u32(sH3), uG = smem_u32(sG);
   const uint64_t pol_stream = policy_evict_first();
   const uint64_t pol_keep = policy_evict_last();
-  uint32_t phase = 0;
+  uint32_t phase = 0, phase_wg = 0;
   float dsc = 0.f;
   float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
   if (m.tid == 0) {
@@ -403,7 +422,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       load_vec32(p.b4, m.c0, bb);
       load_vec32(p.scale, m.c0, sc);
       mma_wait();
-      dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);
+      dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m, p.inv_sqrt_d, p.norm_d);
       tile_ready();
     }
     tl.stamp();   // 4 R4 + norm done
@@ -411,8 +430,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uG, 128, 0, uW4, 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
@@ -422,7 +442,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         load_w_slot(sWA, p.W, 0, &bar_wA);                 // W4 is done: We -> A for D1 (and the next tile's R1)
       }
     }
-    epi_relu_mask_q(tm_W + qoff, sH3, m);
+    epi_relu_mask_after(tm_W + qoff, sH3, m, &bar_wg, phase_wg);
+    phase_wg ^= 1;
     tile_ready();
     // ---- D3
     if (m.tid == 0) {
@@ -431,22 +452,25 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       if (FAST && has_next) issue_e16(tile + gridDim.x);
       fence_after_sync();
       umma_tile(tm_W, uH3, 128, 0, uW3, 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     if (!FAST && has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (!FAST && m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
-    epi_relu_mask_q(tm_W + qoff, sH2, m);
+    epi_relu_mask_after(tm_W + qoff, sH2, m, &bar_wg, phase_wg);
+    phase_wg ^= 1;
     tile_ready();
     // ---- D2
     if (m.tid == 0) {
       if (!FAST) mbar_wait(&bar_wB, 0);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     if (!FAST && has_next) {
       g_store(gq, 0);
@@ -454,7 +478,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
-    epi_relu_mask_q(tm_W + qoff, sH1, m);    // sH1 <- dz1
+    epi_relu_mask_after(tm_W + qoff, sH1, m, &bar_wg, phase_wg);    // sH1 <- dz1
+    phase_wg ^= 1;
     tile_ready();
     tl.stamp();   // 5 D4..D2 done
     // upstream rows of this tile for the residual add, straight into the (now dead) sH2 + sH3 as a linear fp32 tile
@@ -568,6 +593,7 @@ struct NodeBwdParams {
   const float* scale;
   float* grad;
   int no_norm;              // the block has no RMSNorm (decoder): dz4 = g, no scale gradient
+  float inv_sqrt_d, norm_d; // RMSNorm: true hidden size d and d^-1/2
 };
 
 __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
@@ -583,6 +609,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   uint64_t* bar_w = &tail->bar[0];
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_h = tail->bar[3];
+  uint64_t& bar_wg = tail->bar[4];      // weight-gradient products (committed apart from the dgrad product before them)
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
   if (m.tid == 0) {
@@ -590,6 +617,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     mbar_init(&bar_w[1], 1);
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_h, 1);
+    mbar_init(&bar_wg, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -616,7 +644,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     }
   };
   auto wait_load = [&](uint32_t qq) { mbar_wait(&bar_w[qq & 1], (qq >> 1) & 1); };
-  uint32_t phase = 0;
+  uint32_t phase = 0, phase_wg = 0;
   auto mma_wait = [&]() {
     mbar_wait(&bar_mma, phase);
     phase ^= 1;
@@ -659,46 +687,52 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       load_vec32(p.b4, m.c0, bb);
       load_vec32(p.scale, m.c0, sc);
       mma_wait();
-      if (!p.no_norm) dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m);      // else sG already holds dz4 = g
+      if (!p.no_norm) dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m, p.inv_sqrt_d, p.norm_d);      // else sG already holds dz4 = g
       tile_ready();
     }
     // ---- D4
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uG, 128, 0, uW[q0 & 1], 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 2);
-    epi_relu_mask_q(tm_W + qoff, sH3, m);
+    epi_relu_mask_after(tm_W + qoff, sH3, m, &bar_wg, phase_wg);
+    phase_wg ^= 1;
     tile_ready();
     // ---- D3
     if (m.tid == 0) {
       wait_load(q0 + 1);
       fence_after_sync();
       umma_tile(tm_W, uH3, 128, 0, uW[(q0 + 1) & 1], 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 3);
-    epi_relu_mask_q(tm_W + qoff, sH2, m);
+    epi_relu_mask_after(tm_W + qoff, sH2, m, &bar_wg, phase_wg);
+    phase_wg ^= 1;
     tile_ready();
     // ---- D2
     if (m.tid == 0) {
       wait_load(q0 + 2);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uW[(q0 + 2) & 1], 128, 1, 0, 128, 8, 0);
-      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
       mma_commit(&bar_mma);
+      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_wg);
     }
     tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 4);
-    epi_relu_mask_q(tm_W + qoff, sH1, m);     // sH1 <- dz1'
+    epi_relu_mask_after(tm_W + qoff, sH1, m, &bar_wg, phase_wg);     // sH1 <- dz1'
+    phase_wg ^= 1;
     tile_ready();
     // ---- D1a: g_x = g_xout + dz1' W1'[:, :128]
     if (m.tid == 0) {
@@ -1109,9 +1143,10 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
                             const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
                             const int32_t* receivers, float* g_e, void* dz16_out, const void* packed,
                             const float* b2, const float* b3, const float* b4, const float* scale,
-                            float* grad_block, void* stream_) {
+                            float* grad_block, int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0, "edge_bwd: bad sizes");
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "edge_bwd: norm_dim must be in 1..128");
   if (E == 0) return MGN_OK;
   MGN_CHECK_ARG((e_in || e16) && g_aggr && P && senders && receivers && g_e && dz16_out && packed && b2 && b3 && b4 &&
                     scale && grad_block, "edge_bwd: null pointer");
@@ -1120,6 +1155,7 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
   p.senders = senders; p.receivers = receivers; p.g_e = g_e; p.dz16_out = (__half*)dz16_out;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale; p.grad = grad_block;
+  p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static const int dbg_skip = getenv("MGN_DEBUG_SKIP") ? atoi(getenv("MGN_DEBUG_SKIP")) : 0;
   p.dbg_skip = dbg_skip;
@@ -1143,7 +1179,7 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
 // flags bit 0: the block has no RMSNorm (see mgn_node_fwd2)
 extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                              float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                             const float* scale, float* grad_block, int flags, void* stream_) {
+                             const float* scale, float* grad_block, int flags, int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && g_xout && h1 && h2 && h3 && g_x && g_aggr && dz1 && packed && b4 && scale && grad_block,
                 "node_bwd: bad args");
@@ -1152,6 +1188,8 @@ extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, con
   p.g_x = g_x; p.g_aggr = g_aggr; p.dz1 = (__half*)dz1;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
   p.b4 = b4; p.scale = scale; p.grad = grad_block; p.no_norm = flags & 1;
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_bwd: norm_dim must be in 1..128");
+  p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(node_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_BWD_SMEM));
@@ -1166,7 +1204,7 @@ extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, con
 extern "C" int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                             float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
                             const float* scale, float* grad_block, void* stream_) {
-  return mgn_node_bwd2(N, g_xout, h1, h2, h3, g_x, g_aggr, dz1, packed, b4, scale, grad_block, 0, stream_);
+  return mgn_node_bwd2(N, g_xout, h1, h2, h3, g_x, g_aggr, dz1, packed, b4, scale, grad_block, 0, H, stream_);
 }
 
 // Backward of the gathers x[col], x[row]: dP [N,256] fp16 = [sum of dz1 over received edges | over sent edges] from

@@ -13,6 +13,7 @@
 // streams, RMSNorm and the segmented sum are fp32.
 #define MGN_FILE_ID 1
 #include "mlp_v2.cuh"
+#include "mlp_fwd_abi.cuh"
 
 using namespace mgn;
 
@@ -26,7 +27,10 @@ struct FwdParams {
   const __half* P;            // edge: [N,256] fp16 (P_i + b1 | P_j)
   const int32_t* senders;     // edge, CSR order
   const int32_t* receivers;   // edge, CSR order
-  float* aggr;                // edge: [N,128] fp32, zero on entry, receives red.add
+  float* aggr;                // edge: [N,128] fp32, zero on entry
+  float* carry;               // edge: [ceil(E/8),128] fp32 (deterministic aggregation: edge_fwd_hl.cu
+                              // aggr_fixup_kernel, slots of 8 rows = one warp's rows here)
+  float inv_sqrt_d;           // RMSNorm: d^-1/2 of the TRUE hidden size (zero-padded narrower models)
   const __half* W;            // packed fp16 weight tiles
   const float* b1;            // node only
   const float* b2;
@@ -118,11 +122,13 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
   const uint64_t pol_keep = policy_evict_last();      // per-node arrays gathered by every edge
   // Index registers run one tile ahead (the loads for tile i+1 are issued during tile i), so no
   // thread waits on an index before it can issue its tile's row loads.
-  struct Idx { int rcv_o, snd_o, dst_c, rcv_c, snd_c; };
+  struct Idx { int rcv_o, snd_o, dst_c, rcv_c, snd_c, prev_c; };   // prev_c: receiver of the row before this warp's 8 rows
   auto load_idx = [&](long long tile_) -> Idx {
-    Idx ix{0, 0, -1, -1, -1};
+    Idx ix{0, 0, -1, -1, -1, -1};
     if (tile_ >= num_tiles) return ix;
     const long long r0 = tile_ * TILE_ROWS;
+    const long long s0 = r0 + m.warp * 8;
+    if (EDGE && s0 > 0 && s0 < p.M) ix.prev_c = __ldg(p.receivers + s0 - 1);
     if (EDGE && r0 + m.row < p.M) {
       ix.rcv_o = __ldg(p.receivers + r0 + m.row);
       ix.snd_o = __ldg(p.senders + r0 + m.row);
@@ -154,6 +160,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     const bool rvalid = grow < p.M;
     const Idx cur = nxt;
     const int rcv_o = cur.rcv_o, snd_o = cur.snd_o, dst_c = cur.dst_c, rcv_c = cur.rcv_c;
+    const int cur_idx_prev = cur.prev_c;
 
     // P_j[sender] rows (a true gather): asynchronous copies into the idle staging area, half a warp per 256-byte
     // row; they land while the operand tile is loaded and the layer-1 product runs.  P_i[receiver] rows are read by
@@ -328,7 +335,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       float4 sc[8];
       load_vec32(p.scale, m.c0, sc);
       ss = row_sum4(ss, tail->red, m);
-      float inv = 1.0f / (sqrtf(ss) * INV_SQRT_H + RMS_EPS);
+      float inv = 1.0f / (sqrtf(ss) * p.inv_sqrt_d + RMS_EPS);
       if (!EDGE && p.no_norm) {
         inv = 1.0f;
 #pragma unroll
@@ -349,7 +356,19 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
     tl.stamp();   // 9 norm + staging done
     {
       int cur = -1;
+      bool first_run = false;
       float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int prev_c = cur_idx_prev;
+      // a run of equal receivers inside this warp's 8 rows: the run that continues from an earlier 8-row slot leaves
+      // its partial in carry[slot], every other run stores its sum to its node's row of aggr (aggr_fixup_kernel adds
+      // the carries in slot order: deterministic, no atomics)
+      auto flush_run = [&](int node, const float4& v, bool first) {
+        if (first && prev_c == node) {
+          st_f4_hint(p.carry + (tile * 16 + m.warp) * H + 4 * m.lane, v, pol_keep);
+        } else {
+          st_f4_hint(p.aggr + (long long)node * H + 4 * m.lane, v, pol_keep);
+        }
+      };
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float4 y = *reinterpret_cast<const float4*>(stage + stage_off(m.warp * 8 + i, 4 * m.lane));
@@ -378,7 +397,8 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
           }
           if (EDGE) {
             if (rc != cur) {
-              if (cur >= 0) red_add_f4_hint(p.aggr + (long long)cur * H + 4 * m.lane, sum, pol_keep);
+              if (cur >= 0) flush_run(cur, sum, first_run);
+              first_run = (i == 0);
               cur = rc;
               sum = y;
             } else {
@@ -387,7 +407,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
           }
         }
       }
-      if (EDGE && cur >= 0) red_add_f4_hint(p.aggr + (long long)cur * H + 4 * m.lane, sum, pol_keep);
+      if (EDGE && cur >= 0) flush_run(cur, sum, first_run);
     }
     __syncthreads();      // staging / operand tile free for the next tile
     tl.stamp();   // 10 output done
@@ -584,6 +604,7 @@ static constexpr int P_FWD_SMEM = 3 * 32768 + 128 * 528 + TAIL_BYTES;
 
 // GraphNetBlock edge update + aggregation (layers.py:687-698).  e_in/e_out [E,128] fp32 in
 // the caller's edge order when rowmap (= CSR perm) is given, else already in CSR order.
+// carry ([ceil(E/8),128] fp32 workspace or NULL) and norm_dim: as in mgn_edge_fwd_hl (edge_fwd_hl.cu).
 // mgn_edge_fwd2 = mgn_edge_fwd plus e16lo_next (tile images of e_out - fp16(e_out), the second half of the image +
 // remainder form of the residual stream that mgn_edge_fwd_hl consumes); with both images requested e_out may be NULL.
 extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
@@ -591,12 +612,13 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
                              const void* packed, const float* b2, const float* b3, const float* b4,
                              const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
                              const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order,
-                             void* stream_) {
+                             float* carry, int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
   MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
   if (E == 0) return MGN_OK;
-  MGN_CHECK_ARG(e_in && P && senders && receivers && packed && b2 && b3 && b4 && scale, "edge_fwd: null pointer");
+  MGN_CHECK_ARG(e_in && P && senders && receivers && packed && b2 && b3 && b4 && scale && carry,
+                "edge_fwd: null pointer");
   MGN_CHECK_ARG(e_out || (e16_next && e16lo_next), "edge_fwd: e_out may be null only if both output images are given");
   MGN_CHECK_ARG(!e16lo_next || e16_next, "edge_fwd: e16lo_next needs e16_next");
   MGN_CHECK_ARG(e_in != e_out, "edge_fwd: in-place not supported");
@@ -609,6 +631,8 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
   p.e16_out = (__half*)e16_out; p.e16_in = (const __half*)e16_in; p.e16_next = (__half*)e16_next;
   p.e16lo_next = (__half*)e16lo_next;
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "edge_fwd: norm_dim must be in 1..128");
+  p.carry = carry; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
@@ -619,17 +643,7 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
   MGN_CUDA(mgn_launch(mlp_fwd_kernel<true>, grid, NT, EDGE_FWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
-  return MGN_OK;
-}
-
-extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
-                            const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
-                            const void* packed, const float* b2, const float* b3, const float* b4,
-                            const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                            const void* e16_in, void* e16_next, int out_in_csr_order, void* stream_) {
-  MGN_CHECK_ARG(E == 0 || e_out, "edge_fwd: null pointer");
-  return mgn_edge_fwd2(E, N, e_in, rowmap, e_out, P, senders, receivers, aggr, packed, b2, b3, b4, scale, save_h1,
-                       save_h2, save_h3, e16_out, e16_in, e16_next, nullptr, out_in_csr_order, stream_);
+  return mgn_launch_aggr_fixup(E, 8, receivers, carry, aggr, stream);
 }
 
 // GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).
@@ -637,7 +651,7 @@ extern "C" int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32
 extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                              const float* b1, const float* b2, const float* b3, const float* b4,
                              const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags,
-                             void* stream_) {
+                             int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && x && aggr && x_out && packed && b1 && b2 && b3 && b4 && scale, "node_fwd: bad args");
   MGN_CHECK_ARG(x != x_out, "node_fwd: in-place not supported");
@@ -649,6 +663,8 @@ extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float
   p.b1 = b1; p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
   p.no_norm = flags & 1;
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_fwd: norm_dim must be in 1..128");
+  p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
@@ -664,7 +680,7 @@ extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float
 extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                             const float* b1, const float* b2, const float* b3, const float* b4,
                             const float* scale, void* save_h1, void* save_h2, void* save_h3, void* stream_) {
-  return mgn_node_fwd2(N, x, aggr, x_out, packed, b1, b2, b3, b4, scale, save_h1, save_h2, save_h3, 0, stream_);
+  return mgn_node_fwd2(N, x, aggr, x_out, packed, b1, b2, b3, b4, scale, save_h1, save_h2, save_h3, 0, H, stream_);
 }
 
 // per-node layer-1 partial products of the edge block: P = [x W_i^T + b1 | x W_j^T] (fp16)

@@ -69,6 +69,7 @@ class PartitionEngine:
         self.lo_bufs = [ops.e16_image(self.E, dev) for _ in range(min(K - 1, 2))] if self.hl else None
         self.aggrs, self.Ps, self.saves, self.e16s = [], [], [], []
         self.img = None
+        self.carry = ops.carry_buffer(self.E, 8, dev) if (ops.DETERMINISTIC and self.E > 0) else None
         if not self.need_grad:
             self.P = torch.empty((part.num_ext, 2 * H), dtype=torch.float16, device=dev)
             self.aggr = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
@@ -106,12 +107,12 @@ class PartitionEngine:
             if self.hl and k > 0:
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, self.lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers,
                        n_ext, self.packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out,
-                       aggr=aggr)
+                       aggr=aggr, carry=self.carry)
             else:
                 _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
                        b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
                        e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
-                       write_rows=not (self.hl and e_out is None))
+                       write_rows=not (self.hl and e_out is None), carry=self.carry)
             if ng:
                 self.e16s.append(self.img)
             self.img = img_next

@@ -116,13 +116,53 @@ class Normalizer(nn.Module):
                 "_acc_sum": self._acc_sum, "_acc_sum_squared": self._acc_sum_squared, "name": self.name}
 
 
+KERNEL_H, KERNEL_LAYERS = 128, 4      # the shape the sm_100a kernels are built for
+
+
+def _mlp_as_kernel_shape(mlp: nn.Sequential, in_blocks: int, hidden: int, nb_of_layers: int):
+    """The 9 tensors (4 x weight, bias; scale) of a `build_mlp(in_blocks * hidden, hidden, hidden, nb_of_layers)` at
+    the kernels' shape (hidden 128, four layers), built with differentiable torch ops so that autograd hands the
+    gradients back to the module's own parameters:
+      * hidden < 128: every matrix / vector is zero-padded; each `hidden`-wide column block of the first layer goes to
+        the start of its own 128-wide block ([e | x_i | x_j] and [x | aggr] keep their block structure).  Padded
+        latent columns stay exactly zero (zero rows, zero bias, zero scale), and RMSNorm divides by sqrt(hidden)
+        (the kernels' `norm_dim`);
+      * fewer than four layers: identity layers with zero bias are inserted before the last layer -- after a ReLU the
+        activations are >= 0, so relu(I h + 0) = h exactly, forward and backward."""
+    lin = [mlp[2 * i] for i in range(nb_of_layers)]
+    norm = mlp[2 * nb_of_layers - 1]
+    pad = KERNEL_H - hidden
+    F = torch.nn.functional
+
+    def pad_sq(w):          # [hidden, hidden] -> [128, 128]
+        return F.pad(w, (0, pad, 0, pad)) if pad else w
+
+    def pad_vec(v):
+        return F.pad(v, (0, pad)) if pad else v
+    w1 = lin[0].weight
+    if pad:
+        w1 = torch.cat([F.pad(w1[:, j * hidden:(j + 1) * hidden], (0, pad, 0, pad)) for j in range(in_blocks)], dim=1)
+    out = [w1, pad_vec(lin[0].bias)]
+    middles = [(pad_sq(l.weight), pad_vec(l.bias)) for l in lin[1:-1]]
+    while len(middles) < KERNEL_LAYERS - 2:
+        eye = torch.eye(KERNEL_H, dtype=w1.dtype, device=w1.device)
+        middles.append((eye, torch.zeros(KERNEL_H, dtype=w1.dtype, device=w1.device)))
+    for w, b in middles:
+        out += [w, b]
+    out += [pad_sq(lin[-1].weight), pad_vec(lin[-1].bias), pad_vec(norm.scale)]
+    return out
+
+
 def block_param_list(block: "GraphNetBlock"):
-    """The 18 parameters of a block in ops.GRAD_LAYOUT (= state-dict) order."""
+    """The 18 parameters of a block in ops.GRAD_LAYOUT (= state-dict) order, at the kernels' shape."""
     eb, nb = block.edge_block, block.node_block
-    return [eb[0].weight, eb[0].bias, eb[2].weight, eb[2].bias, eb[4].weight, eb[4].bias, eb[6].weight,
-            eb[6].bias, eb[7].scale,
-            nb[0].weight, nb[0].bias, nb[2].weight, nb[2].bias, nb[4].weight, nb[4].bias, nb[6].weight,
-            nb[6].bias, nb[7].scale]
+    if block.hidden_size == KERNEL_H and block.nb_of_layers == KERNEL_LAYERS:
+        return [eb[0].weight, eb[0].bias, eb[2].weight, eb[2].bias, eb[4].weight, eb[4].bias, eb[6].weight,
+                eb[6].bias, eb[7].scale,
+                nb[0].weight, nb[0].bias, nb[2].weight, nb[2].bias, nb[4].weight, nb[4].bias, nb[6].weight,
+                nb[6].bias, nb[7].scale]
+    return (_mlp_as_kernel_shape(eb, 3, block.hidden_size, block.nb_of_layers) +
+            _mlp_as_kernel_shape(nb, 2, block.hidden_size, block.nb_of_layers))
 
 
 class GraphNetBlock(nn.Module):
@@ -139,10 +179,11 @@ class GraphNetBlock(nn.Module):
         self.node_block = build_mlp(2 * hidden_size, hidden_size, hidden_size, nb_of_layers, layer_norm)
 
     def check_supported(self):
-        if self.hidden_size != 128 or self.nb_of_layers != 4 or not self.layer_norm:
-            raise ValueError("graph_physics_b200.GraphNetBlock: the sm_100a kernels are built for hidden_size=128, "
-                             "nb_of_layers=4, layer_norm=True (the configuration EncodeProcessDecode uses); "
-                             "there is no eager fallback")
+        """hidden_size <= 128 and nb_of_layers in 2..4 run on the 128-wide four-layer kernels (narrower / shallower
+        blocks are zero-padded / get identity layers, `block_param_list`); layer_norm=False has no kernel."""
+        if not (0 < self.hidden_size <= KERNEL_H) or not (2 <= self.nb_of_layers <= KERNEL_LAYERS) or not self.layer_norm:
+            raise ValueError("graph_physics_b200.GraphNetBlock: the sm_100a kernels cover hidden_size <= 128, "
+                             "nb_of_layers in {2, 3, 4}, layer_norm=True; there is no eager fallback")
 
     def forward(self, x, edge_index, edge_attr, size=None):
         self.check_supported()

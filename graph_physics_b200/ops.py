@@ -51,12 +51,24 @@ def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
     return out
 
 
+# The sum at the receivers is deterministic and atomics-free (plain stores + a fix-up pass over the slot-boundary
+# carries, csrc/edge_fwd_hl.cu aggr_fixup_kernel).
+DETERMINISTIC = True
+
+
+def carry_buffer(num_edges: int, slot_rows: int, device) -> torch.Tensor:
+    """Workspace of the deterministic aggregation: one 128-float row per `slot_rows`-edge slot (8 for edge_fwd, 32 for
+    edge_fwd_hl).  Contents need no initialisation: only rows a kernel wrote are read back."""
+    return torch.empty(((num_edges + slot_rows - 1) // slot_rows, H), dtype=torch.float32, device=device)
+
+
 def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor, senders: torch.Tensor,
              receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
              e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None, saves=None,
              e16_out: Optional[torch.Tensor] = None, e16_in: Optional[torch.Tensor] = None,
              e16_next: Optional[torch.Tensor] = None, out_in_csr_order: bool = False,
-             e16lo_next: Optional[torch.Tensor] = None, write_rows: bool = True):
+             e16lo_next: Optional[torch.Tensor] = None, write_rows: bool = True,
+             carry: Optional[torch.Tensor] = None, norm_dim: int = H):
     """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
     used by the parity tests only -- the backward kernel recomputes them).
     e16_out: optional `e16_image(E)` buffer receiving the fp16 tile images of e_in that edge_bwd bulk-loads.
@@ -76,10 +88,13 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
         e_out = torch.empty_like(e_in)
     if aggr is None:
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=e_in.device)
+    if carry is None and DETERMINISTIC and E > 0:
+        carry = carry_buffer(E, 8, e_in.device)
     L.check(L.lib().mgn_edge_fwd2(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(rowmap), L.p(e_out), L.p(P),
                                   L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
                                   L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next),
-                                  L.p(e16lo_next), L.i32(1 if out_in_csr_order else 0), L.stream()))
+                                  L.p(e16lo_next), L.i32(1 if out_in_csr_order else 0),
+                                  L.p(carry), L.i32(norm_dim), L.stream()))
     return e_out, aggr
 
 
@@ -91,16 +106,20 @@ EDGE_FWD_HL = bool(int(__import__("os").environ.get("MGN_EDGE_FWD_HL", "1")))
 def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, senders: torch.Tensor,
                 receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
                 hi_out: Optional[torch.Tensor] = None, lo_out: Optional[torch.Tensor] = None,
-                e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None):
+                e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None,
+                carry: Optional[torch.Tensor] = None, norm_dim: int = H):
     """Edge update of one step (layers.py:687-698) on the image + remainder form of the edge stream:
     e_in = hi_in + lo_in (`e16_image` buffers, CSR tile order).  hi_out / lo_out receive the same form of e_out,
     e_out (optional, [E,128] fp32, CSR order) its fp32 rows.  -> aggr"""
     E = senders.shape[0]
     if aggr is None:
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=hi_in.device)
+    if carry is None and DETERMINISTIC and E > 0:
+        carry = carry_buffer(E, 32, hi_in.device)
     L.check(L.lib().mgn_edge_fwd_hl(L.i64(E), L.i64(num_nodes), L.p(hi_in), L.p(lo_in), L.p(hi_out), L.p(lo_out),
                                     L.p(e_out), L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed),
-                                    L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.stream()))
+                                    L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(carry),
+                                    L.i32(norm_dim), L.stream()))
     return aggr
 
 
@@ -128,7 +147,7 @@ def image_rows(img: torch.Tensor, num_rows: int) -> torch.Tensor:
 
 
 def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
-             x_out: Optional[torch.Tensor] = None, saves=None, norm: bool = True) -> torch.Tensor:
+             x_out: Optional[torch.Tensor] = None, saves=None, norm: bool = True, norm_dim: int = H) -> torch.Tensor:
     """saves: `node_saves(N)` buffers (tile images), or None.  norm=False: the block has no RMSNorm (decoder)."""
     N = x.shape[0]
     if saves is not None and any(sv.numel() < ((N + 127) // 128) * 128 * H for sv in saves):
@@ -137,7 +156,8 @@ def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, 
         x_out = torch.empty_like(x)
     s1, s2, s3 = saves if saves is not None else (None, None, None)
     L.check(L.lib().mgn_node_fwd2(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
-                                  L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.i32(0 if norm else 1), L.stream()))
+                                  L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.i32(0 if norm else 1), L.i32(norm_dim),
+                                  L.stream()))
     return x_out
 
 
@@ -169,7 +189,7 @@ def split_grad_block(flat: torch.Tensor):
 
 
 def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, packed, b2, b3, b4, scale,
-             grad_block, g_e=None, dz16=None, e16=None, inplace=False):
+             grad_block, g_e=None, dz16=None, e16=None, inplace=False, norm_dim: int = H):
     """-> (g_e [E,128], dz16: fp16 tile images of dz1 for p_bwd).  g_eout may be None (zero upstream edge gradient).
     `inplace` writes g_e over g_eout (each tile is read before it is written).
     e16: the forward kernel's fp16 tile images of e_in (then e_in may be None)."""
@@ -182,11 +202,12 @@ def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, pac
         dz16 = e16_image(E, dev)
     L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16), L.p(rowmap), L.p(g_src),
                                  L.p(g_aggr), L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(dz16), L.p(packed),
-                                 L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.stream()))
+                                 L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.i32(norm_dim), L.stream()))
     return g_e, dz16
 
 
-def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None, norm: bool = True):
+def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None, norm: bool = True,
+             norm_dim: int = H):
     """-> (g_x direct part, g_aggr, dz1 fp16)."""
     N = g_xout.shape[0]
     if g_x is None:
@@ -197,7 +218,8 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
         dz1 = torch.empty((N, H), dtype=torch.float16, device=g_xout.device)
     h1, h2, h3 = saves
     L.check(L.lib().mgn_node_bwd2(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
-                                  L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.i32(0 if norm else 1), L.stream()))
+                                  L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.i32(0 if norm else 1), L.i32(norm_dim),
+                                  L.stream()))
     return g_x, g_aggr, dz1
 
 

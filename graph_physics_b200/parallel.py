@@ -63,10 +63,16 @@ class GradSync:
         if _proc.GRAD_SYNC is self:
             _proc.GRAD_SYNC = None
 
-    def wait(self):
+    def finish(self):
+        """Called by the fused backward before it returns its gradient views: makes the compute stream wait for every
+        all-reduce started so far (a stream-side wait, the host does not block), so the values autograd accumulates
+        into `.grad` -- also with `zero_grad(set_to_none=False)` or gradient accumulation -- are the reduced ones."""
         for h in self.handles:
             h.wait()
         self.handles.clear()
+
+    def wait(self):
+        self.finish()
 
 
 def allreduce_module_grads(params, group=None, average: bool = True) -> Optional[torch.Tensor]:
@@ -95,3 +101,18 @@ def allreduce_last_grad_blocks(group=None, average: bool = True) -> Optional[tor
         return buf
     dist.all_reduce(buf, op=dist.ReduceOp.AVG if average else dist.ReduceOp.SUM, group=group)
     return buf
+
+
+def check_grads_alias_last_blocks(params) -> None:
+    """`allreduce_last_grad_blocks` reduces the flat buffer of the last backward sweep; that reaches the optimiser only
+    if the parameters' `.grad` ARE views of it, i.e. if `.grad` was None before backward (`zero_grad(set_to_none=True)`,
+    the PyTorch default).  Raises otherwise (accumulated or pre-existing gradients live in their own storage)."""
+    buf = _proc.LAST_GRAD_BLOCKS
+    if buf is None:
+        raise RuntimeError("no fused backward has run yet")
+    lo, hi = buf.data_ptr(), buf.data_ptr() + buf.numel() * buf.element_size()
+    bad = [i for i, p in enumerate(params) if p.grad is not None and not (lo <= p.grad.data_ptr() < hi)]
+    if bad:
+        raise RuntimeError(f"{len(bad)} parameter gradients are not views of processor.LAST_GRAD_BLOCKS: call "
+                           "zero_grad(set_to_none=True) before backward, or use GradSync (per-block hook) instead of "
+                           "allreduce_last_grad_blocks")

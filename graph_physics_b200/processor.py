@@ -116,9 +116,10 @@ def _check_inputs(x, e, params, num_steps):
 
 class _ProcessorFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x0, e0, csr, num_steps, need_edges, *params):
+    def forward(ctx, x0, e0, csr, num_steps, need_edges, norm_dim, *params):
         ctx.set_materialize_grads(False)
         K = int(num_steps)
+        nd = int(norm_dim)
         _check_inputs(x0, e0, params, K)
         dev = x0.device
         N, E = x0.shape[0], e0.shape[0]
@@ -148,6 +149,8 @@ class _ProcessorFn(torch.autograd.Function):
         # writes image k+1 next to e_{k+1}; training keeps them all (the edge backward recomputes from them)
         img_bufs = [ops.e16_image(E, dev) for _ in range(min(K, 2))] if not need_grad else None
         img = None
+        # workspace of the deterministic aggregation (ops.carry_buffer): 8-row slots for step 0, 32-row slots after
+        carry = ops.carry_buffer(E, 8, dev) if (ops.DETERMINISTIC and E > 0) else None
         for k in range(K):
             b = prm[18 * k:18 * (k + 1)]
             if need_grad:
@@ -174,14 +177,15 @@ class _ProcessorFn(torch.autograd.Function):
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
             if hl and k > 0:
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers, N,
-                       packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out, aggr=aggr)
+                       packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out, aggr=aggr,
+                       carry=carry, norm_dim=nd)
             else:
                 _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
                        packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
                        e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
-                       write_rows=not (hl and e_out is None))
+                       write_rows=not (hl and e_out is None), carry=carry, norm_dim=nd)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
-                   saves=sv)
+                   saves=sv, norm_dim=nd)
             if need_grad:
                 aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
             x, img = x_out, img_next
@@ -199,7 +203,7 @@ class _ProcessorFn(torch.autograd.Function):
             ctx.csr, ctx.K, ctx.packed, ctx.prm = csr, K, packed, prm
             # the edge backward needs e_k only as the fp16 tile images: the fp32 versions are not kept
             ctx.xs, ctx.e16s, ctx.aggrs, ctx.Ps, ctx.saves = xs, e16s, aggrs, Ps, saves
-            ctx.E = E
+            ctx.E, ctx.nd = E, nd
         return x, e_ret
 
     @staticmethod
@@ -207,9 +211,9 @@ class _ProcessorFn(torch.autograd.Function):
         csr, K, packed, prm = ctx.csr, ctx.K, ctx.packed, ctx.prm
         xs, e16s = ctx.xs, ctx.e16s
         dev = xs[0].device
-        N, E = xs[0].shape[0], ctx.E
+        N, E, nd = xs[0].shape[0], ctx.E, ctx.nd
         if g_x is None and g_e is None:
-            return (None,) * (5 + 18 * K)
+            return (None,) * (6 + 18 * K)
         # ---- power-of-two gradient scale (device-side, no host sync)
         amax = torch.zeros((), dtype=torch.float32, device=dev)
         if g_x is not None:
@@ -244,12 +248,12 @@ class _ProcessorFn(torch.autograd.Function):
         for k in range(K - 1, -1, -1):
             b = prm[18 * k:18 * (k + 1)]
             _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
-                   g_aggr=g_aggr, dz1=dz1)
+                   g_aggr=g_aggr, dz1=dz1, norm_dim=nd)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
             if E > 0:
                 _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
                        csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
-                       inplace=True)
+                       inplace=True, norm_dim=nd)
                 have_ge = True
                 _timed("edge_wgrad1", ops.edge_wgrad1, dz16, e16s[k], E, grads[k])
                 _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
@@ -261,6 +265,10 @@ class _ProcessorFn(torch.autograd.Function):
             # release what this step saved
             ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None; e16s[k] = None
             xs[k + 1] = None
+        if GRAD_SYNC is not None and hasattr(GRAD_SYNC, "finish"):
+            # the reductions started per block must be complete (in stream order) before autograd hands the views
+            # below to AccumulateGrad: with an existing .grad it would otherwise add partly reduced values
+            GRAD_SYNC.finish()
         g_x0 = gx * inv_s if ctx.needs_input_grad[0] else None
         g_e0 = None
         if ctx.needs_input_grad[1]:
@@ -270,27 +278,40 @@ class _ProcessorFn(torch.autograd.Function):
             else:
                 g_e0 = torch.empty_like(ge)
                 g_e0.index_copy_(0, csr.perm_long, ge)
-        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None, None]
+        out: List[Optional[torch.Tensor]] = [g_x0, g_e0, None, None, None, None]
         for k in range(K):
             views = ops.split_grad_block(grads[k])
             for i, name in enumerate(PARAM_NAMES):
-                out.append(views[name] if ctx.needs_input_grad[5 + 18 * k + i] else None)
+                out.append(views[name] if ctx.needs_input_grad[6 + 18 * k + i] else None)
         return tuple(out)
 
 
 def run_processor(x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
                   block_params: Sequence[Sequence[torch.Tensor]], csr: Optional[G.CSRGraph] = None,
                   need_edges: bool = True):
-    """x [N,128], edge_index [2,E] int64, edge_attr [E,128] (caller's edge order),
-    block_params: per GraphNetBlock the 18 tensors in ops.GRAD_LAYOUT order.
+    """x [N,d], edge_index [2,E] int64, edge_attr [E,d] (caller's edge order), d <= 128;
+    block_params: per GraphNetBlock the 18 tensors in ops.GRAD_LAYOUT order AT THE KERNELS' SHAPE (hidden 128, four
+    layers): for d < 128 or fewer layers `models.layers.block_param_list` zero-pads / inserts identity layers.
+    Latents narrower than 128 are zero-padded here and the result is cut back; RMSNorm divides by sqrt(d).
     Returns (x_K, edge_attr_K) with edge_attr_K in the caller's edge order (an empty tensor if not need_edges)."""
     L.require_device(x)
     if csr is None:
         csr = csr_for(edge_index, x.shape[0])
     if csr.num_edges != edge_attr.shape[0] or csr.num_nodes != x.shape[0]:
         raise ValueError("edge_index / edge_attr / x sizes disagree")
+    d = int(x.shape[1])
+    if edge_attr.shape[1] != d or not (0 < d <= H):
+        raise ValueError(f"graph_physics_b200 processor supports hidden_size <= {H} with equal node / edge widths; got "
+                         f"x {tuple(x.shape)}, edge_attr {tuple(edge_attr.shape)}")
+    if d < H:
+        x = torch.nn.functional.pad(x, (0, H - d))
+        edge_attr = torch.nn.functional.pad(edge_attr, (0, H - d))
     flat = [t for blk in block_params for t in blk]
-    return _ProcessorFn.apply(x, edge_attr, csr, len(block_params), bool(need_edges), *flat)
+    xo, eo = _ProcessorFn.apply(x, edge_attr, csr, len(block_params), bool(need_edges), d, *flat)
+    if d < H:
+        xo = xo[:, :d]
+        eo = eo[:, :d] if need_edges else eo
+    return xo, eo
 
 
 class CapturedStep:

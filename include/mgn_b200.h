@@ -119,28 +119,31 @@ int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edg
  * the images of e_out.  mgn_edge_bwd recomputes from the images of e_in.  out_in_csr_order != 0 with a rowmap:
  * e_in is gathered through the rowmap but e_out is written in CSR order (the entry permutation of a processor
  * loop fused into its first step). */
-int mgn_edge_fwd(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
-                 const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
-                 const void* packed, const float* b2, const float* b3, const float* b4,
-                 const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                 const void* e16_in, void* e16_next, int out_in_csr_order, void* stream);
-/* mgn_edge_fwd plus e16lo_next: tile images of  e_out - fp16(e_out)  (fp16), i.e. together with e16_next the
+/* e16lo_next: tile images of  e_out - fp16(e_out)  (fp16), i.e. together with e16_next the
  * image + remainder form of the residual stream that mgn_edge_fwd_hl consumes.  With both images requested e_out
- * may be NULL (the fp32 rows are then not written at all). */
+ * may be NULL (the fp32 rows are then not written at all).
+ * carry: fp32 workspace [ceil(E/8),128].  The sum at the receivers (PyG scatter-sum, layers.py:694-696) is
+ * DETERMINISTIC and atomics-free: the receiver-sorted edge list is cut into 8-row slots, a run of equal receivers
+ * that starts in a slot is stored to its node's row of aggr, the partial sums of its continuation in later slots go
+ * to carry[slot] and a second kernel adds them in slot order (one writer per node).
+ * norm_dim: the model's true hidden size d for RMSNorm's d^-1/2 (layers.py:66); 128 unless the caller zero-pads a
+ * narrower model into the 128-wide kernels. */
 int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
                   const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                   const void* packed, const float* b2, const float* b3, const float* b4,
                   const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
-                  const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order, void* stream);
+                  const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order, float* carry,
+                  int norm_dim, void* stream);
 /* The same edge update (layers.py:687-698) for steps 1..K-1 with the residual stream held as two fp16 tile-image
  * streams, hi = fp16(e) (= the operand images mgn_edge_bwd recomputes from) and lo = fp16(e - hi): e = hi + lo
  * carries >= 21 significant bits of the fp32 stream, the residual add is done in fp32, and the stream moves only by
  * 32 KB bulk copies (csrc/edge_fwd_hl.cu).  hi_out / lo_out (both or neither) receive the images of e_out; e_out
- * (fp32 rows, CSR order) is optional -- only a caller that wants the edge latents back needs it. */
+ * (fp32 rows, CSR order) is optional -- only a caller that wants the edge latents back needs it.
+ * carry: [ceil(E/32),128] fp32 workspace, norm_dim: as for mgn_edge_fwd2 (slots of 32 rows here). */
 int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
                     float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
-                    void* stream);
+                    float* carry, int norm_dim, void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* (optional, all three or
  * none) receive the hidden activations mgn_node_bwd needs as fp16 TILE IMAGES: ceil(N/128) * 32768 bytes each, one
  * 128-byte-swizzled 128 x 128 operand tile per 128 rows, bulk-stored as it sits in shared memory. */
@@ -151,7 +154,8 @@ int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float* x_out, con
  * EncodeProcessDecode, processors.py:85-90): x_out = x + MLP(cat[x, aggr]); `scale` is ignored. */
 int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                   const float* b1, const float* b2, const float* b3, const float* b4,
-                  const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags, void* stream);
+                  const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags, int norm_dim,
+                  void* stream);
 
 /* ------------------------------------------------------------------ backward of the step
  * What torch.autograd derives from GraphNetBlock.forward in the reference.  Parameter gradients of
@@ -167,7 +171,7 @@ int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2,
 /* mgn_node_bwd with flags: bit 0 = no RMSNorm (see mgn_node_fwd2): dz4 = g_xout, no scale gradient. */
 int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                   float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                  const float* scale, float* grad_block, int flags, void* stream);
+                  const float* scale, float* grad_block, int flags, int norm_dim, void* stream);
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);
@@ -180,7 +184,8 @@ int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* agg
 int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const int32_t* rowmap,
                  const float* g_eout, const float* g_aggr, const void* P, const int32_t* senders,
                  const int32_t* receivers, float* g_e, void* dz16_out, const void* packed, const float* b2,
-                 const float* b3, const float* b4, const float* scale, float* grad_block, void* stream);
+                 const float* b3, const float* b4, const float* scale, float* grad_block, int norm_dim,
+                 void* stream);
 /* edge_block layer-1 weight gradient, edge-latent columns (edge_block.0.weight[:, 0:128]):
  * dWe += dz1^T e over all edges, streamed from the tile images of dz1 (mgn_edge_bwd) and of e (mgn_edge_fwd). */
 int mgn_edge_wgrad1(int64_t E, const void* dz16, const void* e16, float* grad_block, void* stream);

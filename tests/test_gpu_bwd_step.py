@@ -6,7 +6,7 @@ BASELINE.json states no gradient tolerance.  Two are used (DESIGN.md "Numerics")
    rounding points (oracle `emulate_fp16=True`) and differentiated through the SAME ReLU active
    set as the device (masks = [h > 0] of the hidden activations the forward kernels computed):
    this isolates the backward kernels' own error.
- * TOL_GRAD_EXACT = 0.06 against the exact fp64 oracle.  A ReLU network's gradient is
+ * TOL_GRAD_EXACT = 0.10 against the exact fp64 oracle.  A ReLU network's gradient is
    discontinuous in the pre-activations: any 10-bit-mantissa forward (fp16 here, TF32 in the
    reference, train.py:28) flips the ReLU mask of the ~4e-4 fraction of units whose
    pre-activation is within rounding error of 0, which moves the gradient by sqrt(fraction)
@@ -23,7 +23,7 @@ from oracle.synth import processor_inputs
 
 pytestmark = pytest.mark.gpu
 TOL_GRAD = 5e-3
-TOL_GRAD_EXACT = 0.06
+TOL_GRAD_EXACT = 0.10
 
 
 def _step_fwd_bwd(ei_np, n, x0, e0, gx1, ge1, p, use_rowmap=True):
