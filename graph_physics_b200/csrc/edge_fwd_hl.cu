@@ -386,9 +386,10 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
 // slots sit in carry[slot].  Here one warp per slot finds the first continuation slot of each such run and adds the
 // chain carry[s], carry[s+1], ... to aggr[node] in slot order: one writer per node, fixed order, no atomics.
 struct AggrFixupParams {
-  long long E;
+  long long E, N;
   int slot_rows;
   const int32_t* receivers;
+  const int32_t* rowptr;    // [N+1] receiver CSR, or null (then the caller has zeroed aggr)
   const float* carry;
   float* aggr;
 };
@@ -399,7 +400,21 @@ __global__ void __launch_bounds__(256) aggr_fixup_kernel(const AggrFixupParams p
   const int lane = threadIdx.x & 31;
   const long long nslots = (p.E + p.slot_rows - 1) / p.slot_rows;
   const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long s = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1; s < nslots; s += warps) {
+  const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // nodes nobody sends to: no edge kernel wrote their row -- zero it here (this replaces a memset of the whole array)
+  if (p.rowptr != nullptr) {
+    for (long long n0 = warp0 * 32; n0 < p.N; n0 += warps * 32) {
+      const long long n = n0 + lane;
+      const bool empty = n < p.N && __ldg(p.rowptr + n) == __ldg(p.rowptr + n + 1);
+      unsigned mask = __ballot_sync(0xffffffffu, empty);
+      while (mask) {
+        const int b = __ffs(mask) - 1;
+        mask &= mask - 1;
+        reinterpret_cast<float4*>(p.aggr + (n0 + b) * H)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  for (long long s = warp0 + 1; s < nslots; s += warps) {
     const long long r0 = s * p.slot_rows;
     const int k = __ldg(p.receivers + r0);
     if (__ldg(p.receivers + r0 - 1) != k) continue;                       // this slot starts a new run: nothing carried
@@ -417,12 +432,13 @@ __global__ void __launch_bounds__(256) aggr_fixup_kernel(const AggrFixupParams p
   }
 }
 
-int mgn_launch_aggr_fixup(int64_t E, int slot_rows, const int32_t* receivers, const float* carry, float* aggr,
-                          cudaStream_t stream) {
+int mgn_launch_aggr_fixup(int64_t E, int64_t N, int slot_rows, const int32_t* receivers, const int32_t* rowptr,
+                          const float* carry, float* aggr, cudaStream_t stream) {
   const int64_t nslots = ceil_div64(E, slot_rows);
-  if (nslots <= 1) return MGN_OK;
-  AggrFixupParams p{E, slot_rows, receivers, carry, aggr};
-  const int grid = (int)std::min<int64_t>(ceil_div64(nslots, 8), (int64_t)mgn_num_sms() * 8);
+  if (nslots <= 1 && rowptr == nullptr) return MGN_OK;
+  AggrFixupParams p{E, N, slot_rows, receivers, rowptr, carry, aggr};
+  const int64_t work = std::max<int64_t>(nslots, rowptr ? ceil_div64(N, 32) : 0);
+  const int grid = (int)std::min<int64_t>(std::max<int64_t>(ceil_div64(work, 8), 1), (int64_t)mgn_num_sms() * 8);
   MGN_CUDA(mgn_launch(aggr_fixup_kernel, grid, 256, 0, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
@@ -439,10 +455,11 @@ static constexpr int EDGE_HL_SMEM = 7 * 32768 + TAIL_BYTES;
 extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
                                float* e_out, const void* P, const int32_t* senders, const int32_t* receivers,
                                float* aggr, const void* packed, const float* b2, const float* b3, const float* b4,
-                               const float* scale, float* carry, int norm_dim, void* stream_) {
+                               const float* scale, float* carry, const int32_t* rowptr, int norm_dim,
+                               void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd_hl: bad sizes");
-  MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
+  if (rowptr == nullptr || E == 0) MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
   if (E == 0) return MGN_OK;
   MGN_CHECK_ARG(hi_in && lo_in && P && senders && receivers && packed && b2 && b3 && b4 && scale && carry,
                 "edge_fwd_hl: null pointer");
@@ -466,5 +483,5 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
   MGN_CUDA(mgn_launch(edge_fwd_hl_kernel, grid, NT, EDGE_HL_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
-  return mgn_launch_aggr_fixup(E, 32, receivers, carry, aggr, stream);
+  return mgn_launch_aggr_fixup(E, N, 32, receivers, rowptr, carry, aggr, stream);
 }

@@ -74,21 +74,6 @@ __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb
   return warp_colsum32(g, m.lane);
 }
 
-// ReLU backward in place with the store held back: the dgrad product (accumulator) is complete, the weight-gradient
-// product issued right behind it may still be READING `tile` (h) as its operand -- so the accumulator and h are loaded
-// and masked first, and `tile` is only overwritten once `bar_wg` (the weight-gradient product's commit) has fired
-__device__ __forceinline__ void epi_relu_mask_after(uint32_t taddr, uint8_t* tile, const Map& m, uint64_t* bar_wg,
-                                                    uint32_t parity) {
-  float v[32], h[32];
-  tmem_ld32(taddr, v);
-  load_row_chunk_f16(tile, 128, m.row, m.c0, h);
-  tmem_ld_wait();
-#pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = h[j] > 0.f ? v[j] : 0.f;
-  mbar_wait(bar_wg, parity);
-  store_row_chunk_f16(tile, 128, m.row, m.c0, v);
-}
-
 // ===================================================================================== edge
 struct EdgeBwdParams {
   long long E;
@@ -134,7 +119,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   uint64_t& bar_wA = tail->bar[0];
   uint64_t& bar_wB = tail->bar[1];
   uint64_t& bar_mma = tail->bar[2];
-  uint64_t& bar_wg = tail->bar[3];      // weight-gradient products (committed apart from the dgrad product before them)
   uint64_t& bar_e = tail->bar[4];
   uint64_t& bar_g = tail->bar[5];
   uint64_t& bar_g2 = tail->bar[6];
@@ -146,7 +130,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     mbar_init(&bar_wA, 1);
     mbar_init(&bar_wB, 1);
     mbar_init(&bar_mma, 1);
-    mbar_init(&bar_wg, 1);
     mbar_init(&bar_e, 1);
     mbar_init(&bar_g, 1);
     mbar_init(&bar_g2, 1);
@@ -166,7 +149,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
                  uH2 = smem_u32(sH2), uH3 = smem_u32(sH3), uG = smem_u32(sG);
   const uint64_t pol_stream = policy_evict_first();
   const uint64_t pol_keep = policy_evict_last();
-  uint32_t phase = 0, phase_wg = 0;
+  uint32_t phase = 0;
   float dsc = 0.f;
   float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
   if (m.tid == 0) {
@@ -430,9 +413,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uG, 128, 0, uW4, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
@@ -442,8 +424,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
         load_w_slot(sWA, p.W, 0, &bar_wA);                 // W4 is done: We -> A for D1 (and the next tile's R1)
       }
     }
-    epi_relu_mask_after(tm_W + qoff, sH3, m, &bar_wg, phase_wg);
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
     // ---- D3
     if (m.tid == 0) {
@@ -452,25 +433,22 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
       if (FAST && has_next) issue_e16(tile + gridDim.x);
       fence_after_sync();
       umma_tile(tm_W, uH3, 128, 0, uW3, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     if (!FAST && has_next) gq = g_issue(nxt, 0);   // sG is dead: next tile's g, piece 0
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (!FAST && m.tid == 0) load_w_slot(sWA, p.W, 0, &bar_wA);     // We -> A
-    epi_relu_mask_after(tm_W + qoff, sH2, m, &bar_wg, phase_wg);
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
     // ---- D2
     if (m.tid == 0) {
       if (!FAST) mbar_wait(&bar_wB, 0);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uWB, 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     if (!FAST && has_next) {
       g_store(gq, 0);
@@ -478,8 +456,7 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     }
     tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
-    epi_relu_mask_after(tm_W + qoff, sH1, m, &bar_wg, phase_wg);    // sH1 <- dz1
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH1, m);    // sH1 <- dz1
     tile_ready();
     tl.stamp();   // 5 D4..D2 done
     // upstream rows of this tile for the residual add, straight into the (now dead) sH2 + sH3 as a linear fp32 tile
@@ -609,7 +586,6 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   uint64_t* bar_w = &tail->bar[0];
   uint64_t& bar_mma = tail->bar[2];
   uint64_t& bar_h = tail->bar[3];
-  uint64_t& bar_wg = tail->bar[4];      // weight-gradient products (committed apart from the dgrad product before them)
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
   if (m.tid == 0) {
@@ -617,7 +593,6 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     mbar_init(&bar_w[1], 1);
     mbar_init(&bar_mma, 1);
     mbar_init(&bar_h, 1);
-    mbar_init(&bar_wg, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -644,7 +619,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     }
   };
   auto wait_load = [&](uint32_t qq) { mbar_wait(&bar_w[qq & 1], (qq >> 1) & 1); };
-  uint32_t phase = 0, phase_wg = 0;
+  uint32_t phase = 0;
   auto mma_wait = [&]() {
     mbar_wait(&bar_mma, phase);
     phase ^= 1;
@@ -694,45 +669,39 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile(tm_W, uG, 128, 0, uW[q0 & 1], 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     tile_colsum_q(sG, m.tid, db4a, db4b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 2);
-    epi_relu_mask_after(tm_W + qoff, sH3, m, &bar_wg, phase_wg);
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
     // ---- D3
     if (m.tid == 0) {
       wait_load(q0 + 1);
       fence_after_sync();
       umma_tile(tm_W, uH3, 128, 0, uW[(q0 + 1) & 1], 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     tile_colsum_q(sH3, m.tid, db3a, db3b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 3);
-    epi_relu_mask_after(tm_W + qoff, sH2, m, &bar_wg, phase_wg);
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
     // ---- D2
     if (m.tid == 0) {
       wait_load(q0 + 2);
       fence_after_sync();
       umma_tile(tm_W, uH2, 128, 0, uW[(q0 + 2) & 1], 128, 1, 0, 128, 8, 0);
-      mma_commit(&bar_mma);
       umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
-      mma_commit(&bar_wg);
+      mma_commit(&bar_mma);
     }
     tile_colsum_q(sH2, m.tid, db2a, db2b);
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 4);
-    epi_relu_mask_after(tm_W + qoff, sH1, m, &bar_wg, phase_wg);     // sH1 <- dz1'
-    phase_wg ^= 1;
+    epi_relu_mask_q(tm_W + qoff, sH1, m);     // sH1 <- dz1'
     tile_ready();
     // ---- D1a: g_x = g_xout + dz1' W1'[:, :128]
     if (m.tid == 0) {

@@ -612,10 +612,10 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
                              const void* packed, const float* b2, const float* b3, const float* b4,
                              const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
                              const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order,
-                             float* carry, int norm_dim, void* stream_) {
+                             float* carry, const int32_t* rowptr, int norm_dim, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd: bad sizes");
-  MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
+  if (rowptr == nullptr || E == 0) MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
   if (E == 0) return MGN_OK;
   MGN_CHECK_ARG(e_in && P && senders && receivers && packed && b2 && b3 && b4 && scale && carry,
                 "edge_fwd: null pointer");
@@ -643,7 +643,7 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
   MGN_CUDA(mgn_launch(mlp_fwd_kernel<true>, grid, NT, EDGE_FWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
-  return mgn_launch_aggr_fixup(E, 8, receivers, carry, aggr, stream);
+  return mgn_launch_aggr_fixup(E, N, 8, receivers, rowptr, carry, aggr, stream);
 }
 
 // GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).

@@ -3,8 +3,8 @@
 #include <stdint.h>
 #include <cuda_runtime.h>
 // second half of the deterministic receiver aggregation (edge_fwd_hl.cu)
-int mgn_launch_aggr_fixup(int64_t E, int slot_rows, const int32_t* receivers, const float* carry, float* aggr,
-                          cudaStream_t stream);
+int mgn_launch_aggr_fixup(int64_t E, int64_t N, int slot_rows, const int32_t* receivers, const int32_t* rowptr,
+                          const float* carry, float* aggr, cudaStream_t stream);
 namespace mgn {
 static constexpr int64_t PK_EDGE = 0;                 // W1e, W2, W3, W4   (4 x 32 KB)
 static constexpr int64_t PK_WCAT = 4 * 32768;         // [W_i ; W_j] 256 x 128 (64 KB)

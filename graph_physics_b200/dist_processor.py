@@ -107,12 +107,12 @@ class PartitionEngine:
             if self.hl and k > 0:
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, self.lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers,
                        n_ext, self.packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out,
-                       aggr=aggr, carry=self.carry)
+                       aggr=aggr, carry=self.carry, rowptr=csr.rowptr)
             else:
                 _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
                        b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
                        e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
-                       write_rows=not (self.hl and e_out is None), carry=self.carry)
+                       write_rows=not (self.hl and e_out is None), carry=self.carry, rowptr=csr.rowptr)
             if ng:
                 self.e16s.append(self.img)
             self.img = img_next

@@ -68,7 +68,7 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
              e16_out: Optional[torch.Tensor] = None, e16_in: Optional[torch.Tensor] = None,
              e16_next: Optional[torch.Tensor] = None, out_in_csr_order: bool = False,
              e16lo_next: Optional[torch.Tensor] = None, write_rows: bool = True,
-             carry: Optional[torch.Tensor] = None, norm_dim: int = H):
+             carry: Optional[torch.Tensor] = None, norm_dim: int = H, rowptr: Optional[torch.Tensor] = None):
     """saves: optional 3 fp16 [E,128] buffers receiving the hidden activations (row = CSR position;
     used by the parity tests only -- the backward kernel recomputes them).
     e16_out: optional `e16_image(E)` buffer receiving the fp16 tile images of e_in that edge_bwd bulk-loads.
@@ -94,7 +94,7 @@ def edge_fwd(e_in: torch.Tensor, rowmap: Optional[torch.Tensor], P: torch.Tensor
                                   L.p(senders), L.p(receivers), L.p(aggr), L.p(packed), L.p(b2), L.p(b3), L.p(b4),
                                   L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.p(e16_out), L.p(e16_in), L.p(e16_next),
                                   L.p(e16lo_next), L.i32(1 if out_in_csr_order else 0),
-                                  L.p(carry), L.i32(norm_dim), L.stream()))
+                                  L.p(carry), L.p(rowptr), L.i32(norm_dim), L.stream()))
     return e_out, aggr
 
 
@@ -107,7 +107,7 @@ def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, sende
                 receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
                 hi_out: Optional[torch.Tensor] = None, lo_out: Optional[torch.Tensor] = None,
                 e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None,
-                carry: Optional[torch.Tensor] = None, norm_dim: int = H):
+                carry: Optional[torch.Tensor] = None, norm_dim: int = H, rowptr: Optional[torch.Tensor] = None):
     """Edge update of one step (layers.py:687-698) on the image + remainder form of the edge stream:
     e_in = hi_in + lo_in (`e16_image` buffers, CSR tile order).  hi_out / lo_out receive the same form of e_out,
     e_out (optional, [E,128] fp32, CSR order) its fp32 rows.  -> aggr"""
@@ -118,7 +118,7 @@ def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, sende
         carry = carry_buffer(E, 32, hi_in.device)
     L.check(L.lib().mgn_edge_fwd_hl(L.i64(E), L.i64(num_nodes), L.p(hi_in), L.p(lo_in), L.p(hi_out), L.p(lo_out),
                                     L.p(e_out), L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed),
-                                    L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(carry),
+                                    L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(carry), L.p(rowptr),
                                     L.i32(norm_dim), L.stream()))
     return aggr
 

@@ -178,12 +178,12 @@ class _ProcessorFn(torch.autograd.Function):
             if hl and k > 0:
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers, N,
                        packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out, aggr=aggr,
-                       carry=carry, norm_dim=nd)
+                       carry=carry, norm_dim=nd, rowptr=csr.rowptr)
             else:
                 _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
                        packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
                        e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
-                       write_rows=not (hl and e_out is None), carry=carry, norm_dim=nd)
+                       write_rows=not (hl and e_out is None), carry=carry, norm_dim=nd, rowptr=csr.rowptr)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
                    saves=sv, norm_dim=nd)
             if need_grad:

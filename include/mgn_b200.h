@@ -126,6 +126,8 @@ int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edg
  * DETERMINISTIC and atomics-free: the receiver-sorted edge list is cut into 8-row slots, a run of equal receivers
  * that starts in a slot is stored to its node's row of aggr, the partial sums of its continuation in later slots go
  * to carry[slot] and a second kernel adds them in slot order (one writer per node).
+ * rowptr: [N+1] receiver CSR or NULL: with it the second kernel also zeroes the rows of nodes without in-edges and
+ * aggr needs no initialisation (NULL: aggr is cleared with a memset first).
  * norm_dim: the model's true hidden size d for RMSNorm's d^-1/2 (layers.py:66); 128 unless the caller zero-pads a
  * narrower model into the 128-wide kernels. */
 int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap, float* e_out,
@@ -133,7 +135,7 @@ int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap
                   const void* packed, const float* b2, const float* b3, const float* b4,
                   const float* scale, void* save_h1, void* save_h2, void* save_h3, void* e16_out,
                   const void* e16_in, void* e16_next, void* e16lo_next, int out_in_csr_order, float* carry,
-                  int norm_dim, void* stream);
+                  const int32_t* rowptr, int norm_dim, void* stream);
 /* The same edge update (layers.py:687-698) for steps 1..K-1 with the residual stream held as two fp16 tile-image
  * streams, hi = fp16(e) (= the operand images mgn_edge_bwd recomputes from) and lo = fp16(e - hi): e = hi + lo
  * carries >= 21 significant bits of the fp32 stream, the residual add is done in fp32, and the stream moves only by
@@ -143,7 +145,7 @@ int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap
 int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
                     float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
-                    float* carry, int norm_dim, void* stream);
+                    float* carry, const int32_t* rowptr, int norm_dim, void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* (optional, all three or
  * none) receive the hidden activations mgn_node_bwd needs as fp16 TILE IMAGES: ceil(N/128) * 32768 bytes each, one
  * 128-byte-swizzled 128 x 128 operand tile per 128 rows, bulk-stored as it sits in shared memory. */
