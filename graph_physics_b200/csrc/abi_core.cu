@@ -47,7 +47,14 @@ extern "C" int mgn_debug_set_timeline(long long* buf, int cap) {
 static unsigned long long* g_hang_host = nullptr;
 static bool g_hang_tried = false;
 
+// set (per host thread) by entry points that promise not to allocate: the hang buffer is then used if it already
+// exists, but not created
+thread_local bool g_mgn_no_alloc_scope = false;
+bool mgn_no_alloc_scope() { return g_mgn_no_alloc_scope; }
+void mgn_set_no_alloc_scope(bool on) { g_mgn_no_alloc_scope = on; }
+
 void* mgn_hang_buffer() {
+  if (!g_hang_tried && g_mgn_no_alloc_scope) return nullptr;      // would have to cudaHostAlloc: not in this scope
   if (!g_hang_tried) {
     g_hang_tried = true;
     void* h = nullptr;

@@ -72,12 +72,15 @@ __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.laun
 // 8 x u64 of host-mapped pinned memory, allocated once per process (abi_core.cu).  Each translation unit keeps the
 // device pointer in its own __device__ variable, set on that unit's first launch.
 void* mgn_hang_buffer();                       // host pointer == device pointer (UVA), or null if the allocation failed
+bool mgn_no_alloc_scope();                     // abi_core.cu: the calling entry point must not allocate
+void mgn_set_no_alloc_scope(bool on);
 static __device__ unsigned long long* g_mgn_hang_dev = nullptr;
 
 static inline cudaError_t mgn_register_hang_buffer(cudaStream_t stream) {
   static bool done = false;
   if (done) return cudaSuccess;
   void* h = mgn_hang_buffer();
+  if (h == nullptr && mgn_no_alloc_scope()) return cudaSuccess;  // not created yet and may not be: register later
   cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
   if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { (void)cudaGetLastError(); return cudaSuccess; }
   if (cs != cudaStreamCaptureStatusNone) return cudaSuccess;     // first launch under capture: try again later

@@ -485,3 +485,49 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   MGN_LAUNCH_CHECK();
   return mgn_launch_aggr_fixup(E, N, 32, receivers, rowptr, carry, aggr, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// mgn_edge_fwd_hl for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc): the same kernels, with the carry workspace of the deterministic aggregation in a file-scope
+// device array instead of a caller-provided buffer.  No counterpart in the
+// reference.
+//   * limit: E <= MGN_NOALLOC_MAX_EDGES (1,048,576 edges -> 32,768 slots x 512 B = 16 MiB of device memory, held by
+//     every GPU that loads the library until the process exits);
+//   * the array is shared by every call and keeps the last call's contents.  Nothing in it has to start at zero (a
+//     carry row is only read back if this launch wrote it), so nothing is cleared; two calls that overlap on the GPU
+//     (different streams, or graph branches) RACE on it -- serialise them;
+//   * calls no cudaMalloc / cudaFree / allocating routine: the device address of the array is looked up once per device
+//     with cudaGetSymbolAddress (the array's name is only a host-side handle in host code), and the library's lazily
+//     created hang-record buffer (abi_core.cu) is used if it exists but not created from here.
+static constexpr int64_t MGN_NOALLOC_MAX_EDGES = 1 << 20;
+static __device__ __align__(256) float g_noalloc_carry[(MGN_NOALLOC_MAX_EDGES / 32) * H];
+
+extern "C" int64_t mgn_noalloc_max_edges(void) { return MGN_NOALLOC_MAX_EDGES; }
+
+extern "C" int mgn_edge_fwd_hl_noalloc(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out,
+                                       void* lo_out, float* e_out, const void* P, const int32_t* senders,
+                                       const int32_t* receivers, float* aggr, const void* packed, const float* b2,
+                                       const float* b3, const float* b4, const float* scale, const int32_t* rowptr,
+                                       int norm_dim, void* stream_) {
+  if (E > MGN_NOALLOC_MAX_EDGES) {
+    mgn_set_error("edge_fwd_hl_noalloc: E = %lld exceeds the built-in scratch (%lld edges); use mgn_edge_fwd_hl with a "
+                  "caller-provided carry buffer", (long long)E, (long long)MGN_NOALLOC_MAX_EDGES);
+    return MGN_EWORKSPACE;
+  }
+  constexpr int MAX_DEV = 64;
+  static float* dev_ptr[MAX_DEV] = {};          // device address of g_noalloc_carry, per device
+  int dev = 0;
+  MGN_CUDA(cudaGetDevice(&dev));
+  MGN_CHECK_ARG(dev >= 0 && dev < MAX_DEV, "edge_fwd_hl_noalloc: device ordinal out of range");
+  if (dev_ptr[dev] == nullptr) {                // once per device, with that device current
+    float* ptr = nullptr;
+    MGN_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_carry));
+    MGN_CHECK_ARG(ptr != nullptr, "edge_fwd_hl_noalloc: cudaGetSymbolAddress returned null");
+    dev_ptr[dev] = ptr;
+  }
+  mgn_set_no_alloc_scope(true);
+  const int rc = mgn_edge_fwd_hl(E, N, hi_in, lo_in, hi_out, lo_out, e_out, P, senders, receivers, aggr, packed, b2, b3,
+                                 b4, scale, dev_ptr[dev], rowptr, norm_dim, stream_);
+  mgn_set_no_alloc_scope(false);
+  return rc;
+}

@@ -146,6 +146,18 @@ int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, 
                     float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
                     float* carry, const int32_t* rowptr, int norm_dim, void* stream);
+/* mgn_edge_fwd_hl without a caller-provided workspace and WITHOUT ANY ALLOCATION (no cudaMalloc / cudaFree / allocating
+ * routine), for callers that cannot allocate: code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it.  No counterpart in the reference.  The carry scratch is a file-scope
+ * device array of the library: E <= mgn_noalloc_max_edges() = 1,048,576 edges (16 MiB, held by every GPU that loads the
+ * library until exit); larger E returns -3 with a message.  Every call shares that array (contents of the last call
+ * remain; none of it needs clearing): calls that overlap on the GPU race -- serialise them.  Same results as
+ * mgn_edge_fwd_hl. */
+int64_t mgn_noalloc_max_edges(void);
+int mgn_edge_fwd_hl_noalloc(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
+                            float* e_out, const void* P, const int32_t* senders, const int32_t* receivers,
+                            float* aggr, const void* packed, const float* b2, const float* b3, const float* b4,
+                            const float* scale, const int32_t* rowptr, int norm_dim, void* stream);
 /* node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).  save_h* (optional, all three or
  * none) receive the hidden activations mgn_node_bwd needs as fp16 TILE IMAGES: ceil(N/128) * 32768 bytes each, one
  * 128-byte-swizzled 128 x 128 operand tile per 128 rows, bulk-stored as it sits in shared memory. */
