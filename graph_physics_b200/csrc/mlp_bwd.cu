@@ -462,7 +462,12 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     // upstream rows of this tile for the residual add, straight into the (now dead) sH2 + sH3 as a linear fp32 tile
     const long long row0 = tile * TILE_ROWS;
     const uint32_t tile_bytes = (uint32_t)(((p.E - row0) < TILE_ROWS ? (p.E - row0) : TILE_ROWS) * 512);
-    if (m.tid == 0 && p.g_eout != nullptr && p.rowmap == nullptr) {
+    // in place (g_e is the buffer g_eout lives in: the processor loop): g_e += dz1 We is ONE bulk reduce-add of the
+    // accumulator tile, performed at L2 -- the upstream rows are not fetched a second time (64 KB less shared-memory
+    // fill per tile, no wait for them, no read-modify-write of the staging tile).  Every element receives exactly one
+    // add, so the result does not depend on any ordering.
+    const bool red_inplace = FAST && p.g_e == p.g_eout;
+    if (m.tid == 0 && p.g_eout != nullptr && p.rowmap == nullptr && !red_inplace) {
       mbar_arrive_expect_tx(&bar_g, tile_bytes);
       bulk_g2s(lin32, p.g_eout + row0 * H, tile_bytes, &bar_g);
     }
@@ -496,16 +501,17 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
     // ---- g_e = g_eout + dz1 We
     if (p.rowmap == nullptr) {
       // accumulator added to the upstream tile in lin32 (or written there), then one bulk store of the tile
-      if (p.g_eout != nullptr) mbar_wait(&bar_g, it & 1);
+      if (p.g_eout != nullptr && !red_inplace) mbar_wait(&bar_g, it & 1);
       float v[32];
       tmem_ld32(tm_W + qoff, v);
       tmem_ld_wait();
-      if (p.g_eout != nullptr) add_row32_linear(lin32, m, v);
+      if (p.g_eout != nullptr && !red_inplace) add_row32_linear(lin32, m, v);
       else store_row32_linear(lin32, m, v);
       if (m.tid == 0) bulk_wait_read0();    // the dz1 image copy has read sH1
       tile_ready();
       if (m.tid == 0 && !(p.dbg_skip & 8)) {
-        bulk_s2g(p.g_e + row0 * H, lin32, tile_bytes, pol_stream);
+        if (red_inplace) bulk_red_add_f32(p.g_e + row0 * H, lin32, tile_bytes, pol_stream);
+        else bulk_s2g(p.g_e + row0 * H, lin32, tile_bytes, pol_stream);
         bulk_commit();
       }
     } else {

@@ -226,6 +226,7 @@ __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_
 // ------------------------------------------------------------------ developer timeline (tools/timeline.py)
 // When a buffer is registered (mgn_debug_set_timeline; host globals below), thread 0 of block 0 records clock64()
 // at the phase boundaries of its tiles.  Null (the default) costs one predicated load per stamp.
+#ifdef MGN_TIMELINE      // developer builds only: MGN_NVCC_EXTRA=-DMGN_TIMELINE python -m graph_physics_b200.build --force
 struct Timeline {
   long long* buf;
   int n, cap;
@@ -238,6 +239,12 @@ struct Timeline {
     if (buf != nullptr && n < cap) buf[n++] = clock64();
   }
 };
+#else                    // production: the stamps compile to nothing (they cost 2.6 % of edge_bwd's stall samples,
+struct Timeline {        // profiles/r02_ncu_kernels.md)
+  __device__ __forceinline__ void init(bool, long long*, int) {}
+  __device__ __forceinline__ void stamp() {}
+};
+#endif
 
 // ------------------------------------------------------------------ prefetch / misc
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }

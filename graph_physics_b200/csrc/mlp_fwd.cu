@@ -12,6 +12,8 @@
 // All products run on tcgen05 (fp16 operands, fp32 accumulation in TMEM); residual
 // streams, RMSNorm and the segmented sum are fp32.
 #define MGN_FILE_ID 1
+#include <algorithm>
+
 #include "mlp_v2.cuh"
 #include "mlp_fwd_abi.cuh"
 
@@ -584,6 +586,82 @@ __global__ void pack_block_kernel(const PackParams p) {
     pk.x = pack_h2(a.x, a.y); pk.y = pack_h2(a.z, a.w); pk.z = pack_h2(b.x, b.y); pk.w = pack_h2(b.z, b.w);
     *reinterpret_cast<uint4*>(p.out + byte) = pk;
   }
+}
+
+// ---- all blocks of a processor in one launch: grid.y = block index
+static constexpr int PACK_MAX_BLOCKS = 32;
+struct PackManyParams {
+  const float* w[PACK_MAX_BLOCKS][8];   // per block: edge_block.{0,2,4,6}.weight, node_block.{0,2,4,6}.weight
+  uint8_t* out;                         // [K][PK_BYTES]
+};
+
+__global__ void pack_blocks_kernel(const PackManyParams q) {
+  pdl_wait();
+  pdl_launch();
+  const int k = blockIdx.y;
+  PackParams p;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    p.eW[i] = q.w[k][i];
+    p.nW[i] = q.w[k][4 + i];
+  }
+  p.out = q.out + (size_t)k * PK_BYTES;
+  const int total_chunks = (int)(PK_BYTES / 16);
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < total_chunks; c += gridDim.x * blockDim.x) {
+    const int64_t byte = (int64_t)c * 16;
+    const float* src;
+    int ld, rows;
+    int64_t base;
+    if (byte < PK_WCAT) {
+      int ti = (int)(byte / 32768);
+      base = (int64_t)ti * 32768; rows = 128;
+      src = p.eW[ti]; ld = ti == 0 ? 384 : 128;
+    } else if (byte < PK_NODE) {
+      base = PK_WCAT; rows = 256; src = p.eW[0]; ld = 384;
+    } else if (byte < PK_NODE + 65536) {
+      base = PK_NODE; rows = 128; src = p.nW[0]; ld = 256;
+    } else {
+      int ti = (int)((byte - PK_NODE - 65536) / 32768);
+      base = PK_NODE + 65536 + (int64_t)ti * 32768; rows = 128; src = p.nW[1 + ti]; ld = 128;
+    }
+    const uint32_t off = (uint32_t)(byte - base);
+    const uint32_t panel = off / (rows * 128), rem = off % (rows * 128);
+    const uint32_t row = rem / 128, pchunk = (rem % 128) / 16;
+    const uint32_t col = panel * 64 + ((pchunk ^ (row & 7)) << 3);
+    int srow = row, scol = col;
+    if (base == PK_WCAT) {
+      srow = row & 127;
+      scol = col + (row < 128 ? 128 : 256);
+    }
+    const float* sp = src + (int64_t)srow * ld + scol;
+    float4 a = __ldg(reinterpret_cast<const float4*>(sp)), b = __ldg(reinterpret_cast<const float4*>(sp + 4));
+    uint4 pk;
+    pk.x = pack_h2(a.x, a.y); pk.y = pack_h2(a.z, a.w); pk.z = pack_h2(b.x, b.y); pk.w = pack_h2(b.z, b.w);
+    *reinterpret_cast<uint4*>(p.out + byte) = pk;
+  }
+}
+
+// K blocks in one launch per 32 blocks.  weights_host: HOST array of K * 8 DEVICE pointers, per block
+// edge_block.{0,2,4,6}.weight then node_block.{0,2,4,6}.weight (fp32, the nn.Linear layout); packed: [K][packed bytes].
+extern "C" int mgn_pack_blocks(int K, const float* const* weights_host, void* packed, void* stream) {
+  MGN_CHECK_ARG(K > 0 && weights_host && packed, "pack_blocks: bad args");
+  for (int k0 = 0; k0 < K; k0 += PACK_MAX_BLOCKS) {
+    const int kn = std::min(PACK_MAX_BLOCKS, K - k0);
+    PackManyParams q{};
+    for (int k = 0; k < kn; ++k)
+      for (int i = 0; i < 8; ++i) {
+        q.w[k][i] = weights_host[(size_t)(k0 + k) * 8 + i];
+        MGN_CHECK_ARG(q.w[k][i] != nullptr, "pack_blocks: null weight pointer");
+      }
+    q.out = (uint8_t*)packed + (size_t)k0 * PK_BYTES;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(22, (unsigned)kn);
+    cfg.blockDim = dim3(256);
+    cfg.stream = (cudaStream_t)stream;
+    MGN_CUDA(cudaLaunchKernelEx(&cfg, pack_blocks_kernel, q));
+    MGN_LAUNCH_CHECK();
+  }
+  return MGN_OK;
 }
 
 extern "C" int64_t mgn_packed_block_bytes(void) { return PK_BYTES; }

@@ -109,15 +109,26 @@ __device__ __forceinline__ void epi_bias_relu_tmem_q(uint32_t taddr, uint32_t ta
   store_row_chunk_tmem(taddr_a, v, save, grow, m.c0);
 }
 
-// ReLU backward in place: tile holds h = relu(z); overwrite with fp16(acc * [h > 0])
+// ReLU backward in place: tile holds h = relu(z); overwrite with fp16(acc * [h > 0]).  The mask is applied to the
+// PACKED result (h > 0 per half -> 0xFFFF / 0 by one HSET2 per pair, one AND): no fp16 -> fp32 unpacking of h, no
+// per-element select; same bits as fp16(h > 0 ? acc : 0).
 __device__ __forceinline__ void epi_relu_mask_q(uint32_t taddr, uint8_t* tile, const Map& m) {
-  float v[32], h[32];
+  float v[32];
   tmem_ld32(taddr, v);
-  load_row_chunk_f16(tile, 128, m.row, m.c0, h);
-  tmem_ld_wait();
+  uint4 hw[4];
 #pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = h[j] > 0.f ? v[j] : 0.f;
-  store_row_chunk_f16(tile, 128, m.row, m.c0, v);
+  for (int j = 0; j < 4; ++j) hw[j] = *reinterpret_cast<const uint4*>(tile + tile_off(128, m.row, m.c0 + 8 * j));
+  tmem_ld_wait();
+  const __half2 zero2 = __float2half2_rn(0.f);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t h[4] = {hw[j].x, hw[j].y, hw[j].z, hw[j].w};
+    uint32_t o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      o[i] = pack_h2(v[8 * j + 2 * i], v[8 * j + 2 * i + 1]) & __hgt2_mask(*reinterpret_cast<const __half2*>(&h[i]), zero2);
+    *reinterpret_cast<uint4*>(tile + tile_off(128, m.row, m.c0 + 8 * j)) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
 }
 
 // accumulator quarter -> fp32 staging tile (stage_off layout, 64 KB)

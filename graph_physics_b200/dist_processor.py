@@ -54,9 +54,7 @@ class PartitionEngine:
         dev = x_owned.device
         self.dev, self.E = dev, e_local.shape[0]
         self.packed = torch.empty((K, ops.packed_block_bytes()), dtype=torch.uint8, device=dev)
-        for k in range(K):
-            b = self.prm[k]
-            _timed("pack", ops.pack_block, [b[i] for i in _E_W], [b[i] for i in _N_W], out=self.packed[k])
+        _timed("pack", ops.pack_blocks, [[b[i] for i in _E_W + _N_W] for b in self.prm], out=self.packed)
         x0 = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
         x0[:part.num_owned] = x_owned.detach()
         self.xs: List[Optional[torch.Tensor]] = [x0]

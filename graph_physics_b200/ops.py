@@ -42,6 +42,24 @@ def pack_block(edge_w: Sequence[torch.Tensor], node_w: Sequence[torch.Tensor],
     return out
 
 
+def pack_blocks(blocks: Sequence[Sequence[torch.Tensor]], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """All blocks of a processor in ONE launch.  blocks[k] = the 8 weights of block k (edge_block.{0,2,4,6}.weight,
+    node_block.{0,2,4,6}.weight) -> uint8 [K, packed_block_bytes]."""
+    K = len(blocks)
+    L.require_device(blocks[0][0])
+    keep = []
+    for ws in blocks:
+        if tuple(ws[0].shape) != (H, 3 * H) or tuple(ws[4].shape) != (H, 2 * H) or \
+                any(tuple(w.shape) != (H, H) for w in list(ws[1:4]) + list(ws[5:8])):
+            raise ValueError("libmgn_b200 packs hidden_size=128 blocks (3H / 2H first layers) only")
+        keep.append([_f32c(w.detach()) for w in ws])
+    if out is None:
+        out = torch.empty((K, packed_block_bytes()), dtype=torch.uint8, device=blocks[0][0].device)
+    arr = (L.ctypes.c_void_p * (8 * K))(*[w.data_ptr() for ws in keep for w in ws])
+    L.check(L.lib().mgn_pack_blocks(L.i32(K), arr, L.p(out), L.stream()))
+    return out
+
+
 def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
           out: Optional[torch.Tensor] = None) -> torch.Tensor:
     N = x.shape[0]

@@ -126,9 +126,7 @@ class _ProcessorFn(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad)   # False under torch.no_grad() / all-frozen inputs
         prm = [p.detach().contiguous() for p in params]
         packed = torch.empty((K, ops.packed_block_bytes()), dtype=torch.uint8, device=dev)
-        for k in range(K):
-            b = prm[18 * k:18 * (k + 1)]
-            _timed("pack", ops.pack_block, [b[i] for i in _E_W], [b[i] for i in _N_W], out=packed[k])
+        _timed("pack", ops.pack_blocks, [[prm[18 * k + i] for i in _E_W + _N_W] for k in range(K)], out=packed)
         x = x0.detach().contiguous()
         # edges run in receiver-sorted (CSR) order inside the loop; the first edge kernel gathers its input rows
         # through the permutation (no separate pass over the edge stream)
@@ -259,12 +257,14 @@ class _ProcessorFn(torch.autograd.Function):
                 _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
             _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k])
             gx, gx_new = gx_new, gx
-            grads[k].mul_(inv_s)
-            if GRAD_SYNC is not None:
+            if GRAD_SYNC is not None:        # the reduction of block k starts now: it needs the final values
+                grads[k].mul_(inv_s)
                 GRAD_SYNC(grads[k], k)
             # release what this step saved
             ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None; e16s[k] = None
             xs[k + 1] = None
+        if GRAD_SYNC is None:
+            grads.mul_(inv_s)                # one launch for all blocks
         if GRAD_SYNC is not None and hasattr(GRAD_SYNC, "finish"):
             # the reductions started per block must be complete (in stream order) before autograd hands the views
             # below to AccumulateGrad: with an existing .grad it would otherwise add partly reduced values

@@ -107,6 +107,9 @@ int64_t mgn_packed_block_bytes(void);
 int mgn_pack_block(const float* eW1, const float* eW2, const float* eW3, const float* eW4,
                    const float* nW1, const float* nW2, const float* nW3, const float* nW4,
                    void* packed, void* stream);
+/* the same for K blocks in one launch: weights_host = HOST array of K * 8 DEVICE pointers (per block the eight
+ * arguments of mgn_pack_block in order); packed = [K][mgn_packed_block_bytes()] */
+int mgn_pack_blocks(int K, const float* const* weights_host, void* packed, void* stream);
 /* P [N,256] fp16 = [x W_i^T + b1 | x W_j^T]: the x_i / x_j columns of edge_block layer 1
  * (cat order [edge_attr, x_i, x_j], layers.py:703-719). */
 int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P, void* stream);

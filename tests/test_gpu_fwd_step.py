@@ -248,3 +248,20 @@ def test_deterministic_aggregation_hubs_and_isolated_nodes(hub_degree):
                              rowptr=csr.rowptr)
     torch.cuda.synchronize()
     assert torch.equal(aggr2, aggr2b) and torch.equal(aggr1, aggr1b)
+
+
+def test_pack_blocks_equals_pack_block():
+    """mgn_pack_blocks (all blocks, one launch) writes the same bytes as K calls of mgn_pack_block."""
+    from graph_physics_b200 import ops
+    dev = "cuda"
+    torch.manual_seed(3)
+    K = 5
+    blocks = []
+    for _ in range(K):
+        ew = [torch.randn(128, 384, device=dev)] + [torch.randn(128, 128, device=dev) for _ in range(3)]
+        nw = [torch.randn(128, 256, device=dev)] + [torch.randn(128, 128, device=dev) for _ in range(3)]
+        blocks.append(ew + nw)
+    many = ops.pack_blocks(blocks)
+    for k in range(K):
+        one = ops.pack_block(blocks[k][:4], blocks[k][4:])
+        assert torch.equal(many[k], one), k
