@@ -11,7 +11,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmgn_b200.so")
+# MGN_LIB_PATH: developer override (e.g. a -DMGN_TIMELINE build kept next to the production library)
+LIB_PATH = os.environ.get("MGN_LIB_PATH") or os.path.join(_HERE, "libmgn_b200.so")
 
 _lib = None
 _device_ok = False

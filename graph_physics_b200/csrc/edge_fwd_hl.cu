@@ -36,6 +36,8 @@ struct EdgeHLParams {
   float* carry;             // [ceil(E/32),128] fp32: partial sums of runs that continue from an earlier 32-row slot
                             // (deterministic aggregation, aggr_fixup_kernel below)
   float inv_sqrt_d;         // RMSNorm: d^-1/2 of the TRUE hidden size (zero-padded narrower models, ops.py)
+  __half* h_save[3];        // training: tile images of the hidden activations h1, h2, h3 (what mgn_edge_bwd_saved starts
+                            // from instead of recomputing them), all three or all null
   const __half* W;          // We, W2, W3, W4 tiles
   const float* b2;
   const float* b3;
@@ -45,6 +47,12 @@ struct EdgeHLParams {
   int dbg_cap;
 };
 
+// SAVE (training): the hidden activations h1, h2, h3 also leave as tile images.  They are staged in shared-memory tiles
+// that are idle at that point -- h1 in sHi (its hi chunks are parked in tensor memory), h2 in sLo (the remainder tile
+// is only needed after the last product), h3 in sHi again -- so that every 32 KB copy has two layer times to read its
+// tile before the tile is written again; the loads of lo (this tile) and hi (next tile) follow those copies, and the
+// next tile's first product is issued after the scan instead of before it.
+template <bool SAVE>
 __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
@@ -122,10 +130,25 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     phase ^= 1;
     fence_after_sync();
   };
+  constexpr bool save = SAVE;
   auto acts_ready = [&]() {       // the TMEM-resident activations (and parked rows) of every warp are written
     tmem_st_wait();
+    if (save) fence_async_smem();               // ... and the copy of them in sHi is visible to the bulk-copy engine
     fence_before_sync();
     __syncthreads();
+  };
+  // training: the hidden activation chunk of this thread (32 fp32 -> 16 packed words) also goes to its place in sHi
+  auto save_chunk = [&](uint8_t* dst, const float (&v)[32]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<uint4*>(dst + tile_off(128, m.row, m.c0 + 8 * j)) =
+          make_uint4(pack_h2(v[8 * j], v[8 * j + 1]), pack_h2(v[8 * j + 2], v[8 * j + 3]),
+                     pack_h2(v[8 * j + 4], v[8 * j + 5]), pack_h2(v[8 * j + 6], v[8 * j + 7]));
+  };
+  // thread 0: staging tile -> image `which` of tile `tile_` (its own bulk group)
+  auto store_save = [&](int which, long long tile_, const uint8_t* src) {
+    bulk_s2g(reinterpret_cast<uint8_t*>(p.h_save[which]) + (size_t)tile_ * TILE_BYTES, src, TILE_BYTES, pol_stream);
+    bulk_commit();
   };
   // indices, requested one tile ahead: this thread's row (epilogue mapping) -> receiver; coalesced mapping (lane j < 8
   // of warp w stands for tile row 8w + j) -> sender
@@ -222,15 +245,22 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
         for (int i = 0; i < 8; ++i) v[8 * j + i] = fmaxf(v[8 * j + i] + a[i] + b[i], 0.f);
       }
       store_row_chunk_tmem(taddr_a, v, nullptr, 0, m.c0);
+      if (save) save_chunk(sHi, v);            // this thread's hi chunk is parked: the same bytes of sHi take h1
     }
     acts_ready();
     if (m.tid == 0) {
       fence_after_sync();
       umma_tile_ts(tmem_acc, tmem_a, sW_u32 + TILE_BYTES, 128, 0, 0, 128, 8, 0);
-      mma_commit(&mbar);
-      if (has_next) issue_hi(k + 1);           // the hi tile is parked: next tile's operand image, three products ahead
-      if (k > 0) bulk_wait_read0();            // the previous tile's stores have read sLo / sOut
-      issue_lo(k);
+      if (!save) {
+        mma_commit(&mbar);
+        if (has_next) issue_hi(k + 1);         // the hi tile is parked: next tile's operand image, three products ahead
+        if (k > 0) bulk_wait_read0();          // the previous tile's stores have read sLo / sOut
+        issue_lo(k);
+      } else {
+        if (k > 0) bulk_wait_read0();          // the previous tile's stores have read sLo (the next epilogue puts h2
+        mma_commit(&mbar);                     // there) and sOut; issued a scan + an epilogue ago: no wait in practice
+        store_save(0, tile, sHi);
+      }
     }
     tl.stamp();   // 2 layer-1 epilogue done
 
@@ -240,12 +270,36 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
       float4 bb[8];
       vec32(layer == 1 ? 0 : 1, bb);
       mma_wait();
-      epi_bias_relu_tmem_q(taddr, taddr_a, bb, m, nullptr, 0);
+      {
+        float v[32];
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[4 * j + 0] = fmaxf(v[4 * j + 0] + bb[j].x, 0.f);
+          v[4 * j + 1] = fmaxf(v[4 * j + 1] + bb[j].y, 0.f);
+          v[4 * j + 2] = fmaxf(v[4 * j + 2] + bb[j].z, 0.f);
+          v[4 * j + 3] = fmaxf(v[4 * j + 3] + bb[j].w, 0.f);
+        }
+        store_row_chunk_tmem(taddr_a, v, nullptr, 0, m.c0);
+        if (save) save_chunk(layer == 1 ? sLo : sHi, v);     // h2 -> sLo, h3 -> sHi
+      }
       acts_ready();
       if (m.tid == 0) {
         fence_after_sync();
         umma_tile_ts(tmem_acc, tmem_a, sW_u32 + (uint32_t)(layer + 1) * TILE_BYTES, 128, 0, 0, 128, 8, 0);
-        mma_commit(&mbar);
+        if (!save) {
+          mma_commit(&mbar);
+        } else if (layer == 1) {
+          store_save(1, tile, sLo);
+          bulk_wait_read1();                   // the copy of h1 (two layers old) has read sHi: the epilogue of the
+          mma_commit(&mbar);                   // product just issued writes h3 there
+        } else {
+          mma_commit(&mbar);
+          store_save(2, tile, sHi);
+          bulk_wait_read1();                   // the copy of h2 has read sLo (this wait runs under product 4) ...
+          issue_lo(k);                         // ... the remainder tile lands there for the residual
+        }
       }
       // the output tile is idle (thread 0 saw the previous tile's stores leave it before this barrier): the next
       // tile's P_j rows land there under products 3 and 4
@@ -325,12 +379,16 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     __syncthreads();
     tl.stamp();   // 5 new images staged
     if (m.tid == 0) {
+      if (save) {
+        bulk_wait_read0();                     // the copy of h3 (a product, the norm and the images old) has read sHi
+        if (has_next) issue_hi(k + 1);
+      }
       if (p.hi_out != nullptr) {
         bulk_s2g(reinterpret_cast<uint8_t*>(p.hi_out) + (size_t)tile * TILE_BYTES, sOut, TILE_BYTES, pol_stream);
         bulk_s2g(reinterpret_cast<uint8_t*>(p.lo_out) + (size_t)tile * TILE_BYTES, sLo, TILE_BYTES, pol_stream);
       }
       bulk_commit();
-      if (has_next) issue_l1(k + 1);           // every thread has read the accumulator: next tile's product 1
+      if (!save && has_next) issue_l1(k + 1);  // every thread has read the accumulator: next tile's product 1
     }
     tl.stamp();   // 6 stores + next product 1 issued
     // ---- next tile's indices / P rows, then the segmented sum of y over the receivers (sorted: runs of lanes)
@@ -354,6 +412,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
         }
       }
       tl.stamp();   // 8 scan done
+      if (save && m.tid == 0 && has_next) issue_l1(k + 1);   // hi (requested before the scan) has landed
       const int dn = __shfl_down_sync(0xffffffffu, key, 1);
       const int key0 = __shfl_sync(0xffffffffu, key, 0);
       if (rvalid && (m.lane == 31 || dn != key)) {       // last lane of a run holds its sum over this slot
@@ -456,7 +515,7 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
                                float* e_out, const void* P, const int32_t* senders, const int32_t* receivers,
                                float* aggr, const void* packed, const float* b2, const float* b3, const float* b4,
                                const float* scale, float* carry, const int32_t* rowptr, int norm_dim,
-                               void* stream_) {
+                               void* h1_save, void* h2_save, void* h3_save, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(E >= 0 && N > 0 && aggr, "edge_fwd_hl: bad sizes");
   if (rowptr == nullptr || E == 0) MGN_CUDA(cudaMemsetAsync(aggr, 0, sizeof(float) * N * H, stream));
@@ -473,15 +532,20 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "edge_fwd_hl: norm_dim must be in 1..128");
   p.carry = carry; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
+  MGN_CHECK_ARG((h1_save == nullptr) == (h2_save == nullptr) && (h1_save == nullptr) == (h3_save == nullptr),
+                "edge_fwd_hl: the three hidden-activation saves go together");
+  p.h_save[0] = (__half*)h1_save; p.h_save[1] = (__half*)h2_save; p.h_save[2] = (__half*)h3_save;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
-    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
     attr = true;
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
-  MGN_CUDA(mgn_launch(edge_fwd_hl_kernel, grid, NT, EDGE_HL_SMEM, stream, p));
+  if (h1_save != nullptr) MGN_CUDA(mgn_launch(edge_fwd_hl_kernel<true>, grid, NT, EDGE_HL_SMEM, stream, p));
+  else MGN_CUDA(mgn_launch(edge_fwd_hl_kernel<false>, grid, NT, EDGE_HL_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return mgn_launch_aggr_fixup(E, N, 32, receivers, rowptr, carry, aggr, stream);
 }
@@ -527,7 +591,7 @@ extern "C" int mgn_edge_fwd_hl_noalloc(int64_t E, int64_t N, const void* hi_in, 
   }
   mgn_set_no_alloc_scope(true);
   const int rc = mgn_edge_fwd_hl(E, N, hi_in, lo_in, hi_out, lo_out, e_out, P, senders, receivers, aggr, packed, b2, b3,
-                                 b4, scale, dev_ptr[dev], rowptr, norm_dim, stream_);
+                                 b4, scale, dev_ptr[dev], rowptr, norm_dim, nullptr, nullptr, nullptr, stream_);
   mgn_set_no_alloc_scope(false);
   return rc;
 }

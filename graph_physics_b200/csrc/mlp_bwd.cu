@@ -74,6 +74,52 @@ __device__ __forceinline__ float rmsnorm_bwd_q(uint32_t taddr, const float4 (&bb
   return warp_colsum32(g, m.lane);
 }
 
+// Same with ONE exchange of the two row sums across the four column quarters: (sum z^2, sum scale g z) go as a float2
+// through `scratch` ([4][128] float2 = 4 KB of shared memory that nothing else touches until the caller's next
+// barrier) -- one barrier instead of four.
+__device__ __forceinline__ float rmsnorm_bwd_q2(uint32_t taddr, const float4 (&bb)[8], const float4 (&sc)[8],
+                                                uint8_t* gtile, float2* scratch, const Map& m, float inv_sqrt_d,
+                                                float norm_d) {
+  float z[32], g[32];
+  tmem_ld32(taddr, z);
+  load_row_chunk_f16(gtile, 128, m.row, m.c0, g);
+  tmem_ld_wait();
+  float ss = 0.f, dot = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float b_[4] = {bb[j].x, bb[j].y, bb[j].z, bb[j].w};
+    const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      z[4 * j + i] += b_[i];
+      ss += z[4 * j + i] * z[4 * j + i];
+      dot += s_[i] * g[4 * j + i] * z[4 * j + i];
+    }
+  }
+  scratch[m.cq * 128 + m.row] = make_float2(ss, dot);
+  __syncthreads();
+  {
+    const float2 a = scratch[m.row], b = scratch[128 + m.row], c = scratch[256 + m.row], d = scratch[384 + m.row];
+    ss = (a.x + b.x) + (c.x + d.x);          // same association as row_sum4
+    dot = (a.y + b.y) + (c.y + d.y);
+  }
+  const float r = sqrtf(ss) * inv_sqrt_d;
+  const float inv = 1.0f / (r + RMS_EPS);
+  const float k = r > 0.f ? dot * inv * inv / (norm_d * r) : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float s_[4] = {sc[j].x, sc[j].y, sc[j].z, sc[j].w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float zz = z[4 * j + i], gg = g[4 * j + i];
+      z[4 * j + i] = s_[i] * gg * inv - zz * k;
+      g[4 * j + i] = gg * zz * inv;
+    }
+  }
+  store_row_chunk_f16(gtile, 128, m.row, m.c0, z);
+  return warp_colsum32(g, m.lane);
+}
+
 // ===================================================================================== edge
 struct EdgeBwdParams {
   long long E;
@@ -556,6 +602,304 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   atomicAdd(p.grad + GB_E_SC + m.c0 + m.lane, dsc);
   tl.stamp();   // flush issued
 
+  fence_before_sync();
+  __syncthreads();
+  if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
+}
+
+// ===================================================================================== edge, from saved activations
+// The processor loop's edge backward when the forward kept the edge MLP's hidden activations (mgn_edge_fwd_hl h*_save):
+// no recompute of layers 1-3, no gathers of P, no e image -- the tile starts at z4 = h3 W4^T (needed by the RMSNorm
+// backward), then the same dgrad / wgrad chain as edge_bwd_kernel.  g_e is updated IN PLACE: the upstream rows are
+// read once (bulk copy, for the operand g = fp16(g_e + g_aggr[receiver])) and g_e += dz1 We leaves as one bulk
+// reduce-add performed at L2.  Shared memory (7 x 32 KB):
+//   sA  W4 (R4, D4) <-> W2 (D2)        sB  W3 (resident)
+//   sH1 h1 -> dz1 | sC We              together: landing zone of the upstream fp32 tile (64 KB) before h1 / We arrive
+//   sH3 h3 -> dz3
+//   sH2 h2 -> dz2 | sG g -> dz4        together: row-linear fp32 staging of the g_e tile (64 KB) after D2
+// The product R4 of the NEXT tile is issued before the tile boundary (its operands h3, W4 are loaded as soon as their
+// slots die), so it runs under the reduce-add's read-out, the upstream wait and the build of g.
+struct EdgeBwdSavedParams {
+  long long E;
+  const __half* h1;         // tile images of the hidden activations (32 KB per 128-row tile)
+  const __half* h2;
+  const __half* h3;
+  const float* g_aggr;      // [N,128]
+  const int32_t* receivers;
+  float* g_e;               // [E,128] in: upstream gradient, out: g_e + dz1 We (in place)
+  __half* dz16_out;         // tile images of dz1
+  const __half* W;          // packed edge tiles We, W2, W3, W4
+  const float* b4;
+  const float* scale;
+  float* grad;
+  float inv_sqrt_d, norm_d;
+  long long* dbg;           // developer timeline (MGN_TIMELINE builds)
+  int dbg_cap;
+};
+
+__global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSavedParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  check_smem_alignment(smem);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + SLOT;
+  uint8_t* sH1 = smem + 2 * SLOT;
+  uint8_t* sC = smem + 3 * SLOT;
+  uint8_t* sH3 = smem + 4 * SLOT;
+  uint8_t* sH2 = smem + 5 * SLOT;
+  uint8_t* sG = smem + 6 * SLOT;
+  uint8_t* lin_in = sH1;            // sH1 + sC
+  uint8_t* lin_out = sH2;           // sH2 + sG
+  Tail2* tail = reinterpret_cast<Tail2*>(smem + 7 * SLOT);
+  uint64_t& bar_wA = tail->bar[0];
+  uint64_t& bar_wB = tail->bar[1];
+  uint64_t& bar_mma = tail->bar[2];
+  uint64_t& bar_wC = tail->bar[3];
+  uint64_t& bar_up = tail->bar[4];
+  uint64_t& bar_h3 = tail->bar[5];
+  uint64_t& bar_h2 = tail->bar[6];
+  uint64_t& bar_h1 = tail->bar[7];
+  uint32_t& tmem_slot = tail->tmem_slot;
+  const Map m = make_map();
+  if (m.tid == 0) {
+    for (int i = 0; i < 8; ++i) mbar_init(&tail->bar[i], 1);
+    mbar_init_fence();
+  }
+  if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  pdl_wait();
+  pdl_launch();
+  const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
+  const uint32_t qoff = m.lane_off + m.c0;
+  const long long num_tiles = (p.E + TILE_ROWS - 1) / TILE_ROWS;
+  const uint32_t uA = smem_u32(sA), uB = smem_u32(sB), uC = smem_u32(sC), uH1 = smem_u32(sH1), uH2 = smem_u32(sH2),
+                 uH3 = smem_u32(sH3), uG = smem_u32(sG);
+  const uint64_t pol_stream = policy_evict_first();
+  const uint64_t pol_keep = policy_evict_last();
+  uint32_t phase = 0;
+  float dsc = 0.f;
+  float db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
+  auto mma_wait = [&]() {
+    mbar_wait(&bar_mma, phase);
+    phase ^= 1;
+    fence_after_sync();
+  };
+  auto tile_ready = [&]() {
+    fence_async_smem();
+    fence_before_sync();
+    __syncthreads();
+  };
+  auto tile_rows_bytes = [&](long long tile_) -> uint32_t {
+    const long long r0 = tile_ * TILE_ROWS;
+    return (uint32_t)(((p.E - r0) < TILE_ROWS ? (p.E - r0) : TILE_ROWS) * 512);
+  };
+  // Bulk LOADS (non-blocking) are issued by thread 32, so that they overlap thread 0's product issue; bulk STORES and
+  // the waits for their read-out stay with thread 0 (a bulk group can only be waited for by the thread that made it).
+  const bool loader = m.tid == 32;
+  auto load_img = [&](uint8_t* dst, const __half* img, long long tile_, uint64_t* bar) {      // one thread
+    mbar_arrive_expect_tx(bar, SLOT);
+    bulk_g2s(dst, reinterpret_cast<const uint8_t*>(img) + (size_t)tile_ * SLOT, SLOT, bar);
+  };
+  auto load_upstream = [&](long long tile_) {                                                 // thread 0
+    mbar_arrive_expect_tx(&bar_up, tile_rows_bytes(tile_));
+    bulk_g2s(lin_in, p.g_e + tile_ * TILE_ROWS * H, tile_rows_bytes(tile_), &bar_up);
+  };
+  auto issue_r4 = [&](uint32_t it_) {        // thread 0: z4 = h3 W4^T of the CTA's it_-th tile
+    mbar_wait(&bar_wA, 0);                   // W4: completions 0, 2, 4, ... of slot A
+    mbar_wait(&bar_h3, it_ & 1);
+    fence_after_sync();
+    umma_tile(tm_W, uH3, 128, 0, uA, 128, 0, 0, 128, 8, 0);
+    mma_commit(&bar_mma);
+  };
+  // this thread's row of the tile -> receiver (or -1 past the end); its g_aggr chunks, rotated by lane & 7 (g build)
+  auto load_rcv = [&](long long tile_) -> int {
+    const long long go = tile_ * TILE_ROWS + m.row;
+    return (tile_ < num_tiles && go < p.E) ? __ldg(p.receivers + go) : -1;
+  };
+  float4 gag[8];
+  auto load_gag = [&](int rcv) {
+    const int kx = m.lane & 7;
+    const float* ga = p.g_aggr + (long long)(rcv >= 0 ? rcv : 0) * H + m.c0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+      gag[c] = rcv >= 0 ? ld_f4_hint(ga + 4 * (c ^ kx), pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
+  };
+
+  // b4 and scale live in the tail's 2 KB scratch (unused here: the row sums go through sH1): the norm backward reads
+  // them from shared memory instead of issuing 16 global loads per thread and tile behind the tile's other traffic
+  float* svec = tail->red;                   // [0,128) b4, [128,256) scale
+  if (m.tid < 128) {
+    svec[m.tid] = __ldg(p.b4 + m.tid);
+    svec[128 + m.tid] = __ldg(p.scale + m.tid);
+  }
+  __syncthreads();
+  // ---- prologue
+  const long long tile0 = blockIdx.x;
+  if (loader) {
+    load_w_slot(sA, p.W, 3, &bar_wA);      // W4
+    load_img(sH3, p.h3, tile0, &bar_h3);
+    load_upstream(tile0);
+    load_w_slot(sB, p.W, 2, &bar_wB);      // W3
+    load_img(sH2, p.h2, tile0, &bar_h2);
+  }
+  int rcv_cur = load_rcv(tile0);
+  int rcv_nxt = load_rcv(tile0 + gridDim.x);
+  if (m.tid == 0) issue_r4(0);
+  Timeline tl;
+  tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
+
+  uint32_t it = 0;
+  for (long long tile = tile0; tile < num_tiles; tile += gridDim.x, ++it) {
+    const bool has_next = tile + gridDim.x < num_tiles;
+    const long long row0 = tile * TILE_ROWS;
+    // ---- G: the previous tile's g_e staging (sH2 + sG) has been read out -> h2 may land, sG may be written
+    tl.stamp();   // 0 tile top
+    load_gag(rcv_cur);                       // in flight under the waits below
+    if (it > 0) {
+      if (m.tid == 0) bulk_wait_read0();
+      __syncthreads();
+      if (loader) load_img(sH2, p.h2, tile, &bar_h2);
+    }
+    tl.stamp();   // 1 staging read out
+    {
+      const int kx = m.lane & 7;
+      const bool ok = rcv_cur >= 0;
+      mbar_wait(&bar_up, it & 1);
+      tl.stamp();   // 2 upstream landed
+      const uint8_t* base = lin_in + m.row * 512 + m.c0 * 4;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float4 u = ok ? *reinterpret_cast<const float4*>(base + 16 * (c ^ kx)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        uint2 pk;
+        pk.x = pack_h2(u.x + gag[c].x, u.y + gag[c].y);
+        pk.y = pack_h2(u.z + gag[c].z, u.w + gag[c].w);
+        *reinterpret_cast<uint2*>(sG + tile_off(128, m.row, m.c0 + 4 * (c ^ kx))) = pk;
+      }
+    }
+    tile_ready();                            // g is complete; the landing zone is free
+    tl.stamp();   // 3 g built
+    // ---- R4 (issued before the tile boundary) + RMSNorm backward: sG <- dz4
+    {
+      float4 bb[8], sc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        bb[j] = *reinterpret_cast<const float4*>(svec + m.c0 + 4 * j);
+        sc[j] = *reinterpret_cast<const float4*>(svec + 128 + m.c0 + 4 * j);
+      }
+      mma_wait();
+      tl.stamp();   // 4 R4 product done
+      // the landing zone (sH1 + sC) is idle until h1 / We are requested below: its first 4 KB carry the row sums
+      dsc += rmsnorm_bwd_q2(tm_W + qoff, bb, sc, sG, reinterpret_cast<float2*>(sH1), m, p.inv_sqrt_d, p.norm_d);
+      tile_ready();
+    }
+    tl.stamp();   // 5 norm backward done
+    if (loader) {                            // needed by D2 / D1, two and three products from here
+      load_img(sH1, p.h1, tile, &bar_h1);
+      load_w_slot(sC, p.W, 0, &bar_wC);      // We
+      if (has_next) {                        // next tile's streams into L2
+        const long long nt = tile + gridDim.x;
+        bulk_prefetch_l2(p.g_e + nt * TILE_ROWS * H, tile_rows_bytes(nt));
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h3) + (size_t)nt * SLOT, SLOT);
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h2) + (size_t)nt * SLOT, SLOT);
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h1) + (size_t)nt * SLOT, SLOT);
+      }
+    }
+    // ---- D4: g_h3 = dz4 W4 ; dW4 += dz4^T h3
+    if (m.tid == 0) {
+      fence_after_sync();
+      umma_tile(tm_W, uG, 128, 0, uA, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW4, uG, 128, 1, uH3, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sG, m.tid, db4a, db4b);
+    mma_wait();
+    if (loader) load_w_slot(sA, p.W, 1, &bar_wA);            // W4 is done: W2 -> A
+    epi_relu_mask_q(tm_W + qoff, sH3, m);                    // sH3 <- dz3
+    tile_ready();
+    tl.stamp();   // 6 D4 done
+    // ---- D3
+    if (m.tid == 0) {
+      if (it == 0) mbar_wait(&bar_wB, 0);
+      mbar_wait(&bar_h2, it & 1);
+      fence_after_sync();
+      umma_tile(tm_W, uH3, 128, 0, uB, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW3, uH3, 128, 1, uH2, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sH3, m.tid, db3a, db3b);
+    mma_wait();
+    epi_relu_mask_q(tm_W + qoff, sH2, m);                    // sH2 <- dz2
+    tile_ready();
+    tl.stamp();   // 7 D3 done
+    // sH3 is dead (D3 complete, every thread past its column sums): the next tile's h3
+    if (loader && has_next) load_img(sH3, p.h3, tile + gridDim.x, &bar_h3);
+    // ---- D2
+    if (m.tid == 0) {
+      mbar_wait(&bar_wA, 1);                 // W2: completions 1, 3, 5, ... of slot A
+      mbar_wait(&bar_h1, it & 1);
+      fence_after_sync();
+      umma_tile(tm_W, uH2, 128, 0, uA, 128, 1, 0, 128, 8, 0);
+      umma_tile(tm_dW2, uH2, 128, 1, uH1, 128, 1, 0, 128, 8, it > 0);
+      mma_commit(&bar_mma);
+    }
+    tile_colsum_q(sH2, m.tid, db2a, db2b);
+    mma_wait();
+    if (loader && has_next) load_w_slot(sA, p.W, 3, &bar_wA);       // W2 is done: the next tile's W4
+    epi_relu_mask_q(tm_W + qoff, sH1, m);                    // sH1 <- dz1
+    tile_ready();
+    tl.stamp();   // 8 D2 done
+    if (m.tid == 0) {                        // dz1 leaves as its operand tile (dp_gather, edge_wgrad1 read the images)
+      bulk_s2g(reinterpret_cast<uint8_t*>(p.dz16_out) + (size_t)tile * SLOT, sH1, SLOT, pol_keep);
+      bulk_commit();
+    }
+    // ---- D1: dz1 We
+    if (m.tid == 0) {
+      mbar_wait(&bar_wC, it & 1);
+      fence_after_sync();
+      umma_tile(tm_W, uH1, 128, 0, uC, 128, 1, 0, 128, 8, 0);
+      mma_commit(&bar_mma);
+    }
+    rcv_cur = rcv_nxt;
+    rcv_nxt = load_rcv(tile + 2 * (long long)gridDim.x);
+    mma_wait();
+    tl.stamp();   // 9 D1 done
+    if (m.tid == 0) {
+      bulk_wait_read0();                     // the dz1 image copy has read sH1, D1 has read sH1 / sC: the landing zone
+      if (has_next) load_upstream(tile + gridDim.x);      // is free -- the next tile's upstream rows, a phase early
+    }
+    // ---- g_e += dz1 We: accumulator -> row-linear staging (sH2 + sG, both dead) -> one bulk reduce-add at L2
+    {
+      float v[32];
+      tmem_ld32(tm_W + qoff, v);
+      tmem_ld_wait();
+      store_row32_linear(lin_out, m, v);
+    }
+    tile_ready();
+    tl.stamp();   // 10 g_e staged
+    if (m.tid == 0) {
+      bulk_red_add_f32(p.g_e + row0 * H, lin_out, tile_rows_bytes(tile), pol_stream);
+      bulk_commit();
+      if (has_next) issue_r4(it + 1);        // every thread has read the accumulator (barrier above)
+    }
+  }
+  tl.stamp();     // loop done
+  if (m.tid == 0) bulk_wait0();
+  // ---------------- flush the resident weight gradients, bias and scale gradients
+  fence_after_sync();
+  __syncthreads();
+  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_E_W4, 128, lin_out, m, pol_keep);
+  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_E_W3, 128, lin_out, m, pol_keep);
+  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_E_W2, 128, lin_out, m, pol_keep);
+  const int cp = m.tid & 63;
+  atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
+  atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
+  atomicAdd(p.grad + GB_E_B3 + 2 * cp, db3a);
+  atomicAdd(p.grad + GB_E_B3 + 2 * cp + 1, db3b);
+  atomicAdd(p.grad + GB_E_B2 + 2 * cp, db2a);
+  atomicAdd(p.grad + GB_E_B2 + 2 * cp + 1, db2b);
+  atomicAdd(p.grad + GB_E_SC + m.c0 + m.lane, dsc);
+  tl.stamp();     // flush issued
   fence_before_sync();
   __syncthreads();
   if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
@@ -1146,6 +1490,39 @@ extern "C" int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void*
     MGN_CUDA(mgn_launch(edge_bwd_kernel<true>, grid, NT, EDGE_BWD_SMEM, stream, p));
   else
     MGN_CUDA(mgn_launch(edge_bwd_kernel<false>, grid, NT, EDGE_BWD_SMEM, stream, p));
+  MGN_LAUNCH_CHECK();
+  return MGN_OK;
+}
+
+// mgn_edge_bwd for the processor loop when mgn_edge_fwd_hl saved the edge MLP's hidden activations: starts from the
+// images h1, h2, h3 (no recompute of layers 1-3, no P, no e image).  g_e [E,128] holds the upstream edge gradient on
+// entry (zeros if there is none) and g_e + dz1 We on exit (in place; edges in CSR order).  dz16_out as mgn_edge_bwd.
+// Weight gradients of layers 2-4, their biases and the scale accumulate into grad_block; layer 1 is mgn_edge_wgrad1 +
+// mgn_p_bwd as before.
+extern "C" int mgn_edge_bwd_saved(int64_t E, int64_t N, const void* h1, const void* h2, const void* h3,
+                                  const float* g_aggr, const int32_t* receivers, float* g_e, void* dz16_out,
+                                  const void* packed, const float* b4, const float* scale, float* grad_block,
+                                  int norm_dim, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MGN_CHECK_ARG(E >= 0 && N > 0, "edge_bwd_saved: bad sizes");
+  MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "edge_bwd_saved: norm_dim must be in 1..128");
+  if (E == 0) return MGN_OK;
+  MGN_CHECK_ARG(h1 && h2 && h3 && g_aggr && receivers && g_e && dz16_out && packed && b4 && scale && grad_block,
+                "edge_bwd_saved: null pointer");
+  EdgeBwdSavedParams p{};
+  p.E = E; p.h1 = (const __half*)h1; p.h2 = (const __half*)h2; p.h3 = (const __half*)h3; p.g_aggr = g_aggr;
+  p.receivers = receivers; p.g_e = g_e; p.dz16_out = (__half*)dz16_out;
+  p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_EDGE);
+  p.b4 = b4; p.scale = scale; p.grad = grad_block;
+  p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
+  static bool attr = false;
+  if (!attr) {
+    MGN_CUDA(cudaFuncSetAttribute(edge_bwd_saved_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_BWD_SMEM));
+    attr = true;
+  }
+  const int grid = (int)std::min<int64_t>(mgn_num_sms(), ceil_div64(E, TILE_ROWS));
+  MGN_CUDA(mgn_launch(edge_bwd_saved_kernel, grid, NT, EDGE_BWD_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return MGN_OK;
 }

@@ -125,8 +125,11 @@ def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, sende
                 receivers: torch.Tensor, num_nodes: int, packed: torch.Tensor, b2, b3, b4, scale,
                 hi_out: Optional[torch.Tensor] = None, lo_out: Optional[torch.Tensor] = None,
                 e_out: Optional[torch.Tensor] = None, aggr: Optional[torch.Tensor] = None,
-                carry: Optional[torch.Tensor] = None, norm_dim: int = H, rowptr: Optional[torch.Tensor] = None):
-    """Edge update of one step (layers.py:687-698) on the image + remainder form of the edge stream:
+                carry: Optional[torch.Tensor] = None, norm_dim: int = H, rowptr: Optional[torch.Tensor] = None,
+                h_saves=None):
+    """h_saves: optional 3 `e16_image(E)` buffers receiving the edge MLP's hidden activations (training: what
+    `edge_bwd_saved` starts from instead of recomputing them).
+    Edge update of one step (layers.py:687-698) on the image + remainder form of the edge stream:
     e_in = hi_in + lo_in (`e16_image` buffers, CSR tile order).  hi_out / lo_out receive the same form of e_out,
     e_out (optional, [E,128] fp32, CSR order) its fp32 rows.  -> aggr"""
     E = senders.shape[0]
@@ -134,10 +137,11 @@ def edge_fwd_hl(hi_in: torch.Tensor, lo_in: torch.Tensor, P: torch.Tensor, sende
         aggr = torch.empty((num_nodes, H), dtype=torch.float32, device=hi_in.device)
     if carry is None and DETERMINISTIC and E > 0:
         carry = carry_buffer(E, 32, hi_in.device)
+    hs = h_saves if h_saves is not None else (None, None, None)
     L.check(L.lib().mgn_edge_fwd_hl(L.i64(E), L.i64(num_nodes), L.p(hi_in), L.p(lo_in), L.p(hi_out), L.p(lo_out),
                                     L.p(e_out), L.p(P), L.p(senders), L.p(receivers), L.p(aggr), L.p(packed),
                                     L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(carry), L.p(rowptr),
-                                    L.i32(norm_dim), L.stream()))
+                                    L.i32(norm_dim), L.p(hs[0]), L.p(hs[1]), L.p(hs[2]), L.stream()))
     return aggr
 
 
@@ -221,6 +225,26 @@ def edge_bwd(e_in, rowmap, g_eout, g_aggr, P, senders, receivers, num_nodes, pac
     L.check(L.lib().mgn_edge_bwd(L.i64(E), L.i64(num_nodes), L.p(e_in), L.p(e16), L.p(rowmap), L.p(g_src),
                                  L.p(g_aggr), L.p(P), L.p(senders), L.p(receivers), L.p(g_e), L.p(dz16), L.p(packed),
                                  L.p(b2), L.p(b3), L.p(b4), L.p(scale), L.p(grad_block), L.i32(norm_dim), L.stream()))
+    return g_e, dz16
+
+
+# MGN_SAVE_EDGE_HIDDEN=0: the processor loop does not keep the edge MLP's hidden activations (768 B per edge and step)
+# and its backward recomputes them (mgn_edge_bwd) -- smaller memory footprint, ~35 % slower edge backward.
+SAVE_EDGE_HIDDEN = bool(int(__import__("os").environ.get("MGN_SAVE_EDGE_HIDDEN", "1")))
+
+
+def edge_bwd_saved(h_saves, g_e, g_aggr, receivers, num_nodes, packed, b4, scale, grad_block, dz16=None,
+                   norm_dim: int = H):
+    """Edge backward of a processor-loop step from the hidden activations `edge_fwd_hl(h_saves=...)` kept.  g_e [E,128]
+    (CSR order) is updated IN PLACE from the upstream edge gradient to the gradient of the step's input edges.
+    -> (g_e, dz16)"""
+    E = receivers.shape[0]
+    if dz16 is None:
+        dz16 = e16_image(E, g_e.device)
+    h1, h2, h3 = h_saves
+    L.check(L.lib().mgn_edge_bwd_saved(L.i64(E), L.i64(num_nodes), L.p(h1), L.p(h2), L.p(h3), L.p(g_aggr),
+                                       L.p(receivers), L.p(g_e), L.p(dz16), L.p(packed), L.p(b4), L.p(scale),
+                                       L.p(grad_block), L.i32(norm_dim), L.stream()))
     return g_e, dz16
 
 

@@ -132,7 +132,7 @@ class _ProcessorFn(torch.autograd.Function):
         # through the permutation (no separate pass over the edge stream)
         e = e0.detach().contiguous()
         rowmap0 = None if csr.identity else csr.perm
-        xs, aggrs, Ps, saves, e16s = [x], [], [], [], []
+        xs, aggrs, Ps, saves, e16s, esaves = [x], [], [], [], [], []
         hl = ops.EDGE_FWD_HL and E > 0
         # the fp32 edge stream ping-pongs; in image + remainder form (hl) only step 0 reads fp32 rows (the caller's)
         # and only the last step writes them, and only if the caller wants the edge latents back
@@ -173,10 +173,15 @@ class _ProcessorFn(torch.autograd.Function):
                 img_next = ops.e16_image(E, dev) if need_grad else img_bufs[k & 1]
             lo_next = lo_bufs[k & 1] if (hl and not last) else None
             _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
+            esv = None
             if hl and k > 0:
+                # training: the edge MLP's hidden activations are kept as tile images (the edge backward of this step
+                # then starts at layer 4 instead of recomputing the block)
+                if need_grad and ops.SAVE_EDGE_HIDDEN:
+                    esv = tuple(ops.e16_image(E, dev) for _ in range(3))
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers, N,
                        packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out, aggr=aggr,
-                       carry=carry, norm_dim=nd, rowptr=csr.rowptr)
+                       carry=carry, norm_dim=nd, rowptr=csr.rowptr, h_saves=esv)
             else:
                 _timed("edge_fwd", ops.edge_fwd, e, rowmap0 if k == 0 else None, P, csr.senders, csr.receivers, N,
                        packed[k], b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
@@ -186,6 +191,7 @@ class _ProcessorFn(torch.autograd.Function):
                    saves=sv, norm_dim=nd)
             if need_grad:
                 aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
+                esaves.append(esv)
             x, img = x_out, img_next
             if e_out is not None:
                 e = e_out
@@ -200,7 +206,7 @@ class _ProcessorFn(torch.autograd.Function):
         if need_grad:
             ctx.csr, ctx.K, ctx.packed, ctx.prm = csr, K, packed, prm
             # the edge backward needs e_k only as the fp16 tile images: the fp32 versions are not kept
-            ctx.xs, ctx.e16s, ctx.aggrs, ctx.Ps, ctx.saves = xs, e16s, aggrs, Ps, saves
+            ctx.xs, ctx.e16s, ctx.aggrs, ctx.Ps, ctx.saves, ctx.esaves = xs, e16s, aggrs, Ps, saves, esaves
             ctx.E, ctx.nd = E, nd
         return x, e_ret
 
@@ -249,9 +255,15 @@ class _ProcessorFn(torch.autograd.Function):
                    g_aggr=g_aggr, dz1=dz1, norm_dim=nd)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
             if E > 0:
-                _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k], csr.senders,
-                       csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf, dz16=dz16, e16=e16s[k],
-                       inplace=True, norm_dim=nd)
+                if ctx.esaves[k] is not None:
+                    if not have_ge:          # no upstream edge gradient: the in-place kernel adds to zeros
+                        ge_buf.zero_()
+                    _timed("edge_bwd", ops.edge_bwd_saved, ctx.esaves[k], ge_buf, g_aggr, csr.receivers, N, packed[k],
+                           b[7], b[8], grads[k], dz16=dz16, norm_dim=nd)
+                else:
+                    _timed("edge_bwd", ops.edge_bwd, None, None, ge_buf if have_ge else None, g_aggr, ctx.Ps[k],
+                           csr.senders, csr.receivers, N, packed[k], b[3], b[5], b[7], b[8], grads[k], g_e=ge_buf,
+                           dz16=dz16, e16=e16s[k], inplace=True, norm_dim=nd)
                 have_ge = True
                 _timed("edge_wgrad1", ops.edge_wgrad1, dz16, e16s[k], E, grads[k])
                 _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
@@ -261,7 +273,7 @@ class _ProcessorFn(torch.autograd.Function):
                 grads[k].mul_(inv_s)
                 GRAD_SYNC(grads[k], k)
             # release what this step saved
-            ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None; e16s[k] = None
+            ctx.saves[k] = None; ctx.aggrs[k] = None; ctx.Ps[k] = None; e16s[k] = None; ctx.esaves[k] = None
             xs[k + 1] = None
         if GRAD_SYNC is None:
             grads.mul_(inv_s)                # one launch for all blocks

@@ -144,11 +144,14 @@ int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int32_t* rowmap
  * carries >= 21 significant bits of the fp32 stream, the residual add is done in fp32, and the stream moves only by
  * 32 KB bulk copies (csrc/edge_fwd_hl.cu).  hi_out / lo_out (both or neither) receive the images of e_out; e_out
  * (fp32 rows, CSR order) is optional -- only a caller that wants the edge latents back needs it.
- * carry: [ceil(E/32),128] fp32 workspace, norm_dim: as for mgn_edge_fwd2 (slots of 32 rows here). */
+ * carry: [ceil(E/32),128] fp32 workspace, norm_dim: as for mgn_edge_fwd2 (slots of 32 rows here).
+ * h1_save, h2_save, h3_save (all three or all NULL): tile images (ceil(E/128) * 32768 bytes each) receiving the edge
+ * MLP's hidden activations for mgn_edge_bwd_saved. */
 int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const void* lo_in, void* hi_out, void* lo_out,
                     float* e_out, const void* P, const int32_t* senders, const int32_t* receivers, float* aggr,
                     const void* packed, const float* b2, const float* b3, const float* b4, const float* scale,
-                    float* carry, const int32_t* rowptr, int norm_dim, void* stream);
+                    float* carry, const int32_t* rowptr, int norm_dim, void* h1_save, void* h2_save, void* h3_save,
+                    void* stream);
 /* mgn_edge_fwd_hl without a caller-provided workspace and WITHOUT ANY ALLOCATION (no cudaMalloc / cudaFree / allocating
  * routine), for callers that cannot allocate: code under CUDA-graph capture, tight serving loops, harnesses that forbid
  * it.  No counterpart in the reference.  The carry scratch is a file-scope
@@ -203,6 +206,12 @@ int mgn_edge_bwd(int64_t E, int64_t N, const float* e_in, const void* e16, const
                  const int32_t* receivers, float* g_e, void* dz16_out, const void* packed, const float* b2,
                  const float* b3, const float* b4, const float* scale, float* grad_block, int norm_dim,
                  void* stream);
+/* mgn_edge_bwd for the processor loop when mgn_edge_fwd_hl kept the edge MLP's hidden activations (h1_save ..
+ * h3_save): the autograd of layers.py:703-719, 694-696 WITHOUT recomputing layers 1-3.  g_e [E,128] (CSR order) holds
+ * the upstream edge gradient on entry (zeros if none) and is updated in place to g_e + dz1 We. */
+int mgn_edge_bwd_saved(int64_t E, int64_t N, const void* h1, const void* h2, const void* h3, const float* g_aggr,
+                       const int32_t* receivers, float* g_e, void* dz16_out, const void* packed, const float* b4,
+                       const float* scale, float* grad_block, int norm_dim, void* stream);
 /* edge_block layer-1 weight gradient, edge-latent columns (edge_block.0.weight[:, 0:128]):
  * dWe += dz1^T e over all edges, streamed from the tile images of dz1 (mgn_edge_bwd) and of e (mgn_edge_fwd). */
 int mgn_edge_wgrad1(int64_t E, const void* dz16, const void* e16, float* grad_block, void* stream);

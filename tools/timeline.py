@@ -34,6 +34,10 @@ if which == "edge_pp":
     cap = 6 * 21
 if which == "edge_hl":
     cap = 10 * 19
+if which == "edge_bwd_saved":
+    cap = 11 * 19 + 2
+if which == "edge_hl_save":
+    cap = 10 * 19
 if fine:
     cap = fine * 19
 ge_in = torch.randn(E, 128, device=dev)
@@ -47,8 +51,19 @@ lo16, lo16b = ops.e16_image(E, dev).zero_(), ops.e16_image(E, dev)
 buf = torch.zeros(cap, dtype=torch.int64, device=dev)
 
 
+hs = tuple(ops.e16_image(E, dev) for _ in range(3))
+if which in ("edge_bwd_saved", "edge_hl_save"):
+    ops.edge_fwd_hl(e16, lo16, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=dz16, lo_out=lo16b,
+                    aggr=aggr, h_saves=hs)
+
+
 def run():
-    if which == "edge_bwd":
+    if which == "edge_bwd_saved":
+        ops.edge_bwd_saved(hs, ge_in, g_aggr, csr.receivers, N, packed, b[3], sc, gblock, dz16=dz16)
+    elif which == "edge_hl_save":
+        ops.edge_fwd_hl(e16, lo16, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=dz16,
+                        lo_out=lo16b, aggr=aggr, h_saves=hs)
+    elif which == "edge_bwd":
         ops.edge_bwd(None, None, ge_in, g_aggr, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, gblock,
                      dz16=dz16, e16=e16, inplace=True)
     elif which == "edge_pp":
@@ -90,15 +105,20 @@ if which == "edge_bwd":
 if which == "edge_pp":
     names = ["O3(k-1)", "O1(k)", "O4(k-1)", "O2(k)", "O5(k-1)", "O0(k+1)"]
     per = 6
-if which == "edge_hl":
+if which in ("edge_hl", "edge_hl_save"):
     names = ["L1 mma", "L1 epi", "L2+L3", "L4+norm", "images", "st+mma1", "ldP", "scan", "red", "next"]
     per = 10
+if which == "edge_bwd_saved":
+    names = ["readout", "upstream", "g build", "R4 wait", "norm bwd", "D4", "D3", "D2", "D1", "stage g_e", "next"]
+    per = 11
 if fine:
     per = fine
     names = [f"s{i}" for i in range(fine)]
 if which.endswith("_raw"):
     print("entry->loop", t[1] - t[0], "tiles", np.diff(t[1:-1]).tolist(), "loop total", t[-2] - t[1], "kernel cycles", t[-2] - t[0])
     sys.exit(0)
+if which == "edge_bwd_saved" and len(t) == 11 * 19 + 2:
+    print("after last tile -> loop done", t[-2] - t[-3], "flush", t[-1] - t[-2], "kernel body", t[-1] - t[0])
 if which == "edge_bwd" and len(t) == 8 * 19 + 2:
     print("after last tile -> loop done", t[-2] - t[-3], "flush", t[-1] - t[-2], "kernel body", t[-1] - t[0])
 ntile = len(t) // per
