@@ -324,7 +324,8 @@ class TrajectoryDataset:
 
     def __init__(self, container_path: str, meta_path: str, device="cuda", preprocessing=None, khop: int = 1,
                  add_edge_features: bool = True, use_previous_data: bool = False, switch_to_val: bool = False,
-                 resident_bytes: int = 64 << 30, masking_ratio: Optional[float] = None, new_edges_ratio: float = 0.0):
+                 resident_bytes: int = 64 << 30, masking_ratio: Optional[float] = None, new_edges_ratio: float = 0.0,
+                 world_pos_index_start: Optional[int] = None, world_pos_index_end: Optional[int] = None):
         if switch_to_val:
             container_path = container_path.replace("train", "test")
         self.meta = load_meta(meta_path)
@@ -340,6 +341,13 @@ class TrajectoryDataset:
         self.resident_bytes = int(resident_bytes)
         self.masking_ratio = masking_ratio
         self.new_edges_ratio = new_edges_ratio
+        self.world_pos_index_start, self.world_pos_index_end = world_pos_index_start, world_pos_index_end
+        # K-hop expansion: the reference applies it AFTER the preprocessing and caches the result per trajectory
+        # (`_apply_k_hop`, dataset.py:139-175).  Without a preprocessing the expansion of the mesh edges is part of the
+        # resident topology (same result, computed once); with one -- it may add world edges -- it runs here, on what
+        # the preprocessing produced.
+        self._khop_after = self.khop > 1 and preprocessing is not None
+        self._khop_cache: Dict[int, Tuple[torch.Tensor, Optional[torch.Tensor]]] = {}
         self._resident: "OrderedDict[int, ResidentTrajectory]" = OrderedDict()
 
     @property
@@ -361,7 +369,7 @@ class TrajectoryDataset:
             return hit
         group = self.container[self.datasets_index[traj_index]]
         rt = ResidentTrajectory(traj_as_meshes(group, self.meta), self.meta, self.device,
-                                add_edge_features=self.add_edge_features, khop=self.khop)
+                                add_edge_features=self.add_edge_features, khop=1 if self._khop_after else self.khop)
         self._resident[traj_index] = rt
         while len(self._resident) > 1 and sum(t.nbytes for t in self._resident.values()) > self.resident_bytes:
             self._resident.popitem(last=False)
@@ -375,6 +383,8 @@ class TrajectoryDataset:
         g = rt.sample(frame, frame + 1, use_previous_data=self.use_previous_data)
         if self.preprocessing is not None:
             g = self.preprocessing(g)
+        if self._khop_after:
+            g = self._apply_k_hop(g, traj_index, rt.num_nodes)
         if 0.0 < self.new_edges_ratio <= 1.0:
             g = self._add_random_edges(g, rt.num_nodes)
         if hasattr(g, "previous_data"):
@@ -384,6 +394,28 @@ class TrajectoryDataset:
         g.csr = _proc.csr_for(g.edge_index, rt.num_nodes)
         if self.masking_ratio is not None:
             return g, masked_indexes(rt.num_nodes, self.masking_ratio)
+        return g
+
+    def _apply_k_hop(self, g, traj_index: int, num_nodes: int):
+        """`BaseDataset._apply_k_hop` (dataset.py:139-175) + `compute_k_hop_graph` (utils/torch_graph.py:56-112): the
+        K-hop edge set of the PREPROCESSED graph, with Cartesian / Distance features recomputed on it (and the world-
+        position features when the index range is configured); computed for the first sample of a trajectory and
+        reused for its other frames, as the reference's per-trajectory cache does."""
+        from . import graph as G
+        hit = self._khop_cache.get(traj_index)
+        if hit is None:
+            ei = G.compute_k_hop_edge_index(g.edge_index, self.khop, num_nodes)
+            ea = None
+            if self.add_edge_features:
+                ea = G.edge_features(g.pos.contiguous(), ei)
+                if self.world_pos_index_start is not None and self.world_pos_index_end is not None:
+                    wp = g.x[:, self.world_pos_index_start:self.world_pos_index_end].contiguous()
+                    ea = G.world_pos_features(ea, wp, ei)
+            hit = (ei, ea)
+            self._khop_cache[traj_index] = hit
+        g.edge_index = hit[0]
+        if self.add_edge_features:
+            g.edge_attr = hit[1]
         return g
 
     def _add_random_edges(self, g, num_nodes: int):

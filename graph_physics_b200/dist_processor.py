@@ -65,7 +65,7 @@ class PartitionEngine:
         self.e_bufs = [torch.empty_like(self.e) for _ in range(min(K, 2))] if not self.hl else None
         self.e_last = torch.empty_like(self.e) if (self.hl and (self.need_edges or K == 1)) else None
         self.lo_bufs = [ops.e16_image(self.E, dev) for _ in range(min(K - 1, 2))] if self.hl else None
-        self.aggrs, self.Ps, self.saves, self.e16s = [], [], [], []
+        self.aggrs, self.Ps, self.saves, self.e16s, self.esaves = [], [], [], [], []
         self.img = None
         self.carry = ops.carry_buffer(self.E, 8, dev) if (ops.DETERMINISTIC and self.E > 0) else None
         if not self.need_grad:
@@ -102,10 +102,13 @@ class PartitionEngine:
                 img_next = ops.e16_image(E, dev) if ng else self.img_bufs[k & 1]
             lo_next = self.lo_bufs[k & 1] if (self.hl and not last) else None
             rowmap = csr.perm if (k == 0 and not csr.identity) else None
+            esv = None
             if self.hl and k > 0:
+                if ng and ops.SAVE_EDGE_HIDDEN:     # as processor.py: the edge backward starts from these
+                    esv = tuple(ops.e16_image(E, dev) for _ in range(3))
                 _timed("edge_fwd", ops.edge_fwd_hl, img_in, self.lo_bufs[(k - 1) & 1], P, csr.senders, csr.receivers,
                        n_ext, self.packed[k], b[3], b[5], b[7], b[8], hi_out=img_next, lo_out=lo_next, e_out=e_out,
-                       aggr=aggr, carry=self.carry, rowptr=csr.rowptr)
+                       aggr=aggr, carry=self.carry, rowptr=csr.rowptr, h_saves=esv)
             else:
                 _timed("edge_fwd", ops.edge_fwd, self.e, rowmap, P, csr.senders, csr.receivers, n_ext, self.packed[k],
                        b[3], b[5], b[7], b[8], e_out=e_out, aggr=aggr, e16_out=img_self, e16_in=img_in,
@@ -113,6 +116,7 @@ class PartitionEngine:
                        write_rows=not (self.hl and e_out is None), carry=self.carry, rowptr=csr.rowptr)
             if ng:
                 self.e16s.append(self.img)
+                self.esaves.append(esv)
             self.img = img_next
             if e_out is not None:
                 self.e = e_out
@@ -120,6 +124,7 @@ class PartitionEngine:
             aggr.zero_()
             if ng:
                 self.e16s.append(None)
+                self.esaves.append(None)
         _timed("node_fwd", ops.node_fwd, x[:n_own], aggr[:n_own], self.packed[k], b[10], b[12], b[14], b[16], b[17],
                x_out=x_out[:n_own], saves=sv)
         if ng:
@@ -192,16 +197,22 @@ class PartitionEngine:
             gx_new[n_own:].zero_()            # halo rows only collect what this rank's edges send back
         _timed("node_wgrad1", ops.node_wgrad1, self.dz1, self.xs[k][:n_own], self.aggrs[k][:n_own], gk)
         if E > 0:
-            _timed("edge_bwd", ops.edge_bwd, None, None, self.ge_buf if self.have_ge else None, self.g_aggr,
-                   self.Ps[k], csr.senders, csr.receivers, n_ext, pk, b[3], b[5], b[7], b[8], gk, g_e=self.ge_buf,
-                   dz16=self.dz16, e16=self.e16s[k], inplace=True)
+            if self.esaves[k] is not None:
+                if not self.have_ge:
+                    self.ge_buf.zero_()
+                _timed("edge_bwd", ops.edge_bwd_saved, self.esaves[k], self.ge_buf, self.g_aggr, csr.receivers, n_ext,
+                       pk, b[7], b[8], gk, dz16=self.dz16)
+            else:
+                _timed("edge_bwd", ops.edge_bwd, None, None, self.ge_buf if self.have_ge else None, self.g_aggr,
+                       self.Ps[k], csr.senders, csr.receivers, n_ext, pk, b[3], b[5], b[7], b[8], gk, g_e=self.ge_buf,
+                       dz16=self.dz16, e16=self.e16s[k], inplace=True)
             self.have_ge = True
             _timed("edge_wgrad1", ops.edge_wgrad1, self.dz16, self.e16s[k], E, gk)
             _timed("dp_gather", ops.dp_gather, self.dz16, csr, self.dP)
         _timed("p_bwd", ops.p_bwd, self.dP, self.xs[k], gx_new, pk, gk)
         self.gx, self.gx_new = gx_new, gx
         gk.mul_(self.inv_s)
-        self.saves[k] = None; self.aggrs[k] = None; self.Ps[k] = None; self.e16s[k] = None
+        self.saves[k] = None; self.aggrs[k] = None; self.Ps[k] = None; self.e16s[k] = None; self.esaves[k] = None
         self.xs[k + 1] = None
 
     def input_grads(self, need_gx: bool = True, need_ge: bool = True):

@@ -27,6 +27,9 @@ DEBUG_KEEP_SAVES = False
 LAST_SAVES = None
 
 
+FP16_MAX = 65504.0
+
+
 def _pad_cols(t: torch.Tensor, cols: int) -> torch.Tensor:
     out = torch.zeros((t.shape[0], cols), dtype=torch.float32, device=t.device)
     out[:, :t.shape[1]] = t
@@ -43,7 +46,14 @@ class _EncoderFn(torch.autograd.Function):
             raise ValueError("fused encoder supports build_mlp(in, 128, 128, nb_of_layers=4, layer_norm=True) only")
         M, fin = feat.shape
         dev = feat.device
-        a = _pad_cols(feat.detach().float(), H)                         # the "aggr" half of the node kernel's input
+        # The features become fp16 tensor-core operands.  A normalised column whose accumulated std is still at the
+        # Normalizer's 1e-8 floor (a node type not seen yet, the time column early on) can reach 1e5..1e8, which the
+        # non-saturating fp16 conversion would turn into inf and the MLP into NaN; the reference stays finite there
+        # (fp32 + the encoder's RMSNorm).  Values are clamped to the fp16 finite range: finite results, exact for every
+        # |x| <= 65504.
+        f32 = feat.detach().float()
+        a = _pad_cols(f32.clamp(-FP16_MAX, FP16_MAX), H)                # the "aggr" half of the node kernel's input
+        ctx.clamped = (f32.abs() > FP16_MAX) if any(ctx.needs_input_grad[:1]) else None
         xz = torch.zeros((M, H), dtype=torch.float32, device=dev)
         w1p = torch.zeros((H, 2 * H), dtype=torch.float32, device=dev)
         w1p[:, H:H + fin] = w1.detach()
@@ -79,6 +89,8 @@ class _EncoderFn(torch.autograd.Function):
             grads.mul_(1.0 / s)
             if ctx.needs_input_grad[0]:
                 g_feat = g_a[:, :fin] * (1.0 / s)
+                if ctx.clamped is not None:
+                    g_feat = g_feat.masked_fill(ctx.clamped, 0.0)      # d clamp / dx = 0 outside the range
         elif ctx.needs_input_grad[0]:
             g_feat = torch.zeros((0, fin), dtype=torch.float32, device=dev)
         v = ops.split_grad_block(grads)

@@ -33,6 +33,8 @@ from .processors import Graph
 
 
 class Simulator(nn.Module):
+    check_node_types = True     # device-side range assert of the node-type column (see _get_one_hot_type)
+
     def __init__(self, node_input_size: int, edge_input_size: int, output_size: int, feature_index_start: int,
                  feature_index_end: int, output_index_start: int, output_index_end: int, node_type_index: int,
                  model: nn.Module, device, model_dir: str = "checkpoint/simulator.pth"):
@@ -64,6 +66,10 @@ class Simulator(nn.Module):
         """[N, NodeType.SIZE] one-hot of the node-type column, in the features' dtype (the reference makes an int64
         one-hot that the concatenation promotes: same values)."""
         node_type = inputs.x[:, self.node_type_index].long()
+        if self.check_node_types and node_type.is_cuda:
+            # the reference's torch.nn.functional.one_hot raises for a class outside [0, SIZE); here the check runs on
+            # the device (no host read: the step stays capturable) and a violation surfaces as a CUDA device assert
+            torch._assert_async(((node_type >= 0) & (node_type < int(NodeType.SIZE))).all())
         classes = torch.arange(int(NodeType.SIZE), device=node_type.device)
         return (node_type.unsqueeze(-1) == classes).to(inputs.x.dtype)
 

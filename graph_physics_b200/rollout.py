@@ -21,6 +21,12 @@ from the first frame's own columns (overwriting a column with itself), so a sing
 A batch of a few hundred sequential steps on a ~2 k-node mesh is launch-latency bound when run eagerly (~150 kernel
 launches of a few microseconds each per step); the replay removes that.
 
+Moving meshes / world edges (DeformingPlate; the reference rebuilds FaceToEdge, `add_world_edges`, Cartesian / Distance
+and the world-position features for EVERY frame, graphphysics/dataset/preprocessing.py:401-427): a frame may carry its
+own `edge_attr` and `edge_index`.  Edge features of the captured topology are copied into the static buffer and the
+replay continues; a different topology (another `edge_index` tensor) runs that step eagerly on the frame's own edges.
+A frame whose `edge_attr` does not match the topology it is used with raises -- nothing falls back to frame-0 edges.
+
 `predict_fn(graph) -> [N, d]` is any forward-only callable built on this package's modules (e.g. an
 `EncodeProcessDecode` wrapped with the simulator's pre / post-processing); it must read `graph.x` (and
 `graph.edge_attr`, `graph.edge_index`) from the tensors it is handed, because those are the static buffers of the capture.
@@ -45,7 +51,8 @@ def boundary_mask(x: torch.Tensor, node_type_index: int) -> torch.Tensor:
 
 class Rollout:
     """rollout = Rollout(predict_fn, graph, out_slice=(s, e), node_type_index=i, prev_slice=None)
-    preds = rollout.run(frames)          # frames: iterable of (x_t [N,F], y_t [N,d]); -> [T,N,d] on the device
+    preds = rollout.run(frames)          # frames: iterable of (x_t [N,F], y_t [N,d][, edge_attr_t[, edge_index_t]])
+                                         # -> [T,N,d] on the device
 
     `graph` is duck typed (`.x`, `.edge_attr`, `.edge_index`, optional `.pos`); its tensors become the static
     buffers.  `capture=False` runs the same step eagerly (the check the tests compare the replay against)."""
@@ -67,6 +74,9 @@ class Rollout:
         self.capture = bool(capture)
         self.warmup = int(warmup)
         self._graph = None
+        # the topology the static buffers (and the capture) belong to
+        self._ei0 = graph.edge_index
+        self._ea0 = getattr(graph, "edge_attr", None)
 
     # one step on the static buffers (graph.x already holds frame t's features, self.y its target)
     def _step(self):
@@ -113,25 +123,53 @@ class Rollout:
         if self.prev is not None:
             self.last_prev.copy_(x0[:, self.prev[0]:self.prev[1]])
 
-    def step(self, x_t: torch.Tensor, y_t: torch.Tensor) -> torch.Tensor:
+    def step(self, x_t: torch.Tensor, y_t: torch.Tensor, edge_attr: Optional[torch.Tensor] = None,
+             edge_index: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One `_make_prediction` call: frame features and target in, prediction out (a view of a static buffer:
-        copy it if it must survive the next step)."""
+        copy it if it must survive the next step).
+        edge_attr: this frame's edge features (moving mesh); edge_index: this frame's topology if it is not the one the
+        rollout was built on -- pass the SAME tensor object (or None) for frames that keep it, so that they replay."""
         self.graph.x.copy_(x_t, non_blocking=True)
         self.y.copy_(y_t, non_blocking=True)
-        if self.capture:
-            self._ensure_captured()
-            self._graph.replay()
-        else:
+        same_topology = edge_index is None or edge_index is self._ei0
+        if same_topology:
+            if edge_attr is not None:
+                if self._ea0 is None or tuple(edge_attr.shape) != tuple(self._ea0.shape):
+                    raise ValueError(f"rollout: edge_attr {tuple(edge_attr.shape)} does not match the topology the "
+                                     f"rollout was built on ({None if self._ea0 is None else tuple(self._ea0.shape)}); "
+                                     "pass this frame's edge_index as well")
+                self._ea0.copy_(edge_attr, non_blocking=True)
+            self.graph.edge_index, self.graph.edge_attr = self._ei0, self._ea0
+            if self.capture:
+                self._ensure_captured()
+                self._graph.replay()
+            else:
+                self._step()
+            return self.pred
+        # another topology: this step runs eagerly on the frame's own edges (the capture belongs to self._ei0)
+        if edge_index.dim() != 2 or edge_index.shape[0] != 2:
+            raise ValueError("rollout: edge_index must be [2, E]")
+        if self._ea0 is not None:
+            if edge_attr is None or edge_attr.shape[0] != edge_index.shape[1] or edge_attr.shape[1] != self._ea0.shape[1]:
+                raise ValueError("rollout: a frame with its own edge_index needs its own edge_attr [E, "
+                                 f"{self._ea0.shape[1]}]")
+        self.graph.edge_index, self.graph.edge_attr = edge_index, edge_attr
+        try:
             self._step()
+        finally:
+            self.graph.edge_index, self.graph.edge_attr = self._ei0, self._ea0
         return self.pred
 
     def run(self, frames: Iterable[Sequence[torch.Tensor]]) -> torch.Tensor:
         out = []
         first = True
-        for x_t, y_t in frames:
+        for fr in frames:
+            x_t, y_t = fr[0], fr[1]
+            ea_t = fr[2] if len(fr) > 2 else None
+            ei_t = fr[3] if len(fr) > 3 else None
             if first:
                 self.graph.x.copy_(x_t, non_blocking=True)      # (the capture warm-up must see real features)
                 self.reset(x_t)
                 first = False
-            out.append(self.step(x_t, y_t).clone())
+            out.append(self.step(x_t, y_t, ea_t, ei_t).clone())
         return torch.stack(out) if out else torch.empty((0,) + tuple(self.pred.shape), device=self.pred.device)

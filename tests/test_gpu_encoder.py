@@ -133,3 +133,30 @@ def test_fused_decoder_matches_eager_module(rows, dout):
     with torch.no_grad():
         out2 = ENC.run_decoder(mlp, lat)
     assert torch.equal(out2, out.detach())
+
+
+def test_fused_encoder_survives_huge_normalised_features():
+    """A normalised column at 1e6 (std still at the Normalizer's 1e-8 floor): the fused encoder must stay finite (inputs
+    are clamped to the fp16 range before they become operands) and agree with the eager fp32 module on the clamped
+    input; rows without such a value are unaffected."""
+    from graph_physics_b200 import encoder as enc
+    from graph_physics_b200.models.layers import build_mlp
+    torch.manual_seed(0)
+    mlp = build_mlp(11, 128, 128).cuda()
+    feat = torch.randn(700, 11, device="cuda")
+    feat[::7, 3] = 1.0e6
+    feat[3::7, 5] = -3.0e7
+    out = enc.run_encoder(mlp, feat)
+    assert torch.isfinite(out).all()
+    ref = mlp(feat.clamp(-65504.0, 65504.0))
+    err = float((out - ref).norm() / ref.norm())
+    assert err < 2e-3, err
+    clean = torch.ones(700, dtype=torch.bool, device="cuda")
+    clean[::7] = False
+    clean[3::7] = False
+    ref_exact = mlp(feat)
+    assert float((out[clean] - ref_exact[clean]).norm() / ref_exact[clean].norm()) < 2e-3
+    # and training through it stays finite
+    feat2 = feat.clone().requires_grad_(True)
+    enc.run_encoder(mlp, feat2).square().mean().backward()
+    assert torch.isfinite(feat2.grad).all() and all(torch.isfinite(p.grad).all() for p in mlp.parameters())

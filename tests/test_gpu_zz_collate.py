@@ -94,3 +94,52 @@ def test_preprocessing_pipeline_on_device(golden_dir):
     assert torch.equal(w.edge_index, ei_w) and w.edge_attr is None
     w = P.add_world_pos_features(P.edge_features(Graph(x=x, pos=pos, edge_index=ei_w, edge_attr=None)), 0, 2)
     assert w.edge_attr.shape == (ei_w.shape[1], 6)
+
+
+def test_k_hop_is_applied_after_the_preprocessing(golden_dir, tmp_path):
+    """`BaseDataset.__getitem__` runs the preprocessing (which may add world edges) and THEN `_apply_k_hop`
+    (graphphysics/dataset/h5_dataset.py:100-101, dataset.py:139-175): with world-edge preprocessing and khop = 2 the
+    edge set is the 2-hop expansion of mesh + world edges (oracle: numpy restatement), cached per trajectory; without a
+    preprocessing the expansion of the mesh edges comes from the resident topology (same as before)."""
+    import json
+    from graph_physics_b200 import dataset as D, preprocessing as P
+    from oracle import graph_oracle as go
+    z = np.load(os.path.join(golden_dir, "ref_dataset.npz"))
+    meta = json.loads(bytes(z["cyl2d.meta"]).decode())
+    group = {k[len("cyl2d.raw."):]: z[k] for k in z.files if k.startswith("cyl2d.raw.")}
+    path = os.path.join(tmp_path, "train.npz")
+    D.save_npz_container(path, {"t0": group})
+    meta_path = os.path.join(tmp_path, "meta.json")
+    with open(meta_path, "w") as fp:
+        json.dump(meta, fp)
+    plain = D.TrajectoryDataset(path, meta_path, device="cuda", khop=2)
+    s0 = plain[0]
+    n = s0.x.shape[0]
+    ei1 = go.face_to_edge(s0.face.cpu().numpy(), n)
+    assert np.array_equal(s0.edge_index.cpu().numpy(), go.k_hop_edge_index(ei1, 2, n))
+    plain.close()
+    # world edges between "obstacle" and "normal" nodes.  Column layout after the transforms (the reference's
+    # DeformingPlate convention, preprocessing.py:47-89): [world_pos (3) | obstacle displacement (3) | node type | ...];
+    # node types are made up from the position, the world position is the mesh position with z = 0
+    def add_cols(g):
+        n_ = g.pos.shape[0]
+        nt_ = (g.pos[:, 0] > g.pos[:, 0].median()).to(g.x.dtype).unsqueeze(1)          # 1 = OBSTACLE, 0 = NORMAL
+        wpos = torch.cat([g.pos.to(g.x.dtype), torch.zeros(n_, 1, dtype=g.x.dtype, device=g.x.device)], dim=1)
+        g.x = torch.cat([wpos, nt_, g.x], dim=1)
+        g.y = torch.cat([wpos + 0.001, g.y], dim=1)
+        return g
+    wp = {"world_pos_index_start": 0, "world_pos_index_end": 3, "node_type_index": 6, "radius": 0.06}
+    pre = P.build_preprocessing(world_pos_parameters=wp, extra_node_features=add_cols)
+    ds = D.TrajectoryDataset(path, meta_path, device="cuda", khop=2, preprocessing=pre, world_pos_index_start=0,
+                             world_pos_index_end=3)
+    s = ds[0]
+    wpos = s.x[:, 0:3].cpu().numpy()
+    nt = s.x[:, 6].cpu().numpy()
+    ei_world = go.world_edges(ei1, wpos.astype(np.float64), nt, n, radius=0.06)
+    assert ei_world.shape[1] > ei1.shape[1], "the fixture must produce world edges for this test to mean anything"
+    want = go.k_hop_edge_index(ei_world, 2, n)
+    assert np.array_equal(s.edge_index.cpu().numpy(), want)
+    assert not np.array_equal(want, go.k_hop_edge_index(ei1, 2, n))
+    assert s.edge_attr.shape == (want.shape[1], 7)                 # Cartesian + Distance (3) + world-position features (4)
+    assert ds[1].edge_index is s.edge_index                        # cached per trajectory, as the reference does
+    ds.close()
