@@ -17,6 +17,9 @@
 #define MGN_FILE_ID 2
 #include <algorithm>
 
+#include <cuda.h>                 // CUtensorMap (types only: cuTensorMapEncodeTiled is looked up at run time)
+#include <cudaTypedefs.h>
+
 #include "mlp_v2.cuh"
 #include "mlp_fwd_abi.cuh"
 
@@ -36,6 +39,10 @@ struct EdgeHLParams {
   float* carry;             // [ceil(E/32),128] fp32: partial sums of runs that continue from an earlier 32-row slot
                             // (deterministic aggregation, aggr_fixup_kernel below)
   float inv_sqrt_d;         // RMSNorm: d^-1/2 of the TRUE hidden size (zero-padded narrower models, ops.py)
+  int pj_tma;               // 1: the P_j[sender] rows are gathered by the TMA engine (cp.async.bulk.tensor ... tile::gather4
+                            // through `tmap_p`) instead of cp.async
+  int num_nodes;
+  alignas(64) CUtensorMap tmap_p;   // P as a [N][256] fp16 tensor, box 64 x 1, 128-byte swizzle
   __half* h_save[3];        // training: tile images of the hidden activations h1, h2, h3 (what mgn_edge_bwd_saved starts
                             // from instead of recomputing them), all three or all null
   const __half* W;          // We, W2, W3, W4 tiles
@@ -52,8 +59,18 @@ struct EdgeHLParams {
 // is only needed after the last product), h3 in sHi again -- so that every 32 KB copy has two layer times to read its
 // tile before the tile is written again; the loads of lo (this tile) and hi (next tile) follow those copies, and the
 // next tile's first product is issued after the scan instead of before it.
-template <bool SAVE>
-__global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p) {
+// four rows of a [N][256] fp16 tensor (64 columns from `col0`) -> four consecutive 128-byte rows of a swizzled panel
+__device__ __forceinline__ void tma_gather4(void* smem_dst, const CUtensorMap* tmap, int col0, int r0, int r1, int r2,
+                                            int r3, uint64_t* bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%2, %3, %4, %5, %6}], [%7], %8;" ::"r"(smem_u32(smem_dst)),
+      "l"(tmap), "r"(col0), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(smem_u32(bar)), "l"(pol)
+      : "memory");
+}
+
+template <bool SAVE, bool PJ_TMA>
+__global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const __grid_constant__ EdgeHLParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   check_smem_alignment(smem);
   uint8_t* sW = smem;                          // 4 x 32 KB
@@ -65,6 +82,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
   uint64_t& mbar = tail->bar[1];
   uint64_t& bar_hi = tail->bar[2];
   uint64_t& bar_lo = tail->bar[3];
+  uint64_t& bar_pj = tail->bar[4];
   uint32_t& tmem_slot = tail->tmem_slot;
   const Map m = make_map();
 
@@ -73,6 +91,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     mbar_init(&mbar, 1);
     mbar_init(&bar_hi, 1);
     mbar_init(&bar_lo, 1);
+    mbar_init(&bar_pj, 1);
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -177,7 +196,28 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     for (int j = 0; j < 4; ++j) pi[j] = ix.ok ? ld_u4_hint(Pi + 8 * j, pol_keep) : make_uint4(0, 0, 0, 0);
   };
   const uint32_t sOut_u32 = smem_u32(sOut);
+  uint32_t pj_phase = 0;
   auto stage_pj = [&](const Idx& ix) {
+    if constexpr (PJ_TMA) {
+      // TMA gather: lanes 0..3 of every warp move the warp's 8 rows -- (row group of 4) x (64-column panel) each, one
+      // cp.async.bulk.tensor.2d.tile::gather4 = 4 x 128 bytes, landing as rows 4g..4g+3 of the panel exactly as
+      // tile_off lays them out (the 128-byte swizzle is a function of the shared-memory address).  Rows past the end
+      // name row N: out of bounds, filled with zeros.
+      int sn[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        sn[i] = __shfl_sync(0xffffffffu, ix.snd_c, i);
+        if (sn[i] < 0) sn[i] = p.num_nodes;
+      }
+      if (m.tid == 0) mbar_arrive_expect_tx(&bar_pj, TILE_BYTES);
+      if (m.lane < 4) {
+        const int g = m.lane & 1, pn = m.lane >> 1;
+        fence_async_smem();
+        tma_gather4(sOut + pn * (TILE_ROWS * 128) + (m.warp * 8 + 4 * g) * 128, &p.tmap_p, 128 + 64 * pn,
+                    g ? sn[4] : sn[0], g ? sn[5] : sn[1], g ? sn[6] : sn[2], g ? sn[7] : sn[3], &bar_pj, pol_keep);
+      }
+      return;
+    }
     const int hw = m.lane >> 4, q = m.lane & 15;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -186,7 +226,15 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
                  p.P + (long long)(sn >= 0 ? sn : 0) * 256 + 128 + 8 * q, sn >= 0 ? 16u : 0u, pol_keep);
     }
   };
-  auto fetch_pj = [&]() {                      // after cp_async_wait_all() and a barrier
+  auto wait_pj = [&]() {                       // this thread may read the staged rows
+    if constexpr (PJ_TMA) {
+      mbar_wait(&bar_pj, pj_phase);
+      pj_phase ^= 1;
+    } else {
+      cp_async_wait_all();
+    }
+  };
+  auto fetch_pj = [&]() {                      // after wait_pj() (and, for cp.async, a barrier)
 #pragma unroll
     for (int j = 0; j < 4; ++j) pj[j] = *reinterpret_cast<const uint4*>(sOut + tile_off(128, m.row, m.c0 + 8 * j));
   };
@@ -210,7 +258,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
     }
     load_pi(cur);
     stage_pj(cur);
-    cp_async_wait_all();
+    wait_pj();
     __syncthreads();
     fetch_pj();
   }
@@ -323,7 +371,7 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const EdgeHLParams p
         y[4 * j] += bb[j].x; y[4 * j + 1] += bb[j].y; y[4 * j + 2] += bb[j].z; y[4 * j + 3] += bb[j].w;
         ss += y[4 * j] * y[4 * j] + y[4 * j + 1] * y[4 * j + 1] + y[4 * j + 2] * y[4 * j + 2] + y[4 * j + 3] * y[4 * j + 3];
       }
-      cp_async_wait_all();        // (the barrier below makes every thread's staged P_j rows visible)
+      if (has_next) wait_pj();    // (the barrier below makes every thread's staged P_j rows visible)
       tmem_st1(taddr_rs + m.cq, __float_as_uint(ss));
       tmem_st_wait();
       fence_before_sync();        // the accumulator is read: the barrier orders this before the next product 1
@@ -505,6 +553,32 @@ int mgn_launch_aggr_fixup(int64_t E, int64_t N, int slot_rows, const int32_t* re
 
 static constexpr int EDGE_HL_SMEM = 7 * 32768 + TAIL_BYTES;
 
+// Tensor map of P [N][256] fp16 for the TMA gather of the P_j rows: box = 64 columns x 1 row (tile::gather4 moves four
+// such boxes per instruction), 128-byte swizzle (= the panel layout of tc05.cuh), out-of-bounds rows read as zeros.
+// cuTensorMapEncodeTiled is a host-side encoder of the driver library: looked up through the runtime, nothing to link.
+static int make_p_tensor_map(CUtensorMap* tm, const void* P, int64_t N) {
+  static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+  if (encode == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    MGN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+    MGN_CHECK_ARG(fn != nullptr && q == cudaDriverEntryPointSuccess, "edge_fwd_hl: cuTensorMapEncodeTiled not available");
+    encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  }
+  const cuuint64_t gdim[2] = {256, (cuuint64_t)N};
+  const cuuint64_t gstride[1] = {512};
+  const cuuint32_t box[2] = {64, 1};
+  const cuuint32_t estride[2] = {1, 1};
+  const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(P), gdim, gstride, box, estride,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mgn_set_error("edge_fwd_hl: cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+    return MGN_EUNSUPPORTED;
+  }
+  return MGN_OK;
+}
+
 // Steps 1..K-1 of the processor loop with the edge stream as image + remainder (see the header of this file).
 // hi_out / lo_out (both or neither) receive the images of e_out; e_out (fp32 rows, CSR order) is optional.
 // carry: [ceil(E/32),128] fp32 workspace of the deterministic aggregation (plain stores + aggr_fixup_kernel: no
@@ -535,17 +609,31 @@ extern "C" int mgn_edge_fwd_hl(int64_t E, int64_t N, const void* hi_in, const vo
   MGN_CHECK_ARG((h1_save == nullptr) == (h2_save == nullptr) && (h1_save == nullptr) == (h3_save == nullptr),
                 "edge_fwd_hl: the three hidden-activation saves go together");
   p.h_save[0] = (__half*)h1_save; p.h_save[1] = (__half*)h2_save; p.h_save[2] = (__half*)h3_save;
+  // MGN_PJ_TMA=1: gather the P_j rows with the TMA engine (tile::gather4) instead of cp.async
+  static const bool pj_tma = getenv("MGN_PJ_TMA") != nullptr && atoi(getenv("MGN_PJ_TMA")) != 0;
+  p.pj_tma = pj_tma ? 1 : 0;
+  p.num_nodes = (int)N;
+  if (pj_tma) {
+    MGN_CHECK_ARG((reinterpret_cast<uintptr_t>(P) & 15) == 0, "edge_fwd_hl: P must be 16-byte aligned for the tensor map");
+    const int rc = make_p_tensor_map(&p.tmap_p, P, N);
+    if (rc != MGN_OK) return rc;
+  }
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   static bool attr = false;
   if (!attr) {
-    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
-    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
+    MGN_CUDA(cudaFuncSetAttribute(edge_fwd_hl_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, EDGE_HL_SMEM));
     attr = true;
   }
   const int64_t tiles = ceil_div64(E, TILE_ROWS);
   const int grid = (int)std::min<int64_t>(mgn_num_sms(), tiles);
-  if (h1_save != nullptr) MGN_CUDA(mgn_launch(edge_fwd_hl_kernel<true>, grid, NT, EDGE_HL_SMEM, stream, p));
-  else MGN_CUDA(mgn_launch(edge_fwd_hl_kernel<false>, grid, NT, EDGE_HL_SMEM, stream, p));
+  const bool sv = h1_save != nullptr;
+  if (pj_tma) MGN_CUDA(sv ? mgn_launch(edge_fwd_hl_kernel<true, true>, grid, NT, EDGE_HL_SMEM, stream, p)
+                          : mgn_launch(edge_fwd_hl_kernel<false, true>, grid, NT, EDGE_HL_SMEM, stream, p));
+  else MGN_CUDA(sv ? mgn_launch(edge_fwd_hl_kernel<true, false>, grid, NT, EDGE_HL_SMEM, stream, p)
+                   : mgn_launch(edge_fwd_hl_kernel<false, false>, grid, NT, EDGE_HL_SMEM, stream, p));
   MGN_LAUNCH_CHECK();
   return mgn_launch_aggr_fixup(E, N, 32, receivers, rowptr, carry, aggr, stream);
 }

@@ -265,3 +265,20 @@ def test_pack_blocks_equals_pack_block():
     for k in range(K):
         one = ops.pack_block(blocks[k][:4], blocks[k][4:])
         assert torch.equal(many[k], one), k
+
+
+def test_tma_gather4_path_matches_cp_async_path():
+    """MGN_PJ_TMA=1 gathers the P_j[sender] rows with cp.async.bulk.tensor.2d.tile::gather4 (TMA) instead of cp.async.
+    The switch is read once per process, so the image + remainder edge-kernel tests of this file and the saved-activation
+    backward test are re-run in a child process with it set (they compare against kernels that do not use it)."""
+    import subprocess
+    import sys
+    if os.environ.get("MGN_PJ_TMA_CHILD"):
+        pytest.skip("already inside the child run")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MGN_PJ_TMA="1", MGN_PJ_TMA_CHILD="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "tests/test_gpu_fwd_step.py", "tests/test_gpu_bwd_step.py",
+                        "-k", "image or remainder or hl or deterministic or saved"], cwd=root, env=env, capture_output=True,
+                       text=True, timeout=280)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
