@@ -589,9 +589,9 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_kernel(const EdgeBwdParams p) 
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
   __syncthreads();          // thread 0 has seen the last g_e store leave lin32
-  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_E_W4, 128, lin32, m, pol_keep);
-  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_E_W3, 128, lin32, m, pol_keep);
-  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_E_W2, 128, lin32, m, pol_keep);
+  // (every bulk load of the loop was consumed inside it, the stores were waited for above: all slots are dead)
+  flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_E_W4, p.grad + GB_E_W3, p.grad + GB_E_W2,
+                  smem, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
@@ -757,9 +757,10 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
     tl.stamp();   // 0 tile top
     load_gag(rcv_cur);                       // in flight under the waits below
     if (it > 0) {
-      if (m.tid == 0) bulk_wait_read0();
+      // the previous tile's g_e staging left as two reduce-adds, the sG half (rows 64..127) first: only that one has
+      // to be read out before g can be built; the sH2 half is waited for where h2 is requested (after the norm)
+      if (m.tid == 0) bulk_wait_read1();
       __syncthreads();
-      if (loader) load_img(sH2, p.h2, tile, &bar_h2);
     }
     tl.stamp();   // 1 staging read out
     {
@@ -791,10 +792,12 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
       tl.stamp();   // 4 R4 product done
       // the landing zone (sH1 + sC) is idle until h1 / We are requested below: its first 4 KB carry the row sums
       dsc += rmsnorm_bwd_q2(tm_W + qoff, bb, sc, sG, reinterpret_cast<float2*>(sH1), m, p.inv_sqrt_d, p.norm_d);
+      if (m.tid == 0 && it > 0) bulk_wait_read0();        // the sH2 half of the previous staging has been read out too
       tile_ready();
     }
     tl.stamp();   // 5 norm backward done
-    if (loader) {                            // needed by D2 / D1, two and three products from here
+    if (loader) {                            // needed by D3 / D2 / D1, one to three products from here
+      if (it > 0) load_img(sH2, p.h2, tile, &bar_h2);     // (thread 0 saw the sH2 half read out before the barrier above)
       load_img(sH1, p.h1, tile, &bar_h1);
       load_w_slot(sC, p.W, 0, &bar_wC);      // We
       if (has_next) {                        // next tile's streams into L2
@@ -878,7 +881,12 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
     tile_ready();
     tl.stamp();   // 10 g_e staged
     if (m.tid == 0) {
-      bulk_red_add_f32(p.g_e + row0 * H, lin_out, tile_rows_bytes(tile), pol_stream);
+      const uint32_t nb = tile_rows_bytes(tile);
+      if (nb > 64 * 512) {                   // rows 64.. (staged in sG) first, as their own group
+        bulk_red_add_f32(p.g_e + (row0 + 64) * H, sG, nb - 64 * 512, pol_stream);
+        bulk_commit();
+      }
+      bulk_red_add_f32(p.g_e + row0 * H, lin_out, nb > 64 * 512 ? 64 * 512 : nb, pol_stream);
       bulk_commit();
       if (has_next) issue_r4(it + 1);        // every thread has read the accumulator (barrier above)
     }
@@ -888,9 +896,8 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
   // ---------------- flush the resident weight gradients, bias and scale gradients
   fence_after_sync();
   __syncthreads();
-  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_E_W4, 128, lin_out, m, pol_keep);
-  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_E_W3, 128, lin_out, m, pol_keep);
-  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_E_W2, 128, lin_out, m, pol_keep);
+  flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_E_W4, p.grad + GB_E_W3, p.grad + GB_E_W2,
+                  smem, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_E_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_E_B4 + 2 * cp + 1, db4b);
@@ -1113,9 +1120,8 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     __syncthreads();
   }
   fence_after_sync();
-  flush_acc_bulk(tm_dW4 + qoff, p.grad + GB_N_W4, 128, stage, m, pol_keep);
-  flush_acc_bulk(tm_dW3 + qoff, p.grad + GB_N_W3, 128, stage, m, pol_keep);
-  flush_acc_bulk(tm_dW2 + qoff, p.grad + GB_N_W2, 128, stage, m, pol_keep);
+  flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_N_W4, p.grad + GB_N_W3, p.grad + GB_N_W2,
+                  smem, m, pol_keep);
   const int cp = m.tid & 63;
   atomicAdd(p.grad + GB_N_B4 + 2 * cp, db4a);
   atomicAdd(p.grad + GB_N_B4 + 2 * cp + 1, db4b);

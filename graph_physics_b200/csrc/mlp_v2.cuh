@@ -242,6 +242,32 @@ __device__ __forceinline__ void flush_acc_bulk(uint32_t taddr, float* __restrict
   __syncthreads();
 }
 
+// Three resident accumulators at once (the end-of-kernel flush of dW4, dW3, dW2): every tile slot is dead by then, so
+// the three are staged side by side (3 x 64 KB from `base`) and leave as three back-to-back bulk reductions -- one
+// barrier pair and one read-out wait instead of three.  Contiguous destinations ([128][128] blocks).
+__device__ __forceinline__ void flush_acc_bulk3(uint32_t t0, uint32_t t1, uint32_t t2, float* __restrict__ d0,
+                                                float* __restrict__ d1, float* __restrict__ d2, uint8_t* base,
+                                                const Map& m, uint64_t pol) {
+  const uint32_t ta[3] = {t0, t1, t2};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float v[32];
+    tmem_ld32(ta[i], v);
+    tmem_ld_wait();
+    store_row32_linear(base + i * 65536, m, v);
+  }
+  fence_async_smem();
+  __syncthreads();
+  if (m.tid == 0) {
+    bulk_red_add_f32(d0, base, 65536, pol);
+    bulk_red_add_f32(d1, base + 65536, 65536, pol);
+    bulk_red_add_f32(d2, base + 2 * 65536, 65536, pol);
+    bulk_commit();
+    bulk_wait_read0();
+  }
+  __syncthreads();
+}
+
 // ReLU backward in place (tile: h -> fp16(acc * [h > 0])) plus an fp32 copy of the result in a linear tile
 __device__ __forceinline__ void epi_relu_mask_q32(uint32_t taddr, uint8_t* tile, uint8_t* lin32, const Map& m) {
   float v[32], h[32];
