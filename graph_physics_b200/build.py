@@ -14,7 +14,10 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "libmgn_b200.so")
+# MGN_BUILD_TAG=<tag>: a developer variant (with MGN_NVCC_EXTRA, e.g. -DMGN_TIMELINE) built next to the production
+# library as libmgn_b200_<tag>.so from its own object directory; MGN_LIB_PATH selects it at run time
+TAG = os.environ.get("MGN_BUILD_TAG", "")
+OUT = os.path.join(HERE, f"libmgn_b200_{TAG}.so" if TAG else "libmgn_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
@@ -34,7 +37,7 @@ def _stale(target, deps):
 
 def build(force: bool = False, verbose: bool = False) -> str:
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-    objdir = os.path.join(CSRC, "build")
+    objdir = os.path.join(CSRC, f"build_{TAG}" if TAG else "build")
     os.makedirs(objdir, exist_ok=True)
     jobs = []
     for src in _sources():

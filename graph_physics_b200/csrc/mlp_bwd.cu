@@ -705,12 +705,24 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
     mbar_arrive_expect_tx(&bar_up, tile_rows_bytes(tile_));
     bulk_g2s(lin_in, p.g_e + tile_ * TILE_ROWS * H, tile_rows_bytes(tile_), &bar_up);
   };
+  Timeline tl;
+  tl.init(false, nullptr, 0);
+#ifdef MGN_FINE_TL           // developer build: five more stamps around the issue of R4 (tools/timeline.py edge_bwd_saved 16)
+#define FINE_STAMP() tl.stamp()
+#else
+#define FINE_STAMP()
+#endif
   auto issue_r4 = [&](uint32_t it_) {        // thread 0: z4 = h3 W4^T of the CTA's it_-th tile
+    FINE_STAMP();
     mbar_wait(&bar_wA, 0);                   // W4: completions 0, 2, 4, ... of slot A
+    FINE_STAMP();
     mbar_wait(&bar_h3, it_ & 1);
+    FINE_STAMP();
     fence_after_sync();
     umma_tile(tm_W, uH3, 128, 0, uA, 128, 0, 0, 128, 8, 0);
+    FINE_STAMP();
     mma_commit(&bar_mma);
+    FINE_STAMP();
   };
   // this thread's row of the tile -> receiver (or -1 past the end); its g_aggr chunks, rotated by lane & 7 (g build)
   auto load_rcv = [&](long long tile_) -> int {
@@ -746,7 +758,6 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
   int rcv_cur = load_rcv(tile0);
   int rcv_nxt = load_rcv(tile0 + gridDim.x);
   if (m.tid == 0) issue_r4(0);
-  Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
 
   uint32_t it = 0;

@@ -245,6 +245,8 @@ int mgn_selftest_umma_pair(const void* a, const void* b, float* d, int n, int ks
 /* Developer micro-benchmark (csrc/probe.cu, tools/probe.py): cycle counts of TMEM loads / stores by number of active
  * warps and of product issue-to-completion latencies on one SM; out_dev [64] int64. */
 int mgn_probe_sm(long long* out_dev, int iters, void* stream);
+/* Developer micro-benchmark of the SM <-> L2 / DRAM path with bulk copies (csrc/probe.cu: modes 0..6); tools/probe.py. */
+int mgn_probe_mem(void* buf, const void* table, long long* out_dev, int mode, int chunks, int grid, void* stream);
 
 #ifdef __cplusplus
 }
