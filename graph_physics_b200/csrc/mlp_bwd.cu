@@ -939,6 +939,8 @@ struct NodeBwdParams {
   float* grad;
   int no_norm;              // the block has no RMSNorm (decoder): dz4 = g, no scale gradient
   float inv_sqrt_d, norm_d; // RMSNorm: true hidden size d and d^-1/2
+  long long* dbg;           // developer timeline (MGN_TIMELINE builds)
+  int dbg_cap;
 };
 
 __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
@@ -1005,9 +1007,13 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   float dsc = 0.f;
   float db1a = 0.f, db1b = 0.f, db2a = 0.f, db2b = 0.f, db3a = 0.f, db3b = 0.f, db4a = 0.f, db4b = 0.f;
   uint32_t it = 0;
+  Timeline tl;
+  tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
+  tl.stamp();     // kernel body start
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
     const uint32_t q0 = 5 * it;
+    tl.stamp();   // 0 tile top
     auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
     if (m.tid == 0) {          // the three saved activation tiles arrive as they were stored: one bulk copy each
       mbar_arrive_expect_tx(&bar_h, 3 * SLOT);
@@ -1016,8 +1022,19 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       bulk_g2s(sH1, reinterpret_cast<const uint8_t*>(p.h1) + (size_t)tile * SLOT, SLOT, &bar_h);
     }
     load8_f32_to_tile(sG, 128, 0, p.g_xout, m, rf, pol_keep);
+    tl.stamp();   // 1 g tile built
     mbar_wait(&bar_h, it & 1);
     tile_ready();
+    tl.stamp();   // 2 h1..h3 landed
+    // the next tile's inputs into L2 while this tile computes (after this tile's own loads: every CTA is at the same
+    // point of its tile, so a prefetch issued with them would only double the burst)
+    if (m.tid == 32 && tile + gridDim.x < num_tiles) {
+      const long long nt = tile + gridDim.x;
+      prefetch_tile_rows_l2(p.g_xout, nt * TILE_ROWS, p.N, 512);
+      bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h3) + (size_t)nt * SLOT, SLOT);
+      bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h2) + (size_t)nt * SLOT, SLOT);
+      bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h1) + (size_t)nt * SLOT, SLOT);
+    }
     // ---- R4: z4 = h3 W4'^T, RMSNorm backward
     {
       if (m.tid == 0) {
@@ -1033,6 +1050,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       if (!p.no_norm) dsc += rmsnorm_bwd_q(tm_W + qoff, bb, sc, sG, tail->red, m, p.inv_sqrt_d, p.norm_d);      // else sG already holds dz4 = g
       tile_ready();
     }
+    tl.stamp();   // 3 R4 + norm
     // ---- D4
     if (m.tid == 0) {
       fence_after_sync();
@@ -1045,6 +1063,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     if (m.tid == 0) issue_load(q0 + 2);
     epi_relu_mask_q(tm_W + qoff, sH3, m);
     tile_ready();
+    tl.stamp();   // 4 D4
     // ---- D3
     if (m.tid == 0) {
       wait_load(q0 + 1);
@@ -1058,6 +1077,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     if (m.tid == 0) issue_load(q0 + 3);
     epi_relu_mask_q(tm_W + qoff, sH2, m);
     tile_ready();
+    tl.stamp();   // 5 D3
     // ---- D2
     if (m.tid == 0) {
       wait_load(q0 + 2);
@@ -1071,6 +1091,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     if (m.tid == 0) issue_load(q0 + 4);
     epi_relu_mask_q(tm_W + qoff, sH1, m);     // sH1 <- dz1'
     tile_ready();
+    tl.stamp();   // 6 D2
     // ---- D1a: g_x = g_xout + dz1' W1'[:, :128]
     if (m.tid == 0) {
       wait_load(q0 + 3);
@@ -1101,6 +1122,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     acc_to_stage_q(tm_W + qoff, stage, m);
     fence_before_sync();
     __syncthreads();
+    tl.stamp();   // 7 D1a staged
     // ---- D1b issued now (working accumulator free); g_x written meanwhile
     if (m.tid == 0) {
       wait_load(q0 + 4);
@@ -1116,6 +1138,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
         st_f4_hint(p.g_x + g * H + 4 * m.lane,
                    make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_keep);
     }
+    tl.stamp();   // 8 g_x written
     mma_wait();
     if (m.tid == 0) issue_load(q0 + 6);
     __syncthreads();    // all reads of the g_x staging are done
@@ -1129,7 +1152,9 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       if (g >= 0) st_f4_hint(p.g_aggr + g * H + 4 * m.lane, v, pol_keep);
     }
     __syncthreads();
+    tl.stamp();   // 9 g_aggr written
   }
+  tl.stamp();     // loop done
   fence_after_sync();
   flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_N_W4, p.grad + GB_N_W3, p.grad + GB_N_W2,
                   smem, m, pol_keep);
@@ -1143,6 +1168,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   atomicAdd(p.grad + GB_N_B1 + 2 * cp, db1a);
   atomicAdd(p.grad + GB_N_B1 + 2 * cp + 1, db1b);
   atomicAdd(p.grad + GB_N_SC + m.c0 + m.lane, dsc);
+  tl.stamp();     // flush issued
   fence_before_sync();
   __syncthreads();
   if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
@@ -1295,6 +1321,12 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
       const long long g = rf(i);
       old[i] = g >= 0 ? ld_f4_hint(p.g_x + g * H + 4 * m.lane, pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    if (m.tid == 32 && tile + gridDim.x < num_tiles) {      // the next tile's inputs into L2, after this tile's own loads
+      const long long n0 = (tile + gridDim.x) * TILE_ROWS;
+      prefetch_tile_rows_l2(p.dP, n0, p.N, 512);
+      prefetch_tile_rows_l2(p.x, n0, p.N, 512);
+      prefetch_tile_rows_l2(p.g_x, n0, p.N, 512);
+    }
     mbar_wait(&bar_mma, phase);
     phase ^= 1;
     fence_after_sync();
@@ -1367,6 +1399,12 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
     load8_f16_to_tile(sG, p.dz1, m, rf);
     load8_f32_to_tile(sU, 128, 0, p.x, m, rf, pol_keep);
     load8_f32_to_tile(sU, 128, 128, p.aggr, m, rf, pol_keep);
+    if (m.tid == 32 && tile + gridDim.x < num_tiles) {      // the next tile's inputs into L2, a tile time ahead
+      const long long n0 = (tile + gridDim.x) * TILE_ROWS;
+      prefetch_tile_rows_l2(p.dz1, n0, p.N, 256);
+      prefetch_tile_rows_l2(p.x, n0, p.N, 512);
+      prefetch_tile_rows_l2(p.aggr, n0, p.N, 512);
+    }
     fence_async_smem();
     fence_before_sync();
     __syncthreads();
@@ -1557,6 +1595,7 @@ extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, con
   p.g_x = g_x; p.g_aggr = g_aggr; p.dz1 = (__half*)dz1;
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
   p.b4 = b4; p.scale = scale; p.grad = grad_block; p.no_norm = flags & 1;
+  p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_bwd: norm_dim must be in 1..128");
   p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   static bool attr = false;

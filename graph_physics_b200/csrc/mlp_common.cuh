@@ -252,6 +252,14 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 __device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+// one thread: the rows [row0, row0 + 128) of a row-major array (row_bytes a multiple of 16) into L2 -- the persistent
+// kernels call it for the tile they will process NEXT, a whole tile time ahead of its loads
+__device__ __forceinline__ void prefetch_tile_rows_l2(const void* base, long long row0, long long rows_total,
+                                                      uint32_t row_bytes) {
+  if (row0 >= rows_total) return;
+  const long long nr = (rows_total - row0) < TILE_ROWS ? (rows_total - row0) : TILE_ROWS;
+  bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(base) + row0 * row_bytes, (uint32_t)(nr * row_bytes));
+}
 // one 512-byte fp32 row = 4 lines
 __device__ __forceinline__ void prefetch_row_f32(const float* row) {
   const char* c = reinterpret_cast<const char*>(row);

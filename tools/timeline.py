@@ -38,6 +38,8 @@ if which == "edge_bwd_saved":
     cap = 11 * 19 + 2
 if which == "edge_hl_save":
     cap = 10 * 19
+if which == "node_bwd":
+    cap = 10 * 4 + 3
 if fine:
     cap = fine * 19
 ge_in = torch.randn(E, 128, device=dev)
@@ -57,8 +59,18 @@ if which in ("edge_bwd_saved", "edge_hl_save"):
                     aggr=aggr, h_saves=hs)
 
 
+nsaves = ops.node_saves(N, dev) if hasattr(ops, "node_saves") else None
+if which == "node_bwd":
+    ops.node_fwd(x, aggr, packed, b[4], b[5], b[6], b[7], sc, x_out=x2, saves=nsaves)
+g_xout = torch.randn(N, 128, device=dev)
+g_x, g_ag = torch.empty_like(x), torch.empty_like(x)
+dz1n = torch.empty((N, 128), dtype=torch.float16, device=dev)
+
+
 def run():
-    if which == "edge_bwd_saved":
+    if which == "node_bwd":
+        ops.node_bwd(g_xout, nsaves, packed, b[7], sc, gblock, g_x=g_x, g_aggr=g_ag, dz1=dz1n)
+    elif which == "edge_bwd_saved":
         ops.edge_bwd_saved(hs, ge_in, g_aggr, csr.receivers, N, packed, b[3], sc, gblock, dz16=dz16)
     elif which == "edge_hl_save":
         ops.edge_fwd_hl(e16, lo16, P, csr.senders, csr.receivers, N, packed, b[1], b[2], b[3], sc, hi_out=dz16,
@@ -111,6 +123,12 @@ if which in ("edge_hl", "edge_hl_save"):
 if which == "edge_bwd_saved":
     names = ["readout", "upstream", "g build", "R4 wait", "norm bwd", "D4", "D3", "D2", "D1", "stage g_e", "next"]
     per = 11
+if which == "node_bwd":
+    names = ["g tile", "h wait", "R4+norm", "D4", "D3", "D2", "D1a", "g_x out", "D1b+g_aggr", "next"]
+    per = 10
+    print("entry -> first tile", t[1] - t[0], "| after last tile -> loop done", t[-2] - t[-3], "flush", t[-1] - t[-2],
+          "kernel body", t[-1] - t[0])
+    t = t[1:-2]
 if fine:
     per = fine
     names = [f"s{i}" for i in range(fine)]
