@@ -95,6 +95,12 @@ __global__ void __launch_bounds__(NT, 1) edge_fwd_hl_kernel(const __grid_constan
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
+  // the first tile's image and remainder (written by the previous step's edge kernel, three launches back -- not by
+  // the kernel griddepcontrol.wait is for) into L2 while the previous kernel drains
+  if (m.tid == 64 && (long long)blockIdx.x * TILE_ROWS < p.E) {
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.hi_in) + (size_t)blockIdx.x * TILE_BYTES, TILE_BYTES);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.lo_in) + (size_t)blockIdx.x * TILE_BYTES, TILE_BYTES);
+  }
   fence_before_sync();
   __syncthreads();
   fence_after_sync();

@@ -665,6 +665,16 @@ __global__ void __launch_bounds__(NT, 1) edge_bwd_saved_kernel(const EdgeBwdSave
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
+  // The first tile's streams into L2 while the previous kernel drains: the hidden images were written by the forward
+  // pass and g_e by the edge backward of the previous step, five launches back -- none of them by the kernel this
+  // one's griddepcontrol.wait is for, so touching them here is safe.
+  if (m.tid == 64 && (long long)blockIdx.x * TILE_ROWS < p.E) {
+    const long long t0 = blockIdx.x;
+    prefetch_tile_rows_l2(p.g_e, t0 * TILE_ROWS, p.E, 512);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h3) + (size_t)t0 * SLOT, SLOT);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h2) + (size_t)t0 * SLOT, SLOT);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h1) + (size_t)t0 * SLOT, SLOT);
+  }
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
@@ -966,6 +976,13 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
+  // the first tile's hidden images (written by the forward pass, not by the kernel griddepcontrol.wait is for) into L2
+  // while the previous kernel drains
+  if (m.tid == 64 && (long long)blockIdx.x * TILE_ROWS < p.N) {
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h3) + (size_t)blockIdx.x * SLOT, SLOT);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h2) + (size_t)blockIdx.x * SLOT, SLOT);
+    bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h1) + (size_t)blockIdx.x * SLOT, SLOT);
+  }
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
@@ -1263,6 +1280,11 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<512>(&tmem_slot);
+  // x (forward pass) and g_x (node_bwd, four launches back) of the first tile into L2 while the previous kernel drains
+  if (m.tid == 64) {
+    prefetch_tile_rows_l2(p.x, (long long)blockIdx.x * TILE_ROWS, p.N, 512);
+    prefetch_tile_rows_l2(p.g_x, (long long)blockIdx.x * TILE_ROWS, p.N, 512);
+  }
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
@@ -1379,6 +1401,11 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
     mbar_init_fence();
   }
   if (m.warp == 0) tmem_alloc<256>(&tmem_slot);
+  // x and aggr (forward pass) of the first tile into L2 while the previous kernel drains
+  if (m.tid == 64) {
+    prefetch_tile_rows_l2(p.x, (long long)blockIdx.x * TILE_ROWS, p.N, 512);
+    prefetch_tile_rows_l2(p.aggr, (long long)blockIdx.x * TILE_ROWS, p.N, 512);
+  }
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
