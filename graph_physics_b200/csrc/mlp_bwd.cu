@@ -951,6 +951,7 @@ struct NodeBwdParams {
   float inv_sqrt_d, norm_d; // RMSNorm: true hidden size d and d^-1/2
   long long* dbg;           // developer timeline (MGN_TIMELINE builds)
   int dbg_cap;
+  int32_t* ready_out;       // or null: ready_out[tile] = 1 once the tile's dz1, g_x, g_aggr rows are written (chaining)
 };
 
 __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
@@ -1169,6 +1170,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       if (g >= 0) st_f4_hint(p.g_aggr + g * H + 4 * m.lane, v, pol_keep);
     }
     __syncthreads();
+    if (p.ready_out != nullptr && m.tid == 0) tile_publish(p.ready_out, tile);
     tl.stamp();   // 9 g_aggr written
   }
   tl.stamp();     // loop done
@@ -1386,6 +1388,8 @@ struct NodeWgrad1Params {
   const float* x;
   const float* aggr;
   float* grad;
+  int32_t* ready_in;        // or null: tile-level chaining with the node_bwd launch before this one (mlp_common.cuh):
+  int32_t* sched;           // ready flags set by node_bwd, {next tile, CTAs done}
 };
 
 __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Params p) {
@@ -1409,26 +1413,39 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
-  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
+  const bool chained = p.ready_in != nullptr;
+  if (!chained) pdl_wait();     // the previous kernel in the stream is complete: global memory may be touched
+  pdl_launch();                 // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t tm = tmem_slot;
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
   const uint64_t pol_keep = policy_evict_last();
+  int* s_tile = reinterpret_cast<int*>(tail->red);
   uint32_t it = 0;
-  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+  for (long long tile = blockIdx.x;; tile += gridDim.x, ++it) {
+    if (chained) {      // next tile in index order = the order node_bwd finishes them in; wait for its rows
+      if (m.tid == 0) {
+        const int t = atomicAdd(p.sched, 1);
+        if (t < num_tiles) tile_acquire(p.ready_in, t);
+        *s_tile = t;
+      }
+      __syncthreads();
+      tile = *s_tile;   // (thread 0 writes it again only after the barrier before the products below)
+    }
+    if (tile >= num_tiles) break;
     const long long row0 = tile * TILE_ROWS;
     const uint32_t b = it & 1;
     uint8_t* sG = smem + b * 3 * SLOT;          // 32 KB
     uint8_t* sU = sG + SLOT;                    // 128 x 256 fp16 = 64 KB
     auto rf = [&](int i) -> long long { const long long g = row0 + m.warp * 8 + i; return g < p.N ? g : -1; };
     if (it >= 2) mbar_wait(&bar_set[b], ((it >> 1) - 1) & 1);
-    load8_f16_to_tile(sG, p.dz1, m, rf);
+    if (chained) load8_f16_to_tile_cg(sG, p.dz1, m, rf);
+    else load8_f16_to_tile(sG, p.dz1, m, rf);
     load8_f32_to_tile(sU, 128, 0, p.x, m, rf, pol_keep);
     load8_f32_to_tile(sU, 128, 128, p.aggr, m, rf, pol_keep);
-    if (m.tid == 32 && tile + gridDim.x < num_tiles) {      // the next tile's inputs into L2, a tile time ahead
+    if (m.tid == 32 && tile + gridDim.x < num_tiles) {      // the (likely) next tile's inputs into L2, a tile time ahead
       const long long n0 = (tile + gridDim.x) * TILE_ROWS;
-      prefetch_tile_rows_l2(p.dz1, n0, p.N, 256);
+      if (!chained) prefetch_tile_rows_l2(p.dz1, n0, p.N, 256);
       prefetch_tile_rows_l2(p.x, n0, p.N, 512);
       prefetch_tile_rows_l2(p.aggr, n0, p.N, 512);
     }
@@ -1446,6 +1463,10 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
                 (ks > 0 || it > 0) ? 1u : 0u);
       mma_commit(&bar_set[b]);
     }
+  }
+  if (chained) {
+    if (m.tid == 0) sched_done(p.sched);
+    pdl_wait();       // node_bwd is complete (its gradient flush included): what this launch's successors rely on
   }
   // wait for the last commit of each set (commits complete in order; waiting both is simplest)
   if (it >= 1) mbar_wait(&bar_set[(it - 1) & 1], ((it - 1) >> 1) & 1);
@@ -1611,9 +1632,20 @@ extern "C" int mgn_edge_bwd_saved(int64_t E, int64_t N, const void* h1, const vo
 
 // Backward of the node update (autograd of layers.py:733-746, 699) from the fp16 hidden saves.
 // flags bit 0: the block has no RMSNorm (see mgn_node_fwd2)
+extern "C" int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                             float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out,
+                             void* stream_);
 extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                              float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
                              const float* scale, float* grad_block, int flags, int norm_dim, void* stream_) {
+  return mgn_node_bwd3(N, g_xout, h1, h2, h3, g_x, g_aggr, dz1, packed, b4, scale, grad_block, flags, norm_dim, nullptr,
+                       stream_);
+}
+extern "C" int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                             float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out,
+                             void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && g_xout && h1 && h2 && h3 && g_x && g_aggr && dz1 && packed && b4 && scale && grad_block,
                 "node_bwd: bad args");
@@ -1623,6 +1655,7 @@ extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, con
   p.W = reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_NODE);
   p.b4 = b4; p.scale = scale; p.grad = grad_block; p.no_norm = flags & 1;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
+  p.ready_out = ready_out;
   MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_bwd: norm_dim must be in 1..128");
   p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   static bool attr = false;
@@ -1675,11 +1708,18 @@ extern "C" int mgn_p_bwd(int64_t N, const void* dP, const float* x, float* g_x, 
 }
 
 // Weight gradient of node_block layer 1: dW1' += dz1'^T [x | aggr].
+extern "C" int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
+                                int32_t* ready_in, int32_t* sched, void* stream_);
 extern "C" int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                                void* stream_) {
+  return mgn_node_wgrad1c(N, dz1, x, aggr, grad_block, nullptr, nullptr, stream_);
+}
+extern "C" int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
+                                int32_t* ready_in, int32_t* sched, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && dz1 && x && aggr && grad_block, "node_wgrad1: bad args");
-  NodeWgrad1Params p{N, (const __half*)dz1, x, aggr, grad_block};
+  MGN_CHECK_ARG((ready_in == nullptr) == (sched == nullptr), "node_wgrad1: ready_in and sched go together");
+  NodeWgrad1Params p{N, (const __half*)dz1, x, aggr, grad_block, ready_in, sched};
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(node_wgrad1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_WGRAD1_SMEM));

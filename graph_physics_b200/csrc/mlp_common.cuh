@@ -252,6 +252,46 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 __device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+// ------------------------------------------------------------------ tile-level chaining of two launches
+// A persistent kernel that ends in a wave tail (481 node tiles on 148 SMs: 37 CTAs run a fourth tile while 111 SMs
+// idle) can hand its tiles to the NEXT launch one by one: the producer publishes ready[tile] = 1 after the tile's
+// last store, the consumer -- launched with programmatic stream serialization, so its CTAs start on the SMs the
+// producer's CTAs leave -- takes tiles from a counter in index order (= the order the producer finishes them in),
+// waits for ready[tile], clears it for the next launch, and calls griddepcontrol.wait only when its tiles are done
+// (so that ITS successor still sees "predecessor complete => everything before it complete").  Every producer CTA is
+// resident before a consumer CTA can start, so the wait cannot deadlock; it is bounded like the mbarrier waits.
+// sched[0] = next tile, sched[1] = CTAs that finished; the last one to finish zeroes both.
+__device__ __forceinline__ void tile_publish(int32_t* ready, long long tile) {      // one thread, after a CTA barrier
+  __threadfence();
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(ready + tile), "r"(1) : "memory");
+}
+__device__ __forceinline__ void tile_acquire_tagged(int32_t* ready, long long tile, uint32_t tag) {   // one thread
+  int v;
+  unsigned long long t0 = 0;
+#pragma unroll 1
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ready + tile) : "memory");
+    if (v != 0) break;
+    if (spin >= MBAR_FAST_POLLS) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (spin == MBAR_FAST_POLLS) t0 = t;
+      else if (t - t0 > MBAR_TIMEOUT_NS) mbar_timeout(0xf1a9u /* a ready flag, not a barrier */, (uint32_t)tile, tag);
+      if (spin == 0xffffffffu) spin = MBAR_FAST_POLLS;
+    }
+  }
+  ready[tile] = 0;
+}
+#define tile_acquire(ready, tile) \
+  tile_acquire_tagged((ready), (tile), ((uint32_t)(MGN_FILE_ID) << 16) | (uint32_t)__LINE__)
+__device__ __forceinline__ void sched_done(int32_t* sched) {                        // one thread, at the CTA's end
+  if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
+    sched[0] = 0;
+    __threadfence();
+    sched[1] = 0;
+  }
+}
+
 // one thread: the rows [row0, row0 + 128) of a row-major array (row_bytes a multiple of 16) into L2 -- the persistent
 // kernels call it for the tile they will process NEXT, a whole tile time ahead of its loads
 __device__ __forceinline__ void prefetch_tile_rows_l2(const void* base, long long row0, long long rows_total,

@@ -339,4 +339,21 @@ __device__ __forceinline__ void load8_f16_to_tile(uint8_t* tile, const __half* _
     *reinterpret_cast<uint4*>(tile + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q)) = v[i];
 }
 
+// the same through L2 (ld.global.cg): for rows another kernel may have written while this one was already running
+// (tile-level chaining, mlp_common.cuh) -- the non-coherent path of __ldg is for data that is read-only for the launch
+template <class RowFn>
+__device__ __forceinline__ void load8_f16_to_tile_cg(uint8_t* tile, const __half* __restrict__ src, const Map& m,
+                                                     RowFn grow) {
+  const int hw = m.lane >> 4, q = m.lane & 15;
+  uint4 v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long g = grow(2 * i + hw);
+    v[i] = (g >= 0) ? __ldcg(reinterpret_cast<const uint4*>(src + g * H + 8 * q)) : make_uint4(0, 0, 0, 0);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    *reinterpret_cast<uint4*>(tile + tile_off(128, m.warp * 8 + 2 * i + hw, 8 * q)) = v[i];
+}
+
 }  // namespace mgn

@@ -3,6 +3,7 @@ autograd glue lives in processor.py).  All tensors are CUDA, contiguous, fp32 un
 stated; H = 128."""
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -248,9 +249,21 @@ def edge_bwd_saved(h_saves, g_e, g_aggr, receivers, num_nodes, packed, b4, scale
     return g_e, dz16
 
 
+# Tile-level chaining of two launches (csrc/mlp_common.cuh): the producer publishes ready[tile] after a tile's last
+# store, the consumer -- whose CTAs start on the SMs the producer's wave tail leaves idle -- takes tiles from a counter
+# and waits for the flag.  MGN_CHAIN=0 switches it off (plain stream order).
+CHAIN = os.environ.get("MGN_CHAIN", "1") != "0"
+
+
+def chain_state(num_rows: int, device) -> torch.Tensor:
+    """int32 [tiles + 2]: ready flags of one producer / consumer pair + {next tile, CTAs done}; starts (and is left) at
+    zero.  ready = state[:tiles], sched = state[tiles:]."""
+    return torch.zeros((num_rows + 127) // 128 + 2, dtype=torch.int32, device=device)
+
+
 def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None, norm: bool = True,
-             norm_dim: int = H):
-    """-> (g_x direct part, g_aggr, dz1 fp16)."""
+             norm_dim: int = H, chain: Optional[torch.Tensor] = None):
+    """-> (g_x direct part, g_aggr, dz1 fp16).  chain: `chain_state(N)` shared with the node_wgrad1 call that follows."""
     N = g_xout.shape[0]
     if g_x is None:
         g_x = torch.empty_like(g_xout)
@@ -259,9 +272,9 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
     if dz1 is None:
         dz1 = torch.empty((N, H), dtype=torch.float16, device=g_xout.device)
     h1, h2, h3 = saves
-    L.check(L.lib().mgn_node_bwd2(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
+    L.check(L.lib().mgn_node_bwd3(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
                                   L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.i32(0 if norm else 1), L.i32(norm_dim),
-                                  L.stream()))
+                                  L.p(chain), L.stream()))
     return g_x, g_aggr, dz1
 
 
@@ -288,5 +301,9 @@ def p_bwd(dP, x, g_x, packed, grad_block):
     return g_x
 
 
-def node_wgrad1(dz1, x, aggr, grad_block):
-    L.check(L.lib().mgn_node_wgrad1(L.i64(x.shape[0]), L.p(dz1), L.p(x), L.p(aggr), L.p(grad_block), L.stream()))
+def node_wgrad1(dz1, x, aggr, grad_block, chain: Optional[torch.Tensor] = None):
+    """chain: the `chain_state(N)` the node_bwd call JUST BEFORE this one (same stream) was given, or None."""
+    N = x.shape[0]
+    sched = chain[(N + 127) // 128:] if chain is not None else None
+    L.check(L.lib().mgn_node_wgrad1c(L.i64(N), L.p(dz1), L.p(x), L.p(aggr), L.p(grad_block), L.p(chain), L.p(sched),
+                                     L.stream()))

@@ -239,6 +239,7 @@ class _ProcessorFn(torch.autograd.Function):
         gx_new = torch.empty_like(gx)
         g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
+        chain_nw = ops.chain_state(N, dev) if ops.CHAIN else None     # node_bwd -> node_wgrad1, tile by tile
         dz16 = ops.e16_image(E, dev)       # dz1 of the current step: written by edge_bwd, gathered by p_bwd
         dP = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
         if E > 0:
@@ -252,8 +253,8 @@ class _ProcessorFn(torch.autograd.Function):
         for k in range(K - 1, -1, -1):
             b = prm[18 * k:18 * (k + 1)]
             _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
-                   g_aggr=g_aggr, dz1=dz1, norm_dim=nd)
-            _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k])
+                   g_aggr=g_aggr, dz1=dz1, norm_dim=nd, chain=chain_nw)
+            _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k], chain=chain_nw)
             if E > 0:
                 if ctx.esaves[k] is not None:
                     if not have_ge:          # no upstream edge gradient: the in-place kernel adds to zeros

@@ -192,6 +192,18 @@ int mgn_node_bwd(int64_t N, const float* g_xout, const void* h1, const void* h2,
 int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                   float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
                   const float* scale, float* grad_block, int flags, int norm_dim, void* stream);
+/* Tile-level chaining of two launches (no counterpart in the reference: it is what removes the wave tail of the
+ * persistent node kernels -- 481 tiles on 148 SMs).  mgn_node_bwd3 = mgn_node_bwd2 that also publishes
+ * ready_out[tile] = 1 (int32, one per 128-row tile) after the tile's dz1 / g_x / g_aggr rows are written;
+ * mgn_node_wgrad1c = mgn_node_wgrad1 that, launched DIRECTLY after it on the same stream, takes its tiles from
+ * sched[0] in index order, waits for ready_in[tile] (bounded wait, mgn_hang_report) and clears it, and only then waits
+ * for the whole previous launch -- its CTAs start on the SMs node_bwd's last wave leaves idle.  ready / sched
+ * ({next tile, CTAs done}) start at zero and are left at zero.  NULL for both = plain stream order. */
+int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
+                  float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
+                  const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out, void* stream);
+int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
+                     int32_t* ready_in, int32_t* sched, void* stream);
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);

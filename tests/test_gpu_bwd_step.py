@@ -234,3 +234,47 @@ def test_edge_backward_from_saved_activations_equals_recompute(golden_dir, copie
         assert torch.equal(ops.image_rows(dz_s, E), ops.image_rows(dz_r, E))
         assert float((ge_s - ge_r).abs().max()) <= 1e-6 * float(ge_r.abs().max())
         assert float((grad_s - grad_r).abs().max()) <= 1e-5 * float(grad_r.abs().max())
+
+
+@pytest.mark.parametrize("copies", [1, 32])
+def test_chained_node_wgrad1_equals_stream_order(golden_dir, copies):
+    """Tile-level chaining (csrc/mlp_common.cuh): node_bwd publishes a ready flag per tile, node_wgrad1 -- launched
+    directly after it -- takes tiles from a counter and waits for the flags.  Same dz1 rows, so dW1' must agree with
+    the stream-ordered pair up to the order of the cross-CTA reduce-adds (fp32, different tile-to-CTA assignment:
+    tolerance 1e-5 of the largest entry); the chain state is back at zero afterwards; and a second pair on the same
+    state works (the flags and the counter reset themselves)."""
+    from graph_physics_b200 import graph as G, ops
+    dev = "cuda"
+    z = np.load(os.path.join(golden_dir, "cylinder_mesh.npz"))
+    n1 = z["points"].shape[0]
+    N = n1 * copies
+    torch.manual_seed(5 + copies)
+    ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    nb = [torch.randn(128, device=dev) * 0.05 for _ in range(4)]
+    nsc = 1.0 + 0.1 * torch.randn(128, device=dev)
+    packed = ops.pack_block(ew, nw)
+    x, aggr, gx = (torch.randn(N, 128, device=dev) for _ in range(3))
+    saves = ops.node_saves(N, dev)
+    ops.node_fwd(x, aggr, packed, nb[0], nb[1], nb[2], nb[3], nsc, saves=saves)
+
+    def pair(chain):
+        grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
+        g_x, g_aggr, dz1 = ops.node_bwd(gx, saves, packed, nb[3], nsc, grad, chain=chain)
+        ops.node_wgrad1(dz1, x, aggr, grad, chain=chain)
+        torch.cuda.synchronize()
+        return grad, g_x, g_aggr, dz1
+
+    ref = pair(None)
+    chain = ops.chain_state(N, dev)
+    for _ in range(3):
+        got = pair(chain)
+        assert int(chain.abs().sum()) == 0
+        for a, b in zip(got[1:], ref[1:]):
+            assert torch.equal(a, b)
+        w_ref, w_got = ops.split_grad_block(ref[0])["node_block.0.weight"], ops.split_grad_block(got[0])["node_block.0.weight"]
+        assert float((w_got - w_ref).abs().max()) <= 1e-5 * float(w_ref.abs().max())
+        rest_ref, rest_got = ref[0].clone(), got[0].clone()
+        ops.split_grad_block(rest_ref)["node_block.0.weight"].zero_()
+        ops.split_grad_block(rest_got)["node_block.0.weight"].zero_()
+        assert float((rest_got - rest_ref).abs().max()) <= 1e-5 * float(rest_ref.abs().max())
