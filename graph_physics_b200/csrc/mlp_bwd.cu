@@ -1473,8 +1473,10 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   if (it >= 2) mbar_wait(&bar_set[it & 1], ((it - 2) >> 1) & 1);
   fence_after_sync();
   __syncthreads();          // every thread is past its last operand store: the operand buffers are dead
-  flush_acc_bulk(tm + qoff, p.grad + GB_N_W1, 256, smem, m, policy_evict_last());
-  flush_acc_bulk(tm + 128 + qoff, p.grad + GB_N_W1 + 128, 256, smem, m, policy_evict_last());
+  if (it > 0) {             // (a chained CTA that arrived after the last tile was taken has nothing to add)
+    flush_acc_bulk(tm + qoff, p.grad + GB_N_W1, 256, smem, m, policy_evict_last());
+    flush_acc_bulk(tm + 128 + qoff, p.grad + GB_N_W1 + 128, 256, smem, m, policy_evict_last());
+  }
   fence_before_sync();
   __syncthreads();
   if (m.warp == 0) tmem_dealloc<256>(tmem_slot);

@@ -50,6 +50,7 @@ struct FwdParams {
                               // the residual stream as image + remainder); `out` may then be null
   long long* dbg;             // developer timeline (null = off)
   int dbg_cap;
+  int32_t* ready_out;         // node update, or null: ready_out[tile] = 1 once the tile's output rows are written (chaining)
   int no_norm;                // node: the block has no RMSNorm (the decoder, build_mlp(..., layer_norm=False)): out = in0 + z4
 };
 
@@ -412,6 +413,7 @@ __global__ void __launch_bounds__(NT, 1) mlp_fwd_kernel(const FwdParams p) {
       if (EDGE && cur >= 0) flush_run(cur, sum, first_run);
     }
     __syncthreads();      // staging / operand tile free for the next tile
+    if (!EDGE && p.ready_out != nullptr && m.tid == 0) tile_publish(p.ready_out, tile);
     tl.stamp();   // 10 output done
   }
   if (!w_ready) mbar_wait(&wbar, 0);   // never exit with the weight copy in flight
@@ -430,6 +432,8 @@ struct PFwdParams {
   const __half* Wcat;    // panel tile, 256 rows (out) x 128 cols (in) = 64 KB
   const float* b1;       // [128] edge-block layer-1 bias, folded into P_i
   __half* P;             // [N,256]
+  int32_t* ready_in;     // or null: tile-level chaining with the node update launched before this one
+  int32_t* sched;        // (mlp_common.cuh): ready flags of x's tiles, {next tile, CTAs done}
 };
 
 __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
@@ -457,8 +461,9 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
-  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
+  const bool chained = p.ready_in != nullptr;
+  if (!chained) pdl_wait();   // the previous kernel in the stream is complete: global memory may be touched
+  pdl_launch();               // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tmem_acc = tmem_slot;
   if (m.tid == 0) {
     mbar_arrive_expect_tx(&wbar, 2 * TILE_BYTES);
@@ -471,13 +476,26 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
   bool w_ready = false;
   uint32_t phase = 0;
   const long long num_tiles = (p.N + TILE_ROWS - 1) / TILE_ROWS;
-  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  int* s_tile = reinterpret_cast<int*>(tail->red);
+  for (long long tile = blockIdx.x;; tile += gridDim.x) {
+    if (chained) {      // next tile in index order = the order the node update finishes them in; wait for its rows
+      if (m.tid == 0) {
+        const int t = atomicAdd(p.sched, 1);
+        if (t < num_tiles) tile_acquire(p.ready_in, t);
+        *s_tile = t;
+      }
+      __syncthreads();
+      tile = *s_tile;   // (thread 0 writes it again only after the barriers below)
+    }
+    if (tile >= num_tiles) break;
     const long long row0 = tile * TILE_ROWS;
-    load8_f32_to_tile(sA, 128, 0, p.x, m, [&](int i) -> long long {
+    auto rfx = [&](int i) -> long long {
       const long long g = row0 + m.warp * 8 + i;
       return g < p.N ? g : -1;
-    }, pol_keep);
-    if (m.tid == 0 && tile + gridDim.x < num_tiles) {      // next tile's rows into L2: one bulk prefetch
+    };
+    if (chained) load8_f32_to_tile_cg(sA, 128, 0, p.x, m, rfx);
+    else load8_f32_to_tile(sA, 128, 0, p.x, m, rfx, pol_keep);
+    if (!chained && m.tid == 0 && tile + gridDim.x < num_tiles) {      // next tile's rows into L2: one bulk prefetch
       const long long n0 = (tile + gridDim.x) * TILE_ROWS;
       const long long nr = (p.N - n0) < TILE_ROWS ? (p.N - n0) : TILE_ROWS;
       bulk_prefetch_l2(p.x + n0 * H, (uint32_t)(nr * 512));
@@ -529,6 +547,10 @@ __global__ void __launch_bounds__(NT, 1) p_fwd_kernel(const PFwdParams p) {
       bulk_commit();
     }
     (void)grow;
+  }
+  if (chained) {
+    if (m.tid == 0) sched_done(p.sched);
+    pdl_wait();       // the node update is complete: what this launch's successors rely on
   }
   if (!w_ready) mbar_wait(&wbar, 0);
   if (m.tid < 128) bulk_wait0();
@@ -726,10 +748,21 @@ extern "C" int mgn_edge_fwd2(int64_t E, int64_t N, const float* e_in, const int3
 
 // GraphNetBlock node update (layers.py:733-746, 699): x_out = x + node_block(cat[x, aggr]).
 // flags bit 0: no RMSNorm (x_out = x + MLP(...) with the last layer's bias only; `scale` is ignored but must be valid)
+extern "C" int mgn_node_fwd3(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                             const float* b1, const float* b2, const float* b3, const float* b4,
+                             const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags,
+                             int norm_dim, int32_t* ready_out, void* stream_);
 extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
                              const float* b1, const float* b2, const float* b3, const float* b4,
                              const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags,
                              int norm_dim, void* stream_) {
+  return mgn_node_fwd3(N, x, aggr, x_out, packed, b1, b2, b3, b4, scale, save_h1, save_h2, save_h3, flags, norm_dim,
+                       nullptr, stream_);
+}
+extern "C" int mgn_node_fwd3(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                             const float* b1, const float* b2, const float* b3, const float* b4,
+                             const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags,
+                             int norm_dim, int32_t* ready_out, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && x && aggr && x_out && packed && b1 && b2 && b3 && b4 && scale, "node_fwd: bad args");
   MGN_CHECK_ARG(x != x_out, "node_fwd: in-place not supported");
@@ -741,6 +774,7 @@ extern "C" int mgn_node_fwd2(int64_t N, const float* x, const float* aggr, float
   p.b1 = b1; p.b2 = b2; p.b3 = b3; p.b4 = b4; p.scale = scale;
   p.save_h1 = (__half*)save_h1; p.save_h2 = (__half*)save_h2; p.save_h3 = (__half*)save_h3;
   p.no_norm = flags & 1;
+  p.ready_out = ready_out;
   MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_fwd: norm_dim must be in 1..128");
   p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
@@ -762,12 +796,19 @@ extern "C" int mgn_node_fwd(int64_t N, const float* x, const float* aggr, float*
 }
 
 // per-node layer-1 partial products of the edge block: P = [x W_i^T + b1 | x W_j^T] (fp16)
+extern "C" int mgn_p_fwd_c(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P,
+                           int32_t* ready_in, int32_t* sched, void* stream_);
 extern "C" int mgn_p_fwd(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P,
                          void* stream_) {
+  return mgn_p_fwd_c(N, x, packed, b1_edge, P, nullptr, nullptr, stream_);
+}
+extern "C" int mgn_p_fwd_c(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P,
+                           int32_t* ready_in, int32_t* sched, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && x && packed && b1_edge && P, "p_fwd: bad args");
+  MGN_CHECK_ARG((ready_in == nullptr) == (sched == nullptr), "p_fwd: ready_in and sched go together");
   PFwdParams p{N, x, reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_WCAT),
-               b1_edge, (__half*)P};
+               b1_edge, (__half*)P, ready_in, sched};
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(p_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_FWD_SMEM));

@@ -299,6 +299,25 @@ __device__ __forceinline__ void load8_f32_to_tile(uint8_t* tile, uint32_t tile_r
     *reinterpret_cast<uint2*>(tile + tile_off(tile_rows, m.warp * 8 + i, col0 + 4 * m.lane)) = pk;
   }
 }
+// the same through L2 (ld.global.cg), for rows a chained producer launch may still have been writing when this launch
+// started (tile-level chaining, mlp_common.cuh)
+template <class RowFn>
+__device__ __forceinline__ void load8_f32_to_tile_cg(uint8_t* tile, uint32_t tile_rows, uint32_t col0,
+                                                     const float* __restrict__ src, const Map& m, RowFn grow) {
+  float4 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long g = grow(i);
+    v[i] = (g >= 0) ? __ldcg(reinterpret_cast<const float4*>(src + g * H + 4 * m.lane)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    uint2 pk;
+    pk.x = pack_h2(v[i].x, v[i].y);
+    pk.y = pack_h2(v[i].z, v[i].w);
+    *reinterpret_cast<uint2*>(tile + tile_off(tile_rows, m.warp * 8 + i, col0 + 4 * m.lane)) = pk;
+  }
+}
 // tile row <- fp16(a[ga(i)] + b[gb(i)]).  Consecutive rows that name the same b row (edges of one receiver, CSR
 // order) reuse the registers of the previous row instead of fetching it again (warp-uniform test).
 template <class RowFnA, class RowFnB>

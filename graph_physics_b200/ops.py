@@ -62,11 +62,14 @@ def pack_blocks(blocks: Sequence[Sequence[torch.Tensor]], out: Optional[torch.Te
 
 
 def p_fwd(x: torch.Tensor, packed: torch.Tensor, b1_edge: torch.Tensor,
-          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+          out: Optional[torch.Tensor] = None, chain: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """chain: the `chain_state(N)` the node_fwd call that produced `x` (earlier on the same stream) was given, or None."""
     N = x.shape[0]
     if out is None:
         out = torch.empty((N, 2 * H), dtype=torch.float16, device=x.device)
-    L.check(L.lib().mgn_p_fwd(L.i64(N), L.p(x), L.p(packed), L.p(b1_edge), L.p(out), L.stream()))
+    sched = chain[(N + 127) // 128:] if chain is not None else None
+    L.check(L.lib().mgn_p_fwd_c(L.i64(N), L.p(x), L.p(packed), L.p(b1_edge), L.p(out), L.p(chain), L.p(sched),
+                                L.stream()))
     return out
 
 
@@ -170,17 +173,20 @@ def image_rows(img: torch.Tensor, num_rows: int) -> torch.Tensor:
 
 
 def node_fwd(x: torch.Tensor, aggr: torch.Tensor, packed: torch.Tensor, b1, b2, b3, b4, scale,
-             x_out: Optional[torch.Tensor] = None, saves=None, norm: bool = True, norm_dim: int = H) -> torch.Tensor:
-    """saves: `node_saves(N)` buffers (tile images), or None.  norm=False: the block has no RMSNorm (decoder)."""
+             x_out: Optional[torch.Tensor] = None, saves=None, norm: bool = True, norm_dim: int = H,
+             chain: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """saves: `node_saves(N)` buffers (tile images), or None.  norm=False: the block has no RMSNorm (decoder).
+    chain: `chain_state(N)` shared with the p_fwd call that consumes x_out next (it MUST follow: the flags this call
+    sets are cleared by that consumer)."""
     N = x.shape[0]
     if saves is not None and any(sv.numel() < ((N + 127) // 128) * 128 * H for sv in saves):
         raise ValueError("node_fwd: saves must be node_saves(N) tile-image buffers")
     if x_out is None:
         x_out = torch.empty_like(x)
     s1, s2, s3 = saves if saves is not None else (None, None, None)
-    L.check(L.lib().mgn_node_fwd2(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
+    L.check(L.lib().mgn_node_fwd3(L.i64(N), L.p(x), L.p(aggr), L.p(x_out), L.p(packed), L.p(b1), L.p(b2), L.p(b3),
                                   L.p(b4), L.p(scale), L.p(s1), L.p(s2), L.p(s3), L.i32(0 if norm else 1), L.i32(norm_dim),
-                                  L.stream()))
+                                  L.p(chain), L.stream()))
     return x_out
 
 

@@ -149,6 +149,7 @@ class _ProcessorFn(torch.autograd.Function):
         img = None
         # workspace of the deterministic aggregation (ops.carry_buffer): 8-row slots for step 0, 32-row slots after
         carry = ops.carry_buffer(E, 8, dev) if (ops.DETERMINISTIC and E > 0) else None
+        chain_np = ops.chain_state(N, dev) if (ops.CHAIN and K > 1) else None    # node_fwd(k) -> p_fwd(k+1), tile by tile
         for k in range(K):
             b = prm[18 * k:18 * (k + 1)]
             if need_grad:
@@ -172,7 +173,7 @@ class _ProcessorFn(torch.autograd.Function):
             if not last:
                 img_next = ops.e16_image(E, dev) if need_grad else img_bufs[k & 1]
             lo_next = lo_bufs[k & 1] if (hl and not last) else None
-            _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P)
+            _timed("p_fwd", ops.p_fwd, x, packed[k], b[1], out=P, chain=chain_np if k > 0 else None)
             esv = None
             if hl and k > 0:
                 # training: the edge MLP's hidden activations are kept as tile images (the edge backward of this step
@@ -188,7 +189,7 @@ class _ProcessorFn(torch.autograd.Function):
                        e16_next=img_next, out_in_csr_order=True, e16lo_next=lo_next,
                        write_rows=not (hl and e_out is None), carry=carry, norm_dim=nd, rowptr=csr.rowptr)
             _timed("node_fwd", ops.node_fwd, x, aggr, packed[k], b[10], b[12], b[14], b[16], b[17], x_out=x_out,
-                   saves=sv, norm_dim=nd)
+                   saves=sv, norm_dim=nd, chain=None if last else chain_np)
             if need_grad:
                 aggrs.append(aggr); Ps.append(P); saves.append(sv); xs.append(x_out); e16s.append(img)
                 esaves.append(esv)

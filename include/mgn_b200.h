@@ -204,6 +204,14 @@ int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2
                   const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out, void* stream);
 int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                      int32_t* ready_in, int32_t* sched, void* stream);
+/* The same pair in the forward: mgn_node_fwd3 publishes ready_out[tile] after the tile's x_out rows, mgn_p_fwd_c (the
+ * partial products of the NEXT step, launched after it on the same stream) consumes them. */
+int mgn_node_fwd3(int64_t N, const float* x, const float* aggr, float* x_out, const void* packed,
+                  const float* b1, const float* b2, const float* b3, const float* b4,
+                  const float* scale, void* save_h1, void* save_h2, void* save_h3, int flags, int norm_dim,
+                  int32_t* ready_out, void* stream);
+int mgn_p_fwd_c(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P, int32_t* ready_in,
+                int32_t* sched, void* stream);
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);

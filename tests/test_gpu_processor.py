@@ -210,3 +210,45 @@ def test_fifteen_steps_are_bitwise_reproducible(golden_dir):
     worst = max(mo.rel_l2(a, b) for a, b in zip(w1, w2))
     assert worst < 1e-5, worst
     print(f"15 steps twice: x15, g_x0, g_e0 bitwise equal; weight gradients differ by at most {worst:.1e} (L2 reduction order)")
+
+
+@pytest.mark.parametrize("copies", [3, 32])
+def test_chained_launches_equal_stream_order(golden_dir, copies):
+    """Tile-level chaining (ops.CHAIN: node_fwd -> p_fwd of the next step, node_bwd -> node_wgrad1, p_bwd -> node_bwd)
+    changes WHEN tiles are processed and by which CTA, never what is computed: x15 and the input gradients are bitwise
+    equal to the stream-ordered run, training and inference; the weight gradients agree to the rounding of their
+    cross-CTA reduction."""
+    from graph_physics_b200 import graph as G, ops
+    from graph_physics_b200.models import EncodeProcessDecode, Graph
+    ei, n = _cyl(golden_dir)
+    eid = G.tile_batch(ei.cuda(), n, copies)
+    N, E = copies * n, eid.shape[1]
+    p = mo.init_params(15, hidden=128, seed=0)
+    model = EncodeProcessDecode(15, 128, 128, 128, hidden_size=128, only_processor=True).cuda()
+    _load(model, p)
+    x0, e0, gx = processor_inputs(N, E, 128, seed=6)
+    runs = {}
+    saved = ops.CHAIN
+    try:
+        for chain in (False, True, True):
+            ops.CHAIN = chain
+            for q in model.parameters():
+                q.grad = None
+            xd, ed = x0.cuda().requires_grad_(True), e0.cuda().requires_grad_(True)
+            out = model(Graph(x=xd, edge_index=eid, edge_attr=ed))
+            (out * gx.cuda()).sum().backward()
+            with torch.no_grad():
+                out_inf = model(Graph(x=x0.cuda(), edge_index=eid, edge_attr=e0.cuda()))
+            torch.cuda.synchronize()
+            got = (out.detach().clone(), xd.grad.clone(), ed.grad.clone(), out_inf.clone(),
+                   [q.grad.clone() for q in model.parameters()])
+            if not chain:
+                runs["ref"] = got
+            else:
+                ref = runs["ref"]
+                for a, b in zip(got[:4], ref[:4]):
+                    assert torch.equal(a, b)
+                worst = max(mo.rel_l2(a, b) for a, b in zip(got[4], ref[4]))
+                assert worst < 1e-5, worst
+    finally:
+        ops.CHAIN = saved
