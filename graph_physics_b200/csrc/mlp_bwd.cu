@@ -1028,6 +1028,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   Timeline tl;
   tl.init(m.tid == 0 && blockIdx.x == 0, p.dbg, p.dbg_cap);
   tl.stamp();     // kernel body start
+  cta_trace(p.dbg, p.dbg_cap, 0, 0);
   for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const long long row0 = tile * TILE_ROWS;
     const uint32_t q0 = 5 * it;
@@ -1174,6 +1175,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     tl.stamp();   // 9 g_aggr written
   }
   tl.stamp();     // loop done
+  cta_trace(p.dbg, p.dbg_cap, 0, 2);
   fence_after_sync();
   flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_N_W4, p.grad + GB_N_W3, p.grad + GB_N_W2,
                   smem, m, pol_keep);
@@ -1190,6 +1192,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   tl.stamp();     // flush issued
   fence_before_sync();
   __syncthreads();
+  cta_trace(p.dbg, p.dbg_cap, 0, 3);
   if (m.warp == 0) tmem_dealloc<512>(tmem_slot);
 }
 
@@ -1390,6 +1393,8 @@ struct NodeWgrad1Params {
   float* grad;
   int32_t* ready_in;        // or null: tile-level chaining with the node_bwd launch before this one (mlp_common.cuh):
   int32_t* sched;           // ready flags set by node_bwd, {next tile, CTAs done}
+  long long* dbg;           // developer trace (MGN_CTA_TRACE builds)
+  int dbg_cap;
 };
 
 __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Params p) {
@@ -1422,7 +1427,9 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
   const uint64_t pol_keep = policy_evict_last();
   int* s_tile = reinterpret_cast<int*>(tail->red);
   uint32_t it = 0;
+  cta_trace(p.dbg, p.dbg_cap, 1, 0);
   for (long long tile = blockIdx.x;; tile += gridDim.x, ++it) {
+    if (it == 1) cta_trace(p.dbg, p.dbg_cap, 1, 1);
     if (chained) {      // next tile in index order = the order node_bwd finishes them in; wait for its rows
       if (m.tid == 0) {
         const int t = atomicAdd(p.sched, 1);
@@ -1464,10 +1471,12 @@ __global__ void __launch_bounds__(NT, 1) node_wgrad1_kernel(const NodeWgrad1Para
       mma_commit(&bar_set[b]);
     }
   }
+  cta_trace(p.dbg, p.dbg_cap, 1, 2);
   if (chained) {
     if (m.tid == 0) sched_done(p.sched);
     pdl_wait();       // node_bwd is complete (its gradient flush included): what this launch's successors rely on
   }
+  cta_trace(p.dbg, p.dbg_cap, 1, 3);
   // wait for the last commit of each set (commits complete in order; waiting both is simplest)
   if (it >= 1) mbar_wait(&bar_set[(it - 1) & 1], ((it - 1) >> 1) & 1);
   if (it >= 2) mbar_wait(&bar_set[it & 1], ((it - 2) >> 1) & 1);
@@ -1721,7 +1730,8 @@ extern "C" int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, cons
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && dz1 && x && aggr && grad_block, "node_wgrad1: bad args");
   MGN_CHECK_ARG((ready_in == nullptr) == (sched == nullptr), "node_wgrad1: ready_in and sched go together");
-  NodeWgrad1Params p{N, (const __half*)dz1, x, aggr, grad_block, ready_in, sched};
+  NodeWgrad1Params p{N, (const __half*)dz1, x, aggr, grad_block, ready_in, sched, g_mgn_timeline_host,
+                     g_mgn_timeline_cap_host};
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(node_wgrad1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NODE_WGRAD1_SMEM));

@@ -246,6 +246,24 @@ struct Timeline {        // profiles/r02_ncu_kernels.md)
 };
 #endif
 
+// Developer builds with -DMGN_CTA_TRACE: thread 0 of EVERY CTA records %globaltimer at four points of the kernel into
+// the timeline buffer, at [(slot * 148 + blockIdx.x) * 4 + point] (tools/cta_trace.py: when do a chained consumer's
+// CTAs start relative to its producer's end?).  Compiles to nothing otherwise.
+#ifdef MGN_CTA_TRACE
+__device__ __forceinline__ void cta_trace(long long* buf, int cap, int slot, int point) {
+  if (buf != nullptr && threadIdx.x == 0) {
+    const int i = (slot * 148 + (int)blockIdx.x) * 4 + point;
+    if (i < cap) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      buf[i] = (long long)t;
+    }
+  }
+}
+#else
+__device__ __forceinline__ void cta_trace(long long*, int, int, int) {}
+#endif
+
 // ------------------------------------------------------------------ prefetch / misc
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // one instruction, one thread: a contiguous range (16-byte aligned, multiple of 16 bytes) into L2
