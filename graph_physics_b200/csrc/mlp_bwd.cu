@@ -1217,35 +1217,46 @@ __device__ __forceinline__ uint4 ld_dz16_chunk(const __half* img, int pos, int l
   return ldg_u4(reinterpret_cast<const uint8_t*>(img) + off);
 }
 
-// One half-warp per (node, side): a plain high-occupancy streaming kernel (no shared memory), fp32 sums, 4 rows in flight
+// One half-warp per (node, side): a plain high-occupancy streaming kernel (no shared memory), fp32 sums in list order.
+// The kernel is a chain of dependent loads (row pointers -> positions -> rows): up to 8 rows of a node are in flight
+// at once (a mesh node has ~6 edges: one round for most nodes) and the next task's row pointers are requested before
+// the current task's rows are summed.
 __global__ void __launch_bounds__(256) dp_gather_kernel(const DpGatherParams p) {
   pdl_wait();
   pdl_launch();
   const int l = threadIdx.x & 15;
   const long long ntask = 2 * p.N;
-  for (long long task = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4; task < ntask;
-       task += ((long long)gridDim.x * blockDim.x) >> 4) {
+  const long long stride = ((long long)gridDim.x * blockDim.x) >> 4;
+  long long task = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+  int beg = 0, end = 0;
+  if (task < ntask) {
+    const int32_t* rp = (task & 1) ? p.rowptr_s : p.rowptr;
+    beg = __ldg(rp + (task >> 1));
+    end = __ldg(rp + (task >> 1) + 1);
+  }
+  for (; task < ntask; task += stride) {
     const long long n = task >> 1;
     const int side = (int)(task & 1);
-    const int32_t* rp = side ? p.rowptr_s : p.rowptr;
-    const int beg = __ldg(rp + n), end = __ldg(rp + n + 1);
+    const long long nt = task + stride;
+    int nbeg = 0, nend = 0;
+    if (nt < ntask) {
+      const int32_t* rp = (nt & 1) ? p.rowptr_s : p.rowptr;
+      nbeg = __ldg(rp + (nt >> 1));
+      nend = __ldg(rp + (nt >> 1) + 1);
+    }
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
 #pragma unroll 1
-    for (int j = beg; j < end; j += 4) {
-      uint4 v[4];
+    for (int j = beg; j < end; j += 8) {
+      int pos[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (j + u < end) {
-          const int pos = side ? __ldg(p.out_pos + j + u) : j + u;
-          v[u] = ld_dz16_chunk(p.dz16, pos, l);
-        } else {
-          v[u] = make_uint4(0, 0, 0, 0);
-        }
-      }
+      for (int u = 0; u < 8; ++u) pos[u] = (j + u < end) ? (side ? __ldg(p.out_pos + j + u) : j + u) : -1;
+      uint4 v[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) v[u] = pos[u] >= 0 ? ld_dz16_chunk(p.dz16, pos[u], l) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
         float f[8];
         unpack8(v[u], f);
 #pragma unroll
@@ -1256,6 +1267,8 @@ __global__ void __launch_bounds__(256) dp_gather_kernel(const DpGatherParams p) 
     pk.x = pack_h2(acc[0], acc[1]); pk.y = pack_h2(acc[2], acc[3]);
     pk.z = pack_h2(acc[4], acc[5]); pk.w = pack_h2(acc[6], acc[7]);
     *reinterpret_cast<uint4*>(p.dP + n * 256 + side * 128 + 8 * l) = pk;
+    beg = nbeg;
+    end = nend;
   }
 }
 

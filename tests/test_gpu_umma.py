@@ -93,8 +93,6 @@ def test_m64_accumulator_lanes():
     assert float(d[rest].abs().max()) == 0.0
 
 
-@pytest.mark.skipif(os.environ.get("MGN_TEST_PAIR", "0") != "1",
-                    reason="CTA-pair probe (round-2 preparation): not yet confirmed on a B200; run with MGN_TEST_PAIR=1")
 @pytest.mark.parametrize("n,ksteps,a_tmem", [(128, 8, 0), (128, 8, 1), (256, 8, 0), (64, 4, 1)])
 def test_cta_pair_product(n, ksteps, a_tmem):
     """tcgen05.mma.cta_group::2 on a cluster of two CTAs (selftest.cu: umma_selftest_pair_kernel): M = 256, every CTA
