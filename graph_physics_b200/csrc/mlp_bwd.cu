@@ -952,6 +952,8 @@ struct NodeBwdParams {
   long long* dbg;           // developer timeline (MGN_TIMELINE builds)
   int dbg_cap;
   int32_t* ready_out;       // or null: ready_out[tile] = 1 once the tile's dz1, g_x, g_aggr rows are written (chaining)
+  int32_t* ready_in;        // or null: ready_in[tile] is set by the p_bwd launch before this one when g_xout's tile is
+                            // complete (both kernels give tile t to CTA t mod grid, so the static assignment stays)
 };
 
 __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) {
@@ -987,8 +989,9 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  pdl_wait();        // the previous kernel in the stream is complete: global memory may be touched from here on
-  pdl_launch();      // (common.cuh) the next kernel may start its own prologue under this one
+  const bool chained_in = p.ready_in != nullptr;
+  if (!chained_in) pdl_wait();  // the previous kernel in the stream is complete: global memory may be touched
+  pdl_launch();                 // (common.cuh) the next kernel may start its own prologue under this one
   const uint32_t tm_W = tmem_slot, tm_dW4 = tmem_slot + 128, tm_dW3 = tmem_slot + 256, tm_dW2 = tmem_slot + 384;
   const uint32_t qoff = m.lane_off + m.c0;
   const uint32_t uW[2] = {smem_u32(sW[0]), smem_u32(sW[1])};
@@ -1040,7 +1043,13 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
       bulk_g2s(sH2, reinterpret_cast<const uint8_t*>(p.h2) + (size_t)tile * SLOT, SLOT, &bar_h);
       bulk_g2s(sH1, reinterpret_cast<const uint8_t*>(p.h1) + (size_t)tile * SLOT, SLOT, &bar_h);
     }
-    load8_f32_to_tile(sG, 128, 0, p.g_xout, m, rf, pol_keep);
+    if (chained_in) {          // the upstream rows of this tile come from the p_bwd launch that may still be running
+      if (m.tid == 0) tile_acquire(p.ready_in, tile);
+      __syncthreads();
+      load8_f32_to_tile_cg(sG, 128, 0, p.g_xout, m, rf);
+    } else {
+      load8_f32_to_tile(sG, 128, 0, p.g_xout, m, rf, pol_keep);
+    }
     tl.stamp();   // 1 g tile built
     mbar_wait(&bar_h, it & 1);
     tile_ready();
@@ -1049,7 +1058,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
     // point of its tile, so a prefetch issued with them would only double the burst)
     if (m.tid == 32 && tile + gridDim.x < num_tiles) {
       const long long nt = tile + gridDim.x;
-      prefetch_tile_rows_l2(p.g_xout, nt * TILE_ROWS, p.N, 512);
+      if (!chained_in) prefetch_tile_rows_l2(p.g_xout, nt * TILE_ROWS, p.N, 512);
       bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h3) + (size_t)nt * SLOT, SLOT);
       bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h2) + (size_t)nt * SLOT, SLOT);
       bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.h1) + (size_t)nt * SLOT, SLOT);
@@ -1123,7 +1132,9 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const long long g = rf(i);
-      old[i] = g >= 0 ? ld_f4_hint(p.g_xout + g * H + 4 * m.lane, pol_keep) : make_float4(0.f, 0.f, 0.f, 0.f);
+      old[i] = g < 0 ? make_float4(0.f, 0.f, 0.f, 0.f)
+                     : (chained_in ? __ldcg(reinterpret_cast<const float4*>(p.g_xout + g * H + 4 * m.lane))
+                                   : ld_f4_hint(p.g_xout + g * H + 4 * m.lane, pol_keep));
     }
     {  // dz1' tile -> global fp16 (half-warp per row)
       const int hw = m.lane >> 4, q = m.lane & 15;
@@ -1176,6 +1187,7 @@ __global__ void __launch_bounds__(NT, 1) node_bwd_kernel(const NodeBwdParams p) 
   }
   tl.stamp();     // loop done
   cta_trace(p.dbg, p.dbg_cap, 0, 2);
+  if (chained_in) pdl_wait();   // p_bwd is complete (its gradient flush included): what this launch's successors rely on
   fence_after_sync();
   flush_acc_bulk3(tm_dW4 + qoff, tm_dW3 + qoff, tm_dW2 + qoff, p.grad + GB_N_W4, p.grad + GB_N_W3, p.grad + GB_N_W2,
                   smem, m, pol_keep);
@@ -1279,6 +1291,7 @@ struct PBwdParams {
   float* g_x;               // read-modify-write
   const __half* Wcat;       // [256 x 128] panel tile (64 KB)
   float* grad;
+  int32_t* ready_out;       // or null: ready_out[tile] = 1 once the tile's g_x rows are written (chaining with node_bwd)
 };
 
 __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
@@ -1383,6 +1396,7 @@ __global__ void __launch_bounds__(NT, 1) p_bwd_kernel(const PBwdParams p) {
                    make_float4(old[i].x + v.x, old[i].y + v.y, old[i].z + v.z, old[i].w + v.w), pol_keep);
     }
     __syncthreads();
+    if (p.ready_out != nullptr && m.tid == 0) tile_publish(p.ready_out, tile);
   }
   fence_after_sync();
   // dW_i -> edge_block.0.weight[:, 128:256], dW_j -> [:, 256:384]
@@ -1658,18 +1672,18 @@ extern "C" int mgn_edge_bwd_saved(int64_t E, int64_t N, const void* h1, const vo
 // flags bit 0: the block has no RMSNorm (see mgn_node_fwd2)
 extern "C" int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                              float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out,
-                             void* stream_);
+                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_in,
+                             int32_t* ready_out, void* stream_);
 extern "C" int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                              float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
                              const float* scale, float* grad_block, int flags, int norm_dim, void* stream_) {
   return mgn_node_bwd3(N, g_xout, h1, h2, h3, g_x, g_aggr, dz1, packed, b4, scale, grad_block, flags, norm_dim, nullptr,
-                       stream_);
+                       nullptr, stream_);
 }
 extern "C" int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                              float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out,
-                             void* stream_) {
+                             const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_in,
+                             int32_t* ready_out, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && g_xout && h1 && h2 && h3 && g_x && g_aggr && dz1 && packed && b4 && scale && grad_block,
                 "node_bwd: bad args");
@@ -1680,6 +1694,7 @@ extern "C" int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, con
   p.b4 = b4; p.scale = scale; p.grad = grad_block; p.no_norm = flags & 1;
   p.dbg = g_mgn_timeline_host; p.dbg_cap = g_mgn_timeline_cap_host;
   p.ready_out = ready_out;
+  p.ready_in = ready_in;
   MGN_CHECK_ARG(norm_dim > 0 && norm_dim <= H, "node_bwd: norm_dim must be in 1..128");
   p.norm_d = (float)norm_dim; p.inv_sqrt_d = 1.0f / sqrtf((float)norm_dim);
   static bool attr = false;
@@ -1714,12 +1729,18 @@ extern "C" int mgn_dp_gather(int64_t N, const void* dz16, const int32_t* rowptr,
 }
 
 // Backward of the per-node partial products (mgn_p_fwd): g_x += dP [W_i ; W_j], dW_i, dW_j, db1.
+extern "C" int mgn_p_bwd_c(int64_t N, const void* dP, const float* x, float* g_x, const void* packed,
+                           float* grad_block, int32_t* ready_out, void* stream_);
 extern "C" int mgn_p_bwd(int64_t N, const void* dP, const float* x, float* g_x, const void* packed,
                          float* grad_block, void* stream_) {
+  return mgn_p_bwd_c(N, dP, x, g_x, packed, grad_block, nullptr, stream_);
+}
+extern "C" int mgn_p_bwd_c(int64_t N, const void* dP, const float* x, float* g_x, const void* packed,
+                           float* grad_block, int32_t* ready_out, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   MGN_CHECK_ARG(N > 0 && dP && x && g_x && packed && grad_block, "p_bwd: bad args");
   PBwdParams p{N, (const __half*)dP, x, g_x,
-               reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_WCAT), grad_block};
+               reinterpret_cast<const __half*>(reinterpret_cast<const uint8_t*>(packed) + PK_WCAT), grad_block, ready_out};
   static bool attr = false;
   if (!attr) {
     MGN_CUDA(cudaFuncSetAttribute(p_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_BWD_SMEM));

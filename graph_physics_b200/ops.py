@@ -268,8 +268,9 @@ def chain_state(num_rows: int, device) -> torch.Tensor:
 
 
 def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None, dz1=None, norm: bool = True,
-             norm_dim: int = H, chain: Optional[torch.Tensor] = None):
-    """-> (g_x direct part, g_aggr, dz1 fp16).  chain: `chain_state(N)` shared with the node_wgrad1 call that follows."""
+             norm_dim: int = H, chain: Optional[torch.Tensor] = None, chain_in: Optional[torch.Tensor] = None):
+    """-> (g_x direct part, g_aggr, dz1 fp16).  chain: `chain_state(N)` shared with the node_wgrad1 call that follows.
+    chain_in: the `chain_state(N)` the p_bwd call that wrote `g_xout` (earlier on the same stream) was given."""
     N = g_xout.shape[0]
     if g_x is None:
         g_x = torch.empty_like(g_xout)
@@ -280,7 +281,7 @@ def node_bwd(g_xout, saves, packed, b4, scale, grad_block, g_x=None, g_aggr=None
     h1, h2, h3 = saves
     L.check(L.lib().mgn_node_bwd3(L.i64(N), L.p(g_xout), L.p(h1), L.p(h2), L.p(h3), L.p(g_x), L.p(g_aggr), L.p(dz1),
                                   L.p(packed), L.p(b4), L.p(scale), L.p(grad_block), L.i32(0 if norm else 1), L.i32(norm_dim),
-                                  L.p(chain), L.stream()))
+                                  L.p(chain_in), L.p(chain), L.stream()))
     return g_x, g_aggr, dz1
 
 
@@ -300,10 +301,11 @@ def dp_gather(dz16, csr, dP=None):
     return dP
 
 
-def p_bwd(dP, x, g_x, packed, grad_block):
-    """g_x += dP [W_i ; W_j] (in place); dW_i, dW_j, db1 into grad_block."""
-    L.check(L.lib().mgn_p_bwd(L.i64(x.shape[0]), L.p(dP), L.p(x), L.p(g_x), L.p(packed), L.p(grad_block),
-                              L.stream()))
+def p_bwd(dP, x, g_x, packed, grad_block, chain: Optional[torch.Tensor] = None):
+    """g_x += dP [W_i ; W_j] (in place); dW_i, dW_j, db1 into grad_block.  chain: `chain_state(N)` shared with the
+    node_bwd call that consumes g_x next (it MUST follow: the flags this call sets are cleared by that consumer)."""
+    L.check(L.lib().mgn_p_bwd_c(L.i64(x.shape[0]), L.p(dP), L.p(x), L.p(g_x), L.p(packed), L.p(grad_block),
+                                L.p(chain), L.stream()))
     return g_x
 
 

@@ -241,6 +241,7 @@ class _ProcessorFn(torch.autograd.Function):
         g_aggr = torch.empty((N, H), dtype=torch.float32, device=dev)
         dz1 = torch.empty((N, H), dtype=torch.float16, device=dev)
         chain_nw = ops.chain_state(N, dev) if ops.CHAIN else None     # node_bwd -> node_wgrad1, tile by tile
+        chain_pn = ops.chain_state(N, dev) if (ops.CHAIN and K > 1) else None     # p_bwd(k) -> node_bwd(k-1)
         dz16 = ops.e16_image(E, dev)       # dz1 of the current step: written by edge_bwd, gathered by p_bwd
         dP = torch.empty((N, 2 * H), dtype=torch.float16, device=dev)
         if E > 0:
@@ -254,7 +255,7 @@ class _ProcessorFn(torch.autograd.Function):
         for k in range(K - 1, -1, -1):
             b = prm[18 * k:18 * (k + 1)]
             _timed("node_bwd", ops.node_bwd, gx, ctx.saves[k], packed[k], b[16], b[17], grads[k], g_x=gx_new,
-                   g_aggr=g_aggr, dz1=dz1, norm_dim=nd, chain=chain_nw)
+                   g_aggr=g_aggr, dz1=dz1, norm_dim=nd, chain=chain_nw, chain_in=chain_pn if k < K - 1 else None)
             _timed("node_wgrad1", ops.node_wgrad1, dz1, xs[k], ctx.aggrs[k], grads[k], chain=chain_nw)
             if E > 0:
                 if ctx.esaves[k] is not None:
@@ -269,7 +270,7 @@ class _ProcessorFn(torch.autograd.Function):
                 have_ge = True
                 _timed("edge_wgrad1", ops.edge_wgrad1, dz16, e16s[k], E, grads[k])
                 _timed("dp_gather", ops.dp_gather, dz16, csr, dP)
-            _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k])
+            _timed("p_bwd", ops.p_bwd, dP, xs[k], gx_new, packed[k], grads[k], chain=chain_pn if k > 0 else None)
             gx, gx_new = gx_new, gx
             if GRAD_SYNC is not None:        # the reduction of block k starts now: it needs the final values
                 grads[k].mul_(inv_s)

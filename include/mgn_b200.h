@@ -201,7 +201,8 @@ int mgn_node_bwd2(int64_t N, const float* g_xout, const void* h1, const void* h2
  * ({next tile, CTAs done}) start at zero and are left at zero.  NULL for both = plain stream order. */
 int mgn_node_bwd3(int64_t N, const float* g_xout, const void* h1, const void* h2, const void* h3,
                   float* g_x, float* g_aggr, void* dz1, const void* packed, const float* b4,
-                  const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_out, void* stream);
+                  const float* scale, float* grad_block, int flags, int norm_dim, int32_t* ready_in, int32_t* ready_out,
+                  void* stream);
 int mgn_node_wgrad1c(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                      int32_t* ready_in, int32_t* sched, void* stream);
 /* The same pair in the forward: mgn_node_fwd3 publishes ready_out[tile] after the tile's x_out rows, mgn_p_fwd_c (the
@@ -212,6 +213,11 @@ int mgn_node_fwd3(int64_t N, const float* x, const float* aggr, float* x_out, co
                   int32_t* ready_out, void* stream);
 int mgn_p_fwd_c(int64_t N, const float* x, const void* packed, const float* b1_edge, void* P, int32_t* ready_in,
                 int32_t* sched, void* stream);
+/* And p_bwd(k) -> node_bwd(k-1): mgn_p_bwd_c publishes ready_out[tile] after the tile's g_x rows; mgn_node_bwd3's
+ * ready_in (same buffer) makes it wait per tile instead of for the whole p_bwd launch.  Both kernels give tile t to CTA
+ * t mod grid, so this pair needs no tile counter. */
+int mgn_p_bwd_c(int64_t N, const void* dP, const float* x, float* g_x, const void* packed, float* grad_block,
+                int32_t* ready_out, void* stream);
 /* dW1' += dz1^T [x | aggr] */
 int mgn_node_wgrad1(int64_t N, const void* dz1, const float* x, const float* aggr, float* grad_block,
                     void* stream);
