@@ -278,3 +278,29 @@ def test_chained_node_wgrad1_equals_stream_order(golden_dir, copies):
         ops.split_grad_block(rest_ref)["node_block.0.weight"].zero_()
         ops.split_grad_block(rest_got)["node_block.0.weight"].zero_()
         assert float((rest_got - rest_ref).abs().max()) <= 1e-5 * float(rest_ref.abs().max())
+
+
+def test_chained_entry_points_reject_half_a_chain():
+    """ready_in and sched of a chained consumer go together: one without the other is an argument error (code < 0 ->
+    ValueError), not a launch that would wait for flags nobody counts."""
+    from graph_physics_b200 import _lib as L, ops
+    L.require_device()
+    dev = "cuda"
+    N = 300
+    x, aggr = torch.randn(N, 128, device=dev), torch.randn(N, 128, device=dev)
+    dz1 = torch.zeros((N, 128), dtype=torch.float16, device=dev)
+    grad = torch.zeros(ops.GRAD_BLOCK_FLOATS, dtype=torch.float32, device=dev)
+    flags = ops.chain_state(N, dev)
+    with pytest.raises(ValueError, match="go together"):
+        L.check(L.lib().mgn_node_wgrad1c(L.i64(N), L.p(dz1), L.p(x), L.p(aggr), L.p(grad), L.p(flags), L.p(None),
+                                         L.stream()))
+    ew = [torch.randn(128, 384, device=dev) * 0.05] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    nw = [torch.randn(128, 256, device=dev) * 0.06] + [torch.randn(128, 128, device=dev) * 0.08 for _ in range(3)]
+    packed = ops.pack_block(ew, nw)
+    P = torch.empty((N, 256), dtype=torch.float16, device=dev)
+    b1 = torch.zeros(128, device=dev)
+    with pytest.raises(ValueError, match="go together"):
+        L.check(L.lib().mgn_p_fwd_c(L.i64(N), L.p(x), L.p(packed), L.p(b1), L.p(P), L.p(None), L.p(flags[3:]),
+                                    L.stream()))
+    torch.cuda.synchronize()
+    assert int(flags.abs().sum()) == 0
