@@ -15,7 +15,7 @@ void mgn_set_error(const char* fmt, ...) {
 
 extern "C" const char* mgn_last_error(void) { return g_err; }
 
-extern "C" int mgn_version(void) { return 100; /* 0.1.0 */ }
+extern "C" int mgn_version(void) { return 200; /* 0.2.0: round-2 ABI (mgn_edge_fwd removed; carry / rowptr / norm_dim arguments; chained entry points) */ }
 
 // 0 if the current device can run the sm_100a kernels, MGN_EUNSUPPORTED otherwise.
 extern "C" int mgn_check_device(void) {

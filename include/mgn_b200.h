@@ -26,7 +26,7 @@ extern "C" {
 #endif
 
 const char* mgn_last_error(void);
-int mgn_version(void);
+int mgn_version(void);      /* 200 = 0.2.0 (round 2: mgn_edge_fwd removed; carry / rowptr / norm_dim arguments; chained entry points) */
 int mgn_check_device(void); /* 0 iff the current device is sm_100 */
 /* Every mbarrier wait inside the kernels is bounded (4 s): a wait that starves writes {source line, block, thread,
  * barrier, parity} to host-mapped memory and traps, so the launch fails with a cudaError instead of spinning.
