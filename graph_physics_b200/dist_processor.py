@@ -32,8 +32,15 @@ H = ops.H
 
 
 class PartitionEngine:
-    """One rank's share of the loop.  The caller fills the halo rows of `x_ext(k)` before `fwd_step(k)` and returns
-    the halo rows of `g_ext()` to their owners after `bwd_step(k)`."""
+    """One rank's share of the loop.  What crosses a partition boundary is what the edge kernels gather by SENDER: the
+    sender half of the per-node partial products P (fp16, 256 B per node) in the forward, and the sender half of dP in
+    the backward -- half the bytes of the x / g_x rows, and no rank computes P, dP or g_x for nodes it does not own:
+
+        fwd_p(k)   P[:owned] = p_fwd(x_k)                ; caller: halo rows of P_j <- owners (halo_send_fwd / halo_recv_fwd)
+        fwd_rest(k) edge update, aggregation, node update on the owned nodes
+        bwd_a(k)   node_bwd .. dp_gather -> dP (owned + halo) ; caller: owners' dP_j += halo rows (halo_send_bwd / halo_recv_bwd)
+        bwd_b(k)   p_bwd on the owned nodes
+    """
 
     def __init__(self, part: Partition, block_params: Sequence[Sequence[torch.Tensor]], need_grad: bool = True,
                  csr: Optional[G.CSRGraph] = None, need_edges: bool = True):
@@ -55,9 +62,7 @@ class PartitionEngine:
         self.dev, self.E = dev, e_local.shape[0]
         self.packed = torch.empty((K, ops.packed_block_bytes()), dtype=torch.uint8, device=dev)
         _timed("pack", ops.pack_blocks, [[b[i] for i in _E_W + _N_W] for b in self.prm], out=self.packed)
-        x0 = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
-        x0[:part.num_owned] = x_owned.detach()
-        self.xs: List[Optional[torch.Tensor]] = [x0]
+        self.xs: List[Optional[torch.Tensor]] = [x_owned.detach().contiguous()]
         self.e = e_local.detach().contiguous()
         # between steps the edge stream is an fp16 image + fp16 remainder (csrc/edge_fwd_hl.cu, as in processor.py):
         # only step 0 reads fp32 rows, only the last step writes them (and only if somebody wants them)
@@ -73,22 +78,36 @@ class PartitionEngine:
             self.aggr = torch.empty((part.num_ext, H), dtype=torch.float32, device=dev)
             self.img_bufs = [ops.e16_image(self.E, dev) for _ in range(min(K, 2))]
 
-    def x_ext(self, k: int) -> torch.Tensor:
+    def x_cur(self, k: int) -> torch.Tensor:
         return self.xs[k] if self.need_grad else self.xs[-1]
 
-    def fwd_step(self, k: int) -> None:
+    def fwd_p(self, k: int) -> None:
+        """P of the owned nodes; the halo rows' sender halves come from their owners next."""
+        part, dev = self.part, self.dev
+        n_own, n_ext = part.num_owned, part.num_ext
+        self.P_k = torch.empty((n_ext, 2 * H), dtype=torch.float16, device=dev) if self.need_grad else self.P
+        _timed("p_fwd", ops.p_fwd, self.x_cur(k), self.packed[k], self.prm[k][1], out=self.P_k[:n_own])
+
+    def halo_send_fwd(self) -> torch.Tensor:
+        """[len(send_index), 128] fp16: sender halves of the owned rows the other ranks gather from."""
+        p = self.part
+        return self.P_k[:p.num_owned].index_select(0, p.send_index)[:, H:].contiguous()
+
+    def halo_recv_fwd(self, rows: torch.Tensor) -> None:
+        self.P_k[self.part.num_owned:, H:] = rows
+
+    def fwd_rest(self, k: int) -> None:
         part, K, dev, E = self.part, self.K, self.dev, self.E
         n_own, n_ext = part.num_owned, part.num_ext
         b, csr, ng = self.prm[k], self.csr, self.need_grad
-        x = self.x_ext(k)
-        x_out = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
+        x = self.x_cur(k)
+        x_out = torch.empty((n_own, H), dtype=torch.float32, device=dev)
+        P = self.P_k
         if ng:
-            P = torch.empty((n_ext, 2 * H), dtype=torch.float16, device=dev)
             aggr = torch.empty((n_ext, H), dtype=torch.float32, device=dev)
             sv = ops.node_saves(n_own, dev)
         else:
-            P, aggr, sv = self.P, self.aggr, None
-        _timed("p_fwd", ops.p_fwd, x, self.packed[k], b[1], out=P)
+            aggr, sv = self.aggr, None
         if E > 0:
             last = k + 1 == K
             e_out = (self.e_last if last else None) if self.hl else self.e_bufs[k & 1]
@@ -125,8 +144,8 @@ class PartitionEngine:
             if ng:
                 self.e16s.append(None)
                 self.esaves.append(None)
-        _timed("node_fwd", ops.node_fwd, x[:n_own], aggr[:n_own], self.packed[k], b[10], b[12], b[14], b[16], b[17],
-               x_out=x_out[:n_own], saves=sv)
+        _timed("node_fwd", ops.node_fwd, x, aggr[:n_own], self.packed[k], b[10], b[12], b[14], b[16], b[17],
+               x_out=x_out, saves=sv)
         if ng:
             self.aggrs.append(aggr); self.Ps.append(P); self.saves.append(sv); self.xs.append(x_out)
         else:
@@ -134,7 +153,7 @@ class PartitionEngine:
 
     def outputs(self, need_edges: bool = True):
         """(x_K of the owned nodes, e_K of the local edges in the caller's local edge order)."""
-        x = self.xs[-1][:self.part.num_owned]
+        x = self.xs[-1]
         if not need_edges:
             return x, self.e.new_empty((0, H))
         if not self.need_edges and self.hl and self.K > 1:
@@ -164,9 +183,8 @@ class PartitionEngine:
         part, K, dev, E, csr = self.part, self.K, self.dev, self.E, self.csr
         n_own, n_ext = part.num_owned, part.num_ext
         self.s, self.inv_s = s, 1.0 / s
-        self.gx = torch.zeros((n_ext, H), dtype=torch.float32, device=dev)
-        if g_x is not None:
-            self.gx[:n_own] = g_x.detach() * s
+        self.gx = (g_x.detach() * s).contiguous() if g_x is not None else \
+            torch.zeros((n_own, H), dtype=torch.float32, device=dev)
         self.gx_new = torch.empty_like(self.gx)
         if g_e is not None and E > 0:
             ge = g_e.detach() if csr.identity else g_e.detach().index_select(0, csr.perm_long)
@@ -183,19 +201,15 @@ class PartitionEngine:
         else:
             self.dP.zero_()
 
-    def g_ext(self) -> torch.Tensor:
-        return self.gx
-
-    def bwd_step(self, k: int) -> None:
+    def bwd_a(self, k: int) -> None:
+        """node_bwd .. dp_gather: dP of the owned AND the halo nodes (the halo rows hold what this rank's edges send)."""
         part, E, csr = self.part, self.E, self.csr
         n_own, n_ext = part.num_owned, part.num_ext
         b, pk, gk = self.prm[k], self.packed[k], self.grads[k]
         gx, gx_new = self.gx, self.gx_new
-        _timed("node_bwd", ops.node_bwd, gx[:n_own], self.saves[k], pk, b[16], b[17], gk, g_x=gx_new[:n_own],
+        _timed("node_bwd", ops.node_bwd, gx, self.saves[k], pk, b[16], b[17], gk, g_x=gx_new,
                g_aggr=self.g_aggr[:n_own], dz1=self.dz1)
-        if part.num_halo:
-            gx_new[n_own:].zero_()            # halo rows only collect what this rank's edges send back
-        _timed("node_wgrad1", ops.node_wgrad1, self.dz1, self.xs[k][:n_own], self.aggrs[k][:n_own], gk)
+        _timed("node_wgrad1", ops.node_wgrad1, self.dz1, self.xs[k], self.aggrs[k][:n_own], gk)
         if E > 0:
             if self.esaves[k] is not None:
                 if not self.have_ge:
@@ -209,7 +223,24 @@ class PartitionEngine:
             self.have_ge = True
             _timed("edge_wgrad1", ops.edge_wgrad1, self.dz16, self.e16s[k], E, gk)
             _timed("dp_gather", ops.dp_gather, self.dz16, csr, self.dP)
-        _timed("p_bwd", ops.p_bwd, self.dP, self.xs[k], gx_new, pk, gk)
+
+    def halo_send_bwd(self) -> torch.Tensor:
+        """[num_halo, 128] fp16: sender halves of dP this rank holds for its halo nodes."""
+        return self.dP[self.part.num_owned:, H:].contiguous()
+
+    def halo_recv_bwd(self, rows: torch.Tensor) -> None:
+        """rows [len(send_index), 128] fp16 from the other ranks: added to the owners' dP_j.  A slab cut of a grid sends
+        every boundary node to ONE neighbour: `send_index` then has no duplicates and the adds have one order; a node
+        that several ranks gather from receives its (two or three) fp16 contributions in arrival order."""
+        p = self.part
+        if rows.numel():
+            self.dP[:p.num_owned, H:].index_add_(0, p.send_index, rows)
+
+    def bwd_b(self, k: int) -> None:
+        n_own = self.part.num_owned
+        pk, gk = self.packed[k], self.grads[k]
+        gx, gx_new = self.gx, self.gx_new
+        _timed("p_bwd", ops.p_bwd, self.dP[:n_own], self.xs[k], gx_new, pk, gk)
         self.gx, self.gx_new = gx_new, gx
         gk.mul_(self.inv_s)
         self.saves[k] = None; self.aggrs[k] = None; self.Ps[k] = None; self.e16s[k] = None; self.esaves[k] = None
@@ -218,7 +249,7 @@ class PartitionEngine:
     def input_grads(self, need_gx: bool = True, need_ge: bool = True):
         """(g_x0 of the owned nodes, g_e0 of the local edges in the caller's local order); call after the halo return
         of step 0."""
-        g_x0 = self.gx[:self.part.num_owned] * self.inv_s if need_gx else None
+        g_x0 = self.gx * self.inv_s if need_gx else None
         g_e0 = None
         if need_ge:
             ge = (self.ge_buf * self.inv_s) if self.have_ge else torch.zeros_like(self.ge_buf)
@@ -243,9 +274,14 @@ class PartitionedProcessorFn(torch.autograd.Function):
         eng = PartitionEngine(part, blocks, need_grad=need_grad, csr=csr, need_edges=need_edges)
         halo = HaloExchange(part, group)
         eng.fwd_begin(x_owned, e_local)
+        multi = part.world > 1
+        recv = torch.empty((part.num_halo, H), dtype=torch.float16, device=x_owned.device) if multi else None
         for k in range(K):
-            halo.forward(eng.x_ext(k))
-            eng.fwd_step(k)
+            eng.fwd_p(k)
+            if multi:
+                halo.rows_forward(eng.halo_send_fwd(), recv)
+                eng.halo_recv_fwd(recv)
+            eng.fwd_rest(k)
         x, e = eng.outputs(need_edges)
         if not need_edges:
             ctx.mark_non_differentiable(e)
@@ -262,9 +298,13 @@ class PartitionedProcessorFn(torch.autograd.Function):
         if multi:
             dist.all_reduce(amax, op=dist.ReduceOp.MAX, group=ctx.group)
         eng.bwd_begin(g_x, g_e, eng.scale_from_amax(amax))
+        recv = torch.empty((int(eng.part.send_index.numel()), H), dtype=torch.float16, device=eng.dev) if multi else None
         for k in range(K - 1, -1, -1):
-            eng.bwd_step(k)
-            halo.backward(eng.g_ext())
+            eng.bwd_a(k)
+            if multi:
+                halo.rows_backward(eng.halo_send_bwd(), recv)
+                eng.halo_recv_bwd(recv)
+            eng.bwd_b(k)
         if multi:
             dist.all_reduce(eng.grads, op=dist.ReduceOp.SUM, group=ctx.group)
         g_x0, g_e0 = eng.input_grads(ctx.needs_input_grad[0], ctx.needs_input_grad[1])
@@ -304,9 +344,12 @@ def run_partitions_local(parts: Sequence[Partition], x: torch.Tensor, e: torch.T
         lo = p.node_begin
         eng.fwd_begin(x[lo:lo + p.num_owned].contiguous(), e.index_select(0, p.edge_ids))
     for k in range(K):
-        halo.forward_all([eng.x_ext(k) for eng in engs])
         for eng in engs:
-            eng.fwd_step(k)
+            eng.fwd_p(k)
+        halo.rows_forward_all([eng.P_k[:eng.part.num_owned, H:] for eng in engs],
+                              [eng.P_k[eng.part.num_owned:, H:] for eng in engs])
+        for eng in engs:
+            eng.fwd_rest(k)
     x_out, e_out = torch.empty_like(x), torch.empty_like(e)
     for p, eng in zip(parts, engs):
         xo, eo = eng.outputs(True)
@@ -327,8 +370,11 @@ def run_partitions_local(parts: Sequence[Partition], x: torch.Tensor, e: torch.T
         eng.bwd_begin(gxl, gel, s)
     for k in range(K - 1, -1, -1):
         for eng in engs:
-            eng.bwd_step(k)
-        halo.backward_all([eng.g_ext() for eng in engs])
+            eng.bwd_a(k)
+        halo.rows_backward_all([eng.dP[eng.part.num_owned:, H:] for eng in engs],
+                               [eng.dP[:eng.part.num_owned, H:] for eng in engs])
+        for eng in engs:
+            eng.bwd_b(k)
     gx0, ge0 = torch.empty_like(x), torch.empty_like(e)
     for p, eng in zip(parts, engs):
         a, b = eng.input_grads()

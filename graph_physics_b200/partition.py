@@ -106,25 +106,38 @@ class HaloExchange:
     def __init__(self, part: Partition, group=None):
         self.part, self.group = part, group
 
+    def rows_forward(self, send: torch.Tensor, recv: torch.Tensor) -> None:
+        """Owners -> halo copies.  send [len(send_index), C]: this rank's owned rows in `send_index` order (grouped by
+        destination rank); recv [num_halo, C] (contiguous): receives the halo rows in `halo_global` order."""
+        p = self.part
+        if p.world == 1:
+            return
+        dist.all_to_all_single(recv, send, output_split_sizes=p.recv_counts, input_split_sizes=p.send_counts,
+                               group=self.group)
+
+    def rows_backward(self, send: torch.Tensor, recv: torch.Tensor) -> None:
+        """Halo copies -> owners.  send [num_halo, C]: what this rank holds for its halo rows; recv
+        [len(send_index), C]: receives, in `send_index` order, what the other ranks hold for rows this rank owns."""
+        p = self.part
+        if p.world == 1:
+            return
+        dist.all_to_all_single(recv, send, output_split_sizes=p.send_counts, input_split_sizes=p.recv_counts,
+                               group=self.group)
+
     def forward(self, x_ext: torch.Tensor) -> None:
         """x_ext [num_ext, C]: fill the halo rows (num_owned:) with the owners' current rows (0:num_owned)."""
         p = self.part
         if p.world == 1:
             return
-        send = x_ext[:p.num_owned].index_select(0, p.send_index)
-        recv = x_ext[p.num_owned:]
-        dist.all_to_all_single(recv, send, output_split_sizes=p.recv_counts, input_split_sizes=p.send_counts,
-                               group=self.group)
+        self.rows_forward(x_ext[:p.num_owned].index_select(0, p.send_index), x_ext[p.num_owned:])
 
     def backward(self, g_ext: torch.Tensor) -> None:
         """g_ext [num_ext, C]: add the gradient every rank holds for its halo copies to the owners' rows."""
         p = self.part
         if p.world == 1:
             return
-        send = g_ext[p.num_owned:].contiguous()
         recv = g_ext.new_empty((int(p.send_index.numel()), g_ext.shape[1]))
-        dist.all_to_all_single(recv, send, output_split_sizes=p.send_counts, input_split_sizes=p.recv_counts,
-                               group=self.group)
+        self.rows_backward(g_ext[p.num_owned:].contiguous(), recv)
         g_ext[:p.num_owned].index_add_(0, p.send_index, recv)
 
 
@@ -145,6 +158,32 @@ class LocalHaloExchange:
                 if sel.numel():
                     src = p.halo_global[sel] - int(p.bounds[q])
                     x[p.num_owned + sel] = x_exts[q][:self.parts[q].num_owned].index_select(0, src)
+
+    def rows_forward_all(self, owned: Sequence[torch.Tensor], halos: Sequence[torch.Tensor]) -> None:
+        """owned[q] [num_owned_q, C] (any strides): rows the partitions own; halos[p] [num_halo_p, C] (any strides):
+        receive the owners' rows of p's halo nodes."""
+        for p, h in zip(self.parts, halos):
+            if p.num_halo == 0:
+                continue
+            owner = torch.searchsorted(p.bounds.to(p.halo_global.device), p.halo_global, right=True) - 1
+            for q in range(p.world):
+                sel = torch.nonzero(owner == q, as_tuple=False).flatten()
+                if sel.numel():
+                    h[sel] = owned[q].index_select(0, p.halo_global[sel] - int(p.bounds[q]))
+
+    def rows_backward_all(self, halos: Sequence[torch.Tensor], owned: Sequence[torch.Tensor]) -> None:
+        """owned[q] += what every partition p holds in halos[p] for rows q owns (all reads before any add)."""
+        adds = []
+        for p, h in zip(self.parts, halos):
+            if p.num_halo == 0:
+                continue
+            owner = torch.searchsorted(p.bounds.to(p.halo_global.device), p.halo_global, right=True) - 1
+            for q in range(p.world):
+                sel = torch.nonzero(owner == q, as_tuple=False).flatten()
+                if sel.numel():
+                    adds.append((q, p.halo_global[sel] - int(p.bounds[q]), h[sel].clone()))
+        for q, idx, val in adds:
+            owned[q].index_add_(0, idx, val)
 
     def backward_all(self, g_exts: Sequence[torch.Tensor]) -> None:
         adds = []
