@@ -3,10 +3,10 @@
 Every rank runs the same fused kernels as `processor.py` on its partition (`partition.Partition`): its owned nodes,
 the halo copies of remote senders, and every edge whose receiver it owns.  Per message-passing step:
 
-  forward   halo rows of x_k <- owners (all-to-all-v) ; P = p_fwd(x_k[owned | halo]) ; e_{k+1}, aggr = edge_fwd ;
-            x_{k+1}[owned] = node_fwd
+  forward   P[owned] = p_fwd(x_k) ; halo rows of P's sender half <- owners (all-to-all-v, fp16) ;
+            e_{k+1}, aggr = edge_fwd ; x_{k+1}[owned] = node_fwd
   backward  node_bwd, node_wgrad1 on the owned rows ; edge_bwd, edge_wgrad1, dp_gather on the local edges ;
-            p_bwd on owned + halo rows ; halo rows of g_x -> owners, summed there (all-to-all-v)
+            halo rows of dP's sender half -> owners, added there (all-to-all-v, fp16) ; p_bwd on the owned rows
 
 and once per sweep: the gradient pre-scale is agreed with a MAX all-reduce (one float), the 15 flat weight-gradient
 blocks are SUMMED over ranks (every rank holds a partial sum over its edges / nodes).
